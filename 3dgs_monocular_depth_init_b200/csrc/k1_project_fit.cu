@@ -1,0 +1,184 @@
+// k1_project_fit.cu -- SfM-point projection + filtering (a2), normal-equation accumulation with
+// pinv solve (a3) and the SfM-density patch histogram (a8).  One CTA per view; the per-view
+// point sets are a few thousand points, so everything is warp-shuffle / block reductions.
+#include "common.cuh"
+
+namespace mdi {
+
+constexpr int kK1Threads = 512;
+
+// a2.  Reference: points_from_depth.py:145-162 (project, round half-even, cast) and :111-142
+// (bounds / z >= 0 validity, the "< 1/4 in bounds" rule, mask lookup, ordered filter).
+__global__ void __launch_bounds__(kK1Threads)
+project_filter_kernel(const MdiView* __restrict__ views, const float* __restrict__ sfm_xyz,
+                      const int32_t* __restrict__ sfm_index, int64_t slots,
+                      int32_t* __restrict__ uv, float* __restrict__ z_out,
+                      int32_t* __restrict__ n_inbounds, int32_t* __restrict__ n_valid,
+                      int32_t* __restrict__ status) {
+  __shared__ int scan_smem[33];
+  __shared__ int s_inb;
+  const int v = blockIdx.x;
+  const MdiView vw = views[v];
+  const int M = vw.sfm_count;
+  const int64_t base = vw.sfm_begin;
+  if (threadIdx.x == 0) s_inb = 0;
+  __syncthreads();
+
+  int out_base = 0, inb_local = 0;
+  for (int start = 0; start < M; start += blockDim.x) {
+    const int i = start + threadIdx.x;
+    bool ok = false;
+    int iu = 0, iv = 0;
+    float zc = 0.f;
+    if (i < M) {
+      const int64_t src = sfm_index ? (int64_t)sfm_index[base + i] : (base + i);
+      const float X = sfm_xyz[3 * src + 0], Y = sfm_xyz[3 * src + 1], Z = sfm_xyz[3 * src + 2];
+      // P @ [X;1]: dot products accumulated left to right, no contraction
+      const float* P = vw.P;
+      float cx = fadd(fadd(fadd(fmul(P[0], X), fmul(P[1], Y)), fmul(P[2], Z)), P[3]);
+      float cy = fadd(fadd(fadd(fmul(P[4], X), fmul(P[5], Y)), fmul(P[6], Z)), P[7]);
+      zc = fadd(fadd(fadd(fmul(P[8], X), fmul(P[9], Y)), fmul(P[10], Z)), P[11]);
+      float fu = rintf(fdiv(cx, zc));  // torch.round = half to even
+      float fv = rintf(fdiv(cy, zc));
+      // 0 <= u < W, 0 <= v < H, z >= 0 ; NaN / inf / out-of-int64 all fail the comparisons
+      bool inb = (fu >= 0.f) && (fu < (float)vw.W) && (fv >= 0.f) && (fv < (float)vw.H) &&
+                 (zc >= 0.f);
+      if (inb) {
+        iu = (int)fu;
+        iv = (int)fv;
+        ++inb_local;
+        ok = vw.mask ? (vw.mask[(int64_t)iv * vw.W + iu] != 0) : true;
+      }
+    }
+    int total;
+    int pos = block_excl_scan(ok ? 1 : 0, scan_smem, &total);
+    if (ok) {
+      const int64_t o = base + out_base + pos;
+      uv[o] = iu;
+      uv[slots + o] = iv;
+      z_out[o] = zc;
+    }
+    out_base += total;
+  }
+  int inb_w = warp_sum_i32(inb_local);
+  if (lane_id() == 0 && inb_w) atomicAdd(&s_inb, inb_w);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    n_inbounds[v] = s_inb;
+    n_valid[v] = out_base;
+    // torch.sum(valid) < M / 4  (true division)  <=>  4 * n < M
+    status[v] = (4LL * (int64_t)s_inb < (int64_t)M) ? MDI_STATUS_LOW_CONFIDENCE : MDI_STATUS_OK;
+  }
+}
+
+// a3 + a8.  Reference: lstsqrs.py:39-50 (gather depth[v,u]), :21-26 (normal equations + pinv);
+// num_sfm_points_mask.py:45-63 (points per patch, > threshold blocks the patch).
+__global__ void __launch_bounds__(kK1Threads)
+gather_fit_kernel(const MdiView* __restrict__ views, int64_t slots,
+                  const int32_t* __restrict__ uv, const float* __restrict__ z,
+                  const int32_t* __restrict__ n_valid, float* __restrict__ d_out,
+                  double* __restrict__ sums, float* __restrict__ scale_shift, int write_fit,
+                  int patch_threshold, uint8_t* __restrict__ patch_blocked) {
+  __shared__ int s_hist[MDI_PATCH_STRIDE];
+  __shared__ double s_red[5][kK1Threads / 32];
+  const int v = blockIdx.x;
+  const MdiView vw = views[v];
+  const int n = n_valid[v];
+  const int64_t base = vw.sfm_begin;
+  const int n_patches = vw.grid_h * vw.grid_w;
+  if (patch_blocked)
+    for (int p = threadIdx.x; p < MDI_PATCH_STRIDE; p += blockDim.x) s_hist[p] = 0;
+  __syncthreads();
+
+  double sdd = 0, sd = 0, sdg = 0, sg = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int iu = uv[base + i], iv = uv[slots + base + i];
+    const float g = z[base + i];
+    const float dv = vw.depth[(int64_t)iv * vw.W + iu];
+    d_out[base + i] = dv;
+    const double dd = (double)dv, gd = (double)g;
+    sdd += dd * dd; sd += dd; sdg += dd * gd; sg += gd;
+    if (patch_blocked) {
+      const int pr = iv / vw.patch_h, pc = iu / vw.patch_w;
+      if (pr < vw.grid_h && pc < vw.grid_w) atomicAdd(&s_hist[pr * vw.grid_w + pc], 1);
+    }
+  }
+  sdd = warp_sum_f64(sdd); sd = warp_sum_f64(sd); sdg = warp_sum_f64(sdg); sg = warp_sum_f64(sg);
+  if (lane_id() == 0) {
+    const int w = warp_id();
+    s_red[0][w] = sdd; s_red[1][w] = sd; s_red[2][w] = sdg; s_red[3][w] = sg;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0, b = 0, c = 0, e = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+      a += s_red[0][w]; b += s_red[1][w]; c += s_red[2][w]; e += s_red[3][w];
+    }
+    sums[5 * v + 0] = a; sums[5 * v + 1] = b; sums[5 * v + 2] = (double)n;
+    sums[5 * v + 3] = c; sums[5 * v + 4] = e;
+    if (write_fit) {
+      float h0, h1;
+      solve_normal_eq(a, b, (double)n, c, e, &h0, &h1);
+      scale_shift[2 * v + 0] = h0;
+      scale_shift[2 * v + 1] = h1;
+    }
+  }
+  if (patch_blocked) {
+    for (int p = threadIdx.x; p < MDI_PATCH_STRIDE; p += blockDim.x)
+      patch_blocked[(int64_t)v * MDI_PATCH_STRIDE + p] =
+          (p < n_patches && s_hist[p] > patch_threshold) ? 1 : 0;
+  }
+}
+
+__global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_t n,
+                                         const float* __restrict__ scale_shift,
+                                         float* __restrict__ out) {
+  const float s = scale_shift[0], t = scale_shift[1];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    out[i] = align_depth(depth[i], s, t);
+}
+
+}  // namespace mdi
+
+extern "C" int mdi_project_filter(const MdiView* views, int n_views, const float* sfm_xyz,
+                                  const int32_t* sfm_index, int64_t slots, int32_t* uv, float* z,
+                                  int32_t* n_inbounds, int32_t* n_valid, int32_t* status,
+                                  void* stream) {
+  MDI_REQUIRE(n_views >= 0 && slots >= 0, "mdi_project_filter: negative size");
+  if (n_views == 0) return MDI_OK;
+  MDI_REQUIRE(views && sfm_xyz && uv && z && n_inbounds && n_valid && status,
+              "mdi_project_filter: null pointer");
+  mdi::project_filter_kernel<<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
+      views, sfm_xyz, sfm_index, slots, uv, z, n_inbounds, n_valid, status);
+  MDI_CHECK_LAUNCH("mdi_project_filter");
+  return MDI_OK;
+}
+
+extern "C" int mdi_gather_fit(const MdiView* views, int n_views, int64_t slots, const int32_t* uv,
+                              const float* z, const int32_t* n_valid, float* d, double* sums,
+                              float* scale_shift, int write_fit, int patch_threshold,
+                              uint8_t* patch_blocked, void* stream) {
+  MDI_REQUIRE(n_views >= 0 && slots >= 0, "mdi_gather_fit: negative size");
+  if (n_views == 0) return MDI_OK;
+  MDI_REQUIRE(views && uv && z && n_valid && d && sums, "mdi_gather_fit: null pointer");
+  MDI_REQUIRE(!write_fit || scale_shift, "mdi_gather_fit: write_fit without scale_shift");
+  mdi::gather_fit_kernel<<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
+      views, slots, uv, z, n_valid, d, sums, scale_shift, write_fit, patch_threshold,
+      patch_blocked);
+  MDI_CHECK_LAUNCH("mdi_gather_fit");
+  return MDI_OK;
+}
+
+extern "C" int mdi_apply_scale_shift(const float* depth, int64_t n, const float* scale_shift,
+                                     float* out, void* stream) {
+  MDI_REQUIRE(n >= 0, "mdi_apply_scale_shift: negative size");
+  if (n == 0) return MDI_OK;
+  MDI_REQUIRE(depth && scale_shift && out, "mdi_apply_scale_shift: null pointer");
+  int blocks = (int)((n + 1023) / 1024);
+  if (blocks > mdi::kSMs * 16) blocks = mdi::kSMs * 16;
+  mdi::apply_scale_shift_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(depth, n, scale_shift,
+                                                                          out);
+  MDI_CHECK_LAUNCH("mdi_apply_scale_shift");
+  return MDI_OK;
+}

@@ -1,0 +1,223 @@
+/*
+ * mdi_b200.h -- C ABI of libmdi_b200.so: the B200 (sm_100a) kernels behind the
+ * monocular-depth point-cloud initialisation path of deivse/3dgs_monocular_depth_init.
+ *
+ * Every entry point is batched over views, asynchronous on the caller's stream, re-entrant,
+ * and writes only into caller-allocated DEVICE buffers (plain pointers + sizes; no torch
+ * types).  Return value: 0 on success, otherwise a negative MDI_E* code; the message is
+ * available from mdi_last_error().  Per-view soft failures (too few SfM points in bounds,
+ * empty adaptive-subsampling population) are DATA: status[view] != 0, and the Python host
+ * layer turns them into the reference's exceptions.
+ *
+ * Reference interface replaced by each entry point (paths relative to the reference repo):
+ *   mdi_project_filter      gs_init_compare/depth_prediction/points_from_depth.py:111-142,145-162
+ *   mdi_gather_fit          gs_init_compare/depth_alignment/alignment/lstsqrs.py:9-54
+ *                           gs_init_compare/depth_subsampling/num_sfm_points_mask.py:7-64
+ *   mdi_ransac              gs_init_compare/depth_alignment/alignment/ransacs.py:60-189
+ *   mdi_apply_scale_shift   lstsqrs.py:51-54 / ransacs.py:186-189 (aligned_depth = depth*s + t)
+ *   mdi_depth_range         gs_init_compare/depth_subsampling/adaptive_subsampling.py:82-98
+ *   mdi_grad_range          points_from_depth.py:192-212 (min / max of the gradient map)
+ *   mdi_keep_mask           static_subsampler.py:11-22, adaptive_subsampling.py:48-79,105-122,
+ *                           pipeline.py:285-288, points_from_depth.py:268-290
+ *   mdi_scan_tiles          points_from_depth.py:292-297 (boolean-index compaction order),
+ *                           monocular_depth_init.py:170-171,183-184 (view-major concat)
+ *   mdi_emit_points         points_from_depth.py:292-312, monocular_depth_init.py:168
+ *   mdi_min_extents         native_modules/subsampling/src/impl.cpp:17-35,70-126
+ *   mdi_merge_subsample     native_modules/subsampling/src/impl.cpp:198-274,313-426
+ *   mdi_knn / mdi_lof       point_cloud_postprocess/postprocess.py:16-22 (sklearn LOF),
+ *                           utils/runner_utils.py:143-147 (knn)
+ */
+#ifndef MDI_B200_H_
+#define MDI_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MDI_ABI_VERSION 1
+
+/* error codes */
+#define MDI_OK 0
+#define MDI_EINVAL (-1)  /* bad argument */
+#define MDI_ECUDA (-2)   /* CUDA runtime error (launch / config) */
+#define MDI_ENOGPU (-3)  /* no sm_100 device */
+
+/* per-view status bits written by the kernels */
+#define MDI_STATUS_OK 0
+#define MDI_STATUS_LOW_CONFIDENCE 1 /* < 1/4 of SfM points in bounds (points_from_depth.py:124) */
+#define MDI_STATUS_EMPTY_STATS 2    /* adaptive subsampling over zero valid pixels (torch raises) */
+
+/* pixels per tile of the mask / compaction kernels (one CTA per tile) */
+#define MDI_TILE_PX 4096
+#define MDI_TILE_WORDS (MDI_TILE_PX / 32)
+
+/* max patches of the SfM-density grid per view (20 on the small axis, <= 102 on the large) */
+#define MDI_PATCH_STRIDE 2048
+
+/* image element kinds for the RGB gather */
+#define MDI_IMAGE_F32_UNIT 0 /* float32 already in 0..1 (InputImage.data)          */
+#define MDI_IMAGE_F32_255 1  /* float32 in 0..255, divided by 255.0f on the fly    */
+#define MDI_IMAGE_U8 2       /* uint8, converted and divided by 255.0f on the fly  */
+
+/* subsampling modes */
+#define MDI_SUBSAMPLE_STATIC 0
+#define MDI_SUBSAMPLE_ADAPTIVE 1
+
+/* mask-composition flags of mdi_keep_mask */
+#define MDI_KEEP_PRED_MASK 1  /* & predicted.mask                       (pipeline.py:287)          */
+#define MDI_KEEP_SENTINEL 2   /* & aligned != -42.0                     (pipeline.py:253,287)      */
+#define MDI_KEEP_NONNEG 4     /* & aligned >= 0                         (points_from_depth.py:270) */
+#define MDI_KEEP_PATCH 8      /* & SfM-density patch mask               (points_from_depth.py:276) */
+#define MDI_KEEP_GRAD 16      /* & depth-gradient mask                  (points_from_depth.py:271) */
+#define MDI_KEEP_SUBSAMPLE 32 /* & subsampler mask                      (points_from_depth.py:290) */
+
+/* RANSAC loss kinds */
+#define MDI_LOSS_RANSAC 0 /* outlier count       (ransacs.py:60) */
+#define MDI_LOSS_MSAC 1   /* truncated quadratic (ransacs.py:64) */
+
+/*
+ * One view.  The array of descriptors lives in DEVICE memory (the host builds it once per
+ * scene and copies it); all pointers inside are device pointers (the image may be a
+ * device-mapped pinned host pointer: only kept pixels are read from it).
+ */
+typedef struct MdiView {
+  const float* depth;    /* [H*W] float32 predicted depth, row-major                   */
+  const uint8_t* mask;   /* [H*W] bool/uint8 predicted mask, or NULL = all valid       */
+  const void* image;     /* [H*W*3] pixels, element kind given per call                */
+  int32_t H, W;
+  int32_t sfm_begin;     /* first slot of this view in the per-point arrays            */
+  int32_t sfm_count;     /* M: number of SfM points of this view                       */
+  int64_t px_begin;      /* first byte of this view in the keep-mask buffer            */
+  int64_t tile_begin;    /* first global tile of this view                             */
+  int32_t n_tiles;       /* ceil(H*W / MDI_TILE_PX)                                    */
+  int32_t patch_h, patch_w, grid_h, grid_w; /* SfM-density patch geometry              */
+  int32_t _pad;
+  float P[12];           /* 3x4 projection K R^T [I|-C]  (points_from_depth.py:231-233) */
+  float Kinv[9];         /* inverse intrinsics           (points_from_depth.py:303)     */
+  float c2w[12];         /* first three rows of cam2world (points_from_depth.py:304-309) */
+} MdiView;
+
+typedef struct MdiRansacConfig {
+  float inlier_threshold; /* applied to the SQUARED residual (ransacs.py:137) */
+  int32_t max_iters;
+  double confidence;
+  int32_t sample_size;    /* must be 4 when sample_idx is generated on device; <= 8 otherwise */
+  int32_t min_iters;
+  int32_t loss_kind;      /* MDI_LOSS_*                                        */
+  int32_t _pad;
+  uint64_t seed;          /* device sampler seed when sample_idx == NULL       */
+} MdiRansacConfig;
+
+typedef struct MdiSubsampleConfig {
+  int32_t mode;           /* MDI_SUBSAMPLE_*                                   */
+  int32_t static_factor;  /* static stride                                     */
+  int32_t factor_min;     /* adaptive range (depth_subsampling/config.py:11-12) */
+  int32_t factor_max;
+  int32_t flags;          /* MDI_KEEP_* bits                                   */
+  float grad_thresh;      /* depth_grad_mask_thresh                            */
+} MdiSubsampleConfig;
+
+const char* mdi_last_error(void);
+int mdi_abi_version(void);
+/* returns 0 if device `device` is an sm_100 part, MDI_ENOGPU otherwise */
+int mdi_check_device(int device);
+/* sizeof(MdiView), so that the host-side struct packing can be asserted */
+int mdi_sizeof_view(void);
+
+/*
+ * a2: project the SfM points of every view, filter, compact in order.
+ *   sfm_xyz   [Np,3] float32 world points; sfm_index int32 (concatenated per view, slot
+ *   sfm_begin..sfm_begin+M) indexes sfm_xyz, or NULL when the points are already gathered
+ *   (then slot i reads sfm_xyz[i]).
+ * Outputs (slot ranges of each view): uv int32 [2,S] (row 0 = x/u, row 1 = y/v, S = total
+ *   slots, plane stride `slots`), z float32 [S]; n_inbounds/n_valid/status int32 [V].
+ */
+int mdi_project_filter(const MdiView* views, int n_views, const float* sfm_xyz,
+                       const int32_t* sfm_index, int64_t slots, int32_t* uv, float* z,
+                       int32_t* n_inbounds, int32_t* n_valid, int32_t* status, void* stream);
+
+/*
+ * a3 + a8: gather d_i = depth[v_i,u_i], accumulate the normal equations in fp64, solve with
+ * torch.linalg.pinv semantics, count points per patch.
+ *   sums      float64 [V,5] = (sum d*d, sum d, n, sum d*g, sum g)
+ *   scale_shift float32 [V,2] (written only if write_fit != 0)
+ *   patch_blocked uint8 [V, MDI_PATCH_STRIDE] or NULL
+ */
+int mdi_gather_fit(const MdiView* views, int n_views, int64_t slots, const int32_t* uv,
+                   const float* z, const int32_t* n_valid, float* d, double* sums,
+                   float* scale_shift, int write_fit, int patch_threshold,
+                   uint8_t* patch_blocked, void* stream);
+
+/*
+ * a4: LO-RANSAC / MSAC, one CTA per view, one warp per hypothesis, (d, g) staged in shared
+ * memory by a 1-D bulk (TMA) copy.  sample_idx int32 [V, max_iters, sample_size] or NULL
+ * (device sampler).  Outputs: scale_shift float32 [V,2]; inliers uint8 [S] (slot layout) or
+ * NULL; n_iter / n_inliers int32 [V] (n_iter = last loop index, as printed at ransacs.py:183).
+ */
+int mdi_ransac(const MdiView* views, int n_views, const float* d, const float* z,
+               const int32_t* n_valid, const int32_t* status, const int32_t* sample_idx,
+               const MdiRansacConfig* cfg, float* scale_shift, uint8_t* inliers,
+               int32_t* n_iter, int32_t* n_inliers, void* stream);
+
+/* aligned = depth * s + t as two separately rounded fp32 operations; scale_shift on device */
+int mdi_apply_scale_shift(const float* depth, int64_t n, const float* scale_shift, float* out,
+                          void* stream);
+
+/*
+ * a7 (statistics): per view, over pixels with mask & (aligned != -42): min, max and the exact
+ * order statistics torch.quantile(., 0.25 / 0.75) needs; writes lo_hi float32 [V,2] =
+ * (max(min, q1 - 1.5 iqr), min(max, q3 + 1.5 iqr)) and ORs MDI_STATUS_EMPTY_STATS into status.
+ *   workspace: mdi_depth_range_workspace_bytes(n_views) bytes, zeroed by the call itself.
+ *   flags: MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL select the population.
+ */
+int64_t mdi_depth_range_workspace_bytes(int n_views);
+int mdi_depth_range(const MdiView* views, int n_views, int64_t total_tiles,
+                    const float* scale_shift, int32_t* status, int flags, void* workspace,
+                    float* lo_hi, float* quantiles /* [V,4] q1,q3,min,max or NULL */,
+                    void* stream);
+
+/* a9 (statistics): min and max of |dx|+|dy| of the aligned depth per view -> grad_range [V,2] */
+int mdi_grad_range(const MdiView* views, int n_views, int64_t total_tiles,
+                   const float* scale_shift, const int32_t* status, float* grad_range,
+                   void* stream);
+
+/*
+ * a5-a10 (predicate): composes the keep mask of every pixel.
+ *   keep      uint8 [sum H*W] at px_begin (may be NULL), bits uint32 [total_tiles*128] (bit i of
+ *   word w of tile t = pixel t*4096 + 32*w + i), tile_counts int32 [total_tiles].
+ */
+int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_tiles,
+                  const float* scale_shift, const int32_t* status, const float* lo_hi,
+                  const float* grad_range, const uint8_t* patch_blocked,
+                  const MdiSubsampleConfig* cfg, uint8_t* keep, uint32_t* bits,
+                  int32_t* tile_counts, void* stream);
+
+/*
+ * exclusive scan of tile_counts in global (view-major) order -> tile_offsets int64
+ * [total_tiles]; per-view counts / offsets int64 [V]; total int64 [1].
+ */
+int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_tiles,
+                   const int32_t* tile_counts, int64_t* tile_offsets, int64_t* view_counts,
+                   int64_t* view_offsets, int64_t* total, void* stream);
+
+/*
+ * a10 + a11: for every kept pixel in row-major order: unproject to world space and gather RGB.
+ *   xyz float32 [N,3], rgb float32 [N,3] (either may be NULL), written at tile_offsets.
+ */
+int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
+                    const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
+                    int image_kind, float* xyz, float* rgb, void* stream);
+
+/*
+ * a13: minimal Gaussian extent per point over all cameras that see it (else -1).
+ *   K float32 [C,9], P float32 [C,12], sizes int32 [C,2] = (W,H).
+ */
+int mdi_min_extents(const float* pts, int64_t n, const float* K, const float* P,
+                    const int32_t* sizes, int n_cams, float* extents, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDI_B200_H_ */
