@@ -1,0 +1,157 @@
+// k4_emit.cu -- order-preserving compaction offsets (tile scan) and the unprojection + RGB
+// gather of the kept pixels (a10, a11).
+#include "common.cuh"
+
+namespace mdi {
+
+constexpr int kScanThreads = 1024;
+
+// Single-CTA exclusive scan over all tiles in global (view-major, row-major) order.  The tile
+// count is tiny next to the pixel traffic (<= ~1M ints for 500 4K views).
+__global__ void __launch_bounds__(kScanThreads)
+scan_tiles_kernel(const MdiView* __restrict__ views, int n_views, int64_t total_tiles,
+                  const int32_t* __restrict__ tile_counts, int64_t* __restrict__ tile_offsets,
+                  int64_t* __restrict__ view_counts, int64_t* __restrict__ view_offsets,
+                  int64_t* __restrict__ total) {
+  __shared__ int scan_smem[33];
+  __shared__ long long s_base;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  // each thread owns 4 consecutive tiles per step so the loads are 128-bit
+  for (int64_t start = 0; start < total_tiles; start += (int64_t)kScanThreads * 4) {
+    const int64_t i0 = start + (int64_t)threadIdx.x * 4;
+    int c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) c[k] = (i0 + k < total_tiles) ? tile_counts[i0 + k] : 0;
+    const int mine = c[0] + c[1] + c[2] + c[3];
+    int tot;
+    const int excl = block_excl_scan(mine, scan_smem, &tot);
+    long long o = s_base + excl;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (i0 + k < total_tiles) tile_offsets[i0 + k] = o;
+      o += c[k];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_base += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && total) *total = s_base;
+  __syncthreads();
+  const long long grand = s_base;
+  for (int v = threadIdx.x; v < n_views; v += blockDim.x) {
+    const int64_t tb = views[v].tile_begin;
+    const int64_t te = tb + views[v].n_tiles;
+    const long long b = (tb < total_tiles) ? tile_offsets[tb] : grand;
+    const long long e = (te < total_tiles) ? tile_offsets[te] : grand;
+    if (view_offsets) view_offsets[v] = b;
+    if (view_counts) view_counts[v] = e - b;
+  }
+}
+
+constexpr int kEmitThreads = MDI_TILE_WORDS;  // one thread per bit word
+
+// Reference: points_from_depth.py:292-312.  pc = ((x+.5) z, (y+.5) z, z); world =
+// c2w[:3,:3] (Kinv pc) + c2w[:3,3]; dot products left to right, no contraction.
+// RGB: image.view(-1,3)[mask] (monocular_depth_init.py:128,168), image/255.0 as a division.
+template <int IMAGE_KIND>
+__global__ void __launch_bounds__(kEmitThreads)
+emit_points_kernel(const MdiView* __restrict__ views, int n_views,
+                   const float* __restrict__ scale_shift, const uint32_t* __restrict__ bits,
+                   const int64_t* __restrict__ tile_offsets, float* __restrict__ xyz,
+                   float* __restrict__ rgb) {
+  __shared__ int scan_smem[33];
+  const int64_t tile = blockIdx.x;
+  uint32_t word = bits[tile * MDI_TILE_WORDS + threadIdx.x];
+  int tot;
+  const int excl = block_excl_scan(__popc(word), scan_smem, &tot);
+  if (tot == 0) return;
+  const int v = find_view(views, n_views, tile);
+  const MdiView& vw = views[v];
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const int W = vw.W;
+  const float* depth = vw.depth;
+  const float* Ki = vw.Kinv;
+  const float* M = vw.c2w;
+  int64_t out = tile_offsets[tile] + excl;
+  const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX + (int64_t)threadIdx.x * 32;
+  while (word) {
+    const int b = __ffs(word) - 1;
+    word &= word - 1;
+    const int64_t p = px0 + b;
+    const int row = (int)(p / W);
+    const int col = (int)(p - (int64_t)row * W);
+    const float z = align_depth(__ldg(&depth[p]), s, t);
+    if (xyz) {
+      const float px = fmul(fadd((float)col, 0.5f), z);
+      const float py = fmul(fadd((float)row, 0.5f), z);
+      const float cx = fadd(fadd(fmul(Ki[0], px), fmul(Ki[1], py)), fmul(Ki[2], z));
+      const float cy = fadd(fadd(fmul(Ki[3], px), fmul(Ki[4], py)), fmul(Ki[5], z));
+      const float cz = fadd(fadd(fmul(Ki[6], px), fmul(Ki[7], py)), fmul(Ki[8], z));
+      xyz[3 * out + 0] = fadd(fadd(fadd(fmul(M[0], cx), fmul(M[1], cy)), fmul(M[2], cz)), M[3]);
+      xyz[3 * out + 1] = fadd(fadd(fadd(fmul(M[4], cx), fmul(M[5], cy)), fmul(M[6], cz)), M[7]);
+      xyz[3 * out + 2] = fadd(fadd(fadd(fmul(M[8], cx), fmul(M[9], cy)), fmul(M[10], cz)), M[11]);
+    }
+    if (rgb) {
+      float r, g, bl;
+      if (IMAGE_KIND == MDI_IMAGE_U8) {
+        const uint8_t* im = reinterpret_cast<const uint8_t*>(vw.image) + 3 * p;
+        r = fdiv((float)im[0], 255.0f); g = fdiv((float)im[1], 255.0f); bl = fdiv((float)im[2], 255.0f);
+      } else {
+        const float* im = reinterpret_cast<const float*>(vw.image) + 3 * p;
+        r = im[0]; g = im[1]; bl = im[2];
+        if (IMAGE_KIND == MDI_IMAGE_F32_255) {
+          r = fdiv(r, 255.0f); g = fdiv(g, 255.0f); bl = fdiv(bl, 255.0f);
+        }
+      }
+      rgb[3 * out + 0] = r; rgb[3 * out + 1] = g; rgb[3 * out + 2] = bl;
+    }
+    ++out;
+  }
+}
+
+}  // namespace mdi
+
+extern "C" int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_tiles,
+                              const int32_t* tile_counts, int64_t* tile_offsets,
+                              int64_t* view_counts, int64_t* view_offsets, int64_t* total,
+                              void* stream) {
+  MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_scan_tiles: negative size");
+  MDI_REQUIRE(views && tile_counts && tile_offsets, "mdi_scan_tiles: null pointer");
+  mdi::scan_tiles_kernel<<<1, mdi::kScanThreads, 0, (cudaStream_t)stream>>>(
+      views, n_views, total_tiles, tile_counts, tile_offsets, view_counts, view_offsets, total);
+  MDI_CHECK_LAUNCH("mdi_scan_tiles");
+  return MDI_OK;
+}
+
+extern "C" int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
+                               const float* scale_shift, const uint32_t* bits,
+                               const int64_t* tile_offsets, int image_kind, float* xyz, float* rgb,
+                               void* stream) {
+  MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_emit_points: negative size");
+  if (n_views == 0 || total_tiles == 0) return MDI_OK;
+  MDI_REQUIRE(views && bits && tile_offsets, "mdi_emit_points: null pointer");
+  MDI_REQUIRE(total_tiles < (1LL << 31), "mdi_emit_points: too many tiles");
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)total_tiles;
+  switch (image_kind) {
+    case MDI_IMAGE_F32_UNIT:
+      mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitThreads, 0, st>>>(
+          views, n_views, scale_shift, bits, tile_offsets, xyz, rgb);
+      break;
+    case MDI_IMAGE_F32_255:
+      mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitThreads, 0, st>>>(
+          views, n_views, scale_shift, bits, tile_offsets, xyz, rgb);
+      break;
+    case MDI_IMAGE_U8:
+      mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitThreads, 0, st>>>(
+          views, n_views, scale_shift, bits, tile_offsets, xyz, rgb);
+      break;
+    default:
+      mdi::set_error("mdi_emit_points: unknown image kind %d", image_kind);
+      return MDI_EINVAL;
+  }
+  MDI_CHECK_LAUNCH("mdi_emit_points");
+  return MDI_OK;
+}

@@ -155,11 +155,13 @@ int mdi_gather_fit(const MdiView* views, int n_views, int64_t slots, const int32
  * memory by a 1-D bulk (TMA) copy.  sample_idx int32 [V, max_iters, sample_size] or NULL
  * (device sampler).  Outputs: scale_shift float32 [V,2]; inliers uint8 [S] (slot layout) or
  * NULL; n_iter / n_inliers int32 [V] (n_iter = last loop index, as printed at ransacs.py:183).
+ * max_points >= every n_valid[v] sizes the shared-memory staging; the slot ranges of d / z
+ * must be readable up to the next multiple of 4 elements (the host pads sfm_begin to 4).
  */
 int mdi_ransac(const MdiView* views, int n_views, const float* d, const float* z,
                const int32_t* n_valid, const int32_t* status, const int32_t* sample_idx,
-               const MdiRansacConfig* cfg, float* scale_shift, uint8_t* inliers,
-               int32_t* n_iter, int32_t* n_inliers, void* stream);
+               const MdiRansacConfig* cfg, int max_points, float* scale_shift,
+               uint8_t* inliers, int32_t* n_iter, int32_t* n_inliers, void* stream);
 
 /* aligned = depth * s + t as two separately rounded fp32 operations; scale_shift on device */
 int mdi_apply_scale_shift(const float* depth, int64_t n, const float* scale_shift, float* out,
@@ -173,13 +175,13 @@ int mdi_apply_scale_shift(const float* depth, int64_t n, const float* scale_shif
  *   flags: MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL select the population.
  */
 int64_t mdi_depth_range_workspace_bytes(int n_views);
-int mdi_depth_range(const MdiView* views, int n_views, int64_t total_tiles,
+int mdi_depth_range(const MdiView* views, int n_views, int64_t max_tiles_per_view,
                     const float* scale_shift, int32_t* status, int flags, void* workspace,
                     float* lo_hi, float* quantiles /* [V,4] q1,q3,min,max or NULL */,
                     void* stream);
 
 /* a9 (statistics): min and max of |dx|+|dy| of the aligned depth per view -> grad_range [V,2] */
-int mdi_grad_range(const MdiView* views, int n_views, int64_t total_tiles,
+int mdi_grad_range(const MdiView* views, int n_views, int64_t max_tiles_per_view,
                    const float* scale_shift, const int32_t* status, float* grad_range,
                    void* stream);
 
