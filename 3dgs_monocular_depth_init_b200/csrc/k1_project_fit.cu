@@ -33,11 +33,11 @@ project_filter_kernel(const MdiView* __restrict__ views, const float* __restrict
     if (i < M) {
       const int64_t src = sfm_index ? (int64_t)sfm_index[base + i] : (base + i);
       const float X = sfm_xyz[3 * src + 0], Y = sfm_xyz[3 * src + 1], Z = sfm_xyz[3 * src + 2];
-      // P @ [X;1]: dot products accumulated left to right, no contraction
+      // P @ [X;1] as the sgemm of the reference evaluates it: one FMA chain over k = 0..3
       const float* P = vw.P;
-      float cx = fadd(fadd(fadd(fmul(P[0], X), fmul(P[1], Y)), fmul(P[2], Z)), P[3]);
-      float cy = fadd(fadd(fadd(fmul(P[4], X), fmul(P[5], Y)), fmul(P[6], Z)), P[7]);
-      zc = fadd(fadd(fadd(fmul(P[8], X), fmul(P[9], Y)), fmul(P[10], Z)), P[11]);
+      float cx = dot4_fma(P[0], P[1], P[2], P[3], X, Y, Z);
+      float cy = dot4_fma(P[4], P[5], P[6], P[7], X, Y, Z);
+      zc = dot4_fma(P[8], P[9], P[10], P[11], X, Y, Z);
       float fu = rintf(fdiv(cx, zc));  // torch.round = half to even
       float fv = rintf(fdiv(cy, zc));
       // 0 <= u < W, 0 <= v < H, z >= 0 ; NaN / inf / out-of-int64 all fail the comparisons
@@ -130,6 +130,43 @@ gather_fit_kernel(const MdiView* __restrict__ views, int64_t slots,
   }
 }
 
+// a1.  P = (K @ R^T... precisely the reference's `K @ R @ hstack([eye(3), -C[:, None]])` with
+// R = c2w[:3,:3].T, C = c2w[:3,3] (points_from_depth.py:231-233), each matmul an FMA chain over
+// k like the CPU sgemm that evaluates it.  Also copies Kinv and the top 3 rows of c2w into the
+// descriptors.  One thread per view.
+__global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
+                                     const float* __restrict__ K, const float* __restrict__ c2w,
+                                     const float* __restrict__ Kinv, float* __restrict__ P_out) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_views) return;
+  const float* k = K + 9 * (int64_t)v;
+  const float* m = c2w + 16 * (int64_t)v;
+  float T[3][3];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j)  // R[kk][j] = c2w[j][kk]
+      T[i][j] = __fmaf_rn(k[3 * i + 2], m[4 * j + 2],
+                          __fmaf_rn(k[3 * i + 1], m[4 * j + 1], fmul(k[3 * i + 0], m[4 * j + 0])));
+  float P[12];
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) {  // columns of the identity block: chain of T*1 and T*0 terms
+      float acc = fmul(T[i][0], j == 0 ? 1.f : 0.f);
+      acc = __fmaf_rn(T[i][1], j == 1 ? 1.f : 0.f, acc);
+      acc = __fmaf_rn(T[i][2], j == 2 ? 1.f : 0.f, acc);
+      P[4 * i + j] = acc;
+    }
+    float acc = fmul(T[i][0], -m[3]);
+    acc = __fmaf_rn(T[i][1], -m[7], acc);
+    acc = __fmaf_rn(T[i][2], -m[11], acc);
+    P[4 * i + 3] = acc;
+  }
+  for (int q = 0; q < 12; ++q) {
+    views[v].P[q] = P[q];
+    views[v].c2w[q] = m[q];
+    if (P_out) P_out[12 * (int64_t)v + q] = P[q];
+  }
+  for (int q = 0; q < 9; ++q) views[v].Kinv[q] = Kinv[9 * (int64_t)v + q];
+}
+
 __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_t n,
                                          const float* __restrict__ scale_shift,
                                          float* __restrict__ out) {
@@ -140,6 +177,17 @@ __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_
 }
 
 }  // namespace mdi
+
+extern "C" int mdi_setup_cameras(MdiView* views, int n_views, const float* K, const float* c2w,
+                                 const float* Kinv, float* P_out, void* stream) {
+  MDI_REQUIRE(n_views >= 0, "mdi_setup_cameras: negative size");
+  if (n_views == 0) return MDI_OK;
+  MDI_REQUIRE(views && K && c2w && Kinv, "mdi_setup_cameras: null pointer");
+  mdi::setup_cameras_kernel<<<(n_views + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      views, n_views, K, c2w, Kinv, P_out);
+  MDI_CHECK_LAUNCH("mdi_setup_cameras");
+  return MDI_OK;
+}
 
 extern "C" int mdi_project_filter(const MdiView* views, int n_views, const float* sfm_xyz,
                                   const int32_t* sfm_index, int64_t slots, int32_t* uv, float* z,

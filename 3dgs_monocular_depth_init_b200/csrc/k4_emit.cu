@@ -52,7 +52,7 @@ scan_tiles_kernel(const MdiView* __restrict__ views, int n_views, int64_t total_
 constexpr int kEmitThreads = MDI_TILE_WORDS;  // one thread per bit word
 
 // Reference: points_from_depth.py:292-312.  pc = ((x+.5) z, (y+.5) z, z); world =
-// c2w[:3,:3] (Kinv pc) + c2w[:3,3]; dot products left to right, no contraction.
+// c2w[:3,:3] (Kinv pc) + c2w[:3,3]; dot products as FMA chains (mdi_math.cuh dot3/dot4_fma).
 // RGB: image.view(-1,3)[mask] (monocular_depth_init.py:128,168), image/255.0 as a division.
 template <int IMAGE_KIND>
 __global__ void __launch_bounds__(kEmitThreads)
@@ -86,12 +86,13 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
     if (xyz) {
       const float px = fmul(fadd((float)col, 0.5f), z);
       const float py = fmul(fadd((float)row, 0.5f), z);
-      const float cx = fadd(fadd(fmul(Ki[0], px), fmul(Ki[1], py)), fmul(Ki[2], z));
-      const float cy = fadd(fadd(fmul(Ki[3], px), fmul(Ki[4], py)), fmul(Ki[5], z));
-      const float cz = fadd(fadd(fmul(Ki[6], px), fmul(Ki[7], py)), fmul(Ki[8], z));
-      xyz[3 * out + 0] = fadd(fadd(fadd(fmul(M[0], cx), fmul(M[1], cy)), fmul(M[2], cz)), M[3]);
-      xyz[3 * out + 1] = fadd(fadd(fadd(fmul(M[4], cx), fmul(M[5], cy)), fmul(M[6], cz)), M[7]);
-      xyz[3 * out + 2] = fadd(fadd(fadd(fmul(M[8], cx), fmul(M[9], cy)), fmul(M[10], cz)), M[11]);
+      // inv(K) @ pc and cam2world @ [cam;1]: FMA chains over k like the reference's sgemm
+      const float cx = dot3_fma(Ki[0], Ki[1], Ki[2], px, py, z);
+      const float cy = dot3_fma(Ki[3], Ki[4], Ki[5], px, py, z);
+      const float cz = dot3_fma(Ki[6], Ki[7], Ki[8], px, py, z);
+      xyz[3 * out + 0] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
+      xyz[3 * out + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
+      xyz[3 * out + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
     }
     if (rgb) {
       float r, g, bl;

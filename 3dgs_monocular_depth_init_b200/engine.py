@@ -1,0 +1,386 @@
+"""Batched host driver of the kernels: builds the per-view descriptor table, owns the device
+workspaces (torch tensors: plumbing only) and sequences the C-ABI calls on the current CUDA
+stream.  Both the per-view drop-in functions and the scene-level entry point go through
+`Engine.run`; nothing here computes on the CPU except inv(K) of a1 (3x3, batched).
+
+Reference path restated: points_from_depth.py:215-329 (per view) and
+monocular_depth_init.py:120-184 (scene loop), batched over views.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+TensorOrList = Union[torch.Tensor, Sequence[torch.Tensor]]
+
+
+def patch_geometry(H: int, W: int, n_small: int):
+    """(patch_h, patch_w, grid_h, grid_w) -- num_sfm_points_mask.py:7-35."""
+    small_is_h = H <= W
+    small, large = (H, W) if small_is_h else (W, H)
+    ps_small = small // n_small
+    if ps_small <= 0:
+        raise ZeroDivisionError("image smaller than num_patches_small_axis")
+    n_large = -(-large // ps_small)
+    ps_large = large // n_large
+    if small_is_h:
+        return ps_small, ps_large, n_small, n_large
+    return ps_large, ps_small, n_large, n_small
+
+
+@dataclass
+class ViewInputs:
+    """Inputs of a batch of views.  depth / mask / image are either one stacked tensor
+    ([V,H,W], [V,H,W], [V,H,W,3]) or per-view lists (sizes may differ)."""
+
+    depth: TensorOrList                       # float32 cuda
+    mask: Optional[TensorOrList]              # bool/uint8 cuda; None (or None entries) = all valid
+    image: Optional[TensorOrList]             # float32 / uint8, cuda or pinned host; None = no rgb
+    image_kind: int                           # L.IMAGE_*
+    K: torch.Tensor                           # [V,3,3] cpu
+    c2w: torch.Tensor                         # [V,4,4] cpu
+    sfm_xyz: Optional[torch.Tensor] = None    # [Np,3] float32 cuda
+    sfm_index: Optional[torch.Tensor] = None  # int32 cuda, concatenated per view (padded slots)
+    sfm_counts: Optional[np.ndarray] = None   # [V] points per view
+    # alternative to projection (per-view align API): filtered coords given, slot layout
+    uv: Optional[torch.Tensor] = None         # [2,S] int32 cuda
+    z: Optional[torch.Tensor] = None          # [S] float32 cuda
+    n_valid: Optional[torch.Tensor] = None    # [V] int32 cuda
+    P_override: Optional[torch.Tensor] = None  # [V,3,4] float32 cpu: use instead of computing P
+
+
+@dataclass
+class RunOptions:
+    aligner: Optional[str] = "lstsqrs"       # "lstsqrs" | "ransac" | "msac" | None (scale_shift given)
+    scale_shift: Optional[torch.Tensor] = None  # [V,2] float32 cuda when aligner is None
+    ransac_threshold: float = 0.01
+    ransac_max_iters: int = 2500
+    ransac_confidence: float = 0.999
+    ransac_sample_size: int = 4
+    ransac_min_iters: int = 0
+    ransac_seed: int = 0
+    sample_idx: Optional[torch.Tensor] = None   # [V,max_iters,sample] int32 cuda (parity runs)
+    subsample: object = 10                       # int or "adaptive"
+    factor_min: int = 5
+    factor_max: int = 15
+    use_patch_mask: bool = True
+    num_patches_small_axis: int = 20
+    patch_threshold: int = 15
+    grad_thresh: Optional[float] = None
+    flags: int = L.KEEP_PRED_MASK | L.KEEP_SENTINEL | L.KEEP_NONNEG | L.KEEP_SUBSAMPLE
+    want_keep_mask: bool = True
+    want_xyz: bool = True
+    want_rgb: bool = True
+    want_inliers: bool = False
+    stop_after: Optional[str] = None             # "project" | "fit" | "mask": partial pipelines
+
+
+@dataclass
+class RunResult:
+    n_views: int
+    px_begin: np.ndarray                # [V+1] int64
+    sfm_begin: np.ndarray               # [V+1] int64 (padded slot starts)
+    status: Optional[torch.Tensor] = None        # [V] int32 cuda
+    n_inbounds: Optional[torch.Tensor] = None
+    n_valid: Optional[torch.Tensor] = None
+    uv: Optional[torch.Tensor] = None   # [2,S] int32 cuda
+    z: Optional[torch.Tensor] = None
+    d: Optional[torch.Tensor] = None
+    P: Optional[torch.Tensor] = None    # [V,3,4] float32 cuda
+    sums: Optional[torch.Tensor] = None
+    scale_shift: Optional[torch.Tensor] = None   # [V,2] float32 cuda
+    ransac_iters: Optional[torch.Tensor] = None
+    ransac_inliers: Optional[torch.Tensor] = None
+    inlier_mask: Optional[torch.Tensor] = None
+    lo_hi: Optional[torch.Tensor] = None
+    quantiles: Optional[torch.Tensor] = None
+    grad_range: Optional[torch.Tensor] = None
+    patch_blocked: Optional[torch.Tensor] = None
+    keep: Optional[torch.Tensor] = None  # [sum HW] uint8 cuda
+    xyz: Optional[torch.Tensor] = None   # [N,3] float32 cuda
+    rgb: Optional[torch.Tensor] = None   # [N,3] float32 cuda
+    view_counts: Optional[torch.Tensor] = None   # [V] int64 cuda
+    view_offsets: Optional[torch.Tensor] = None  # [V] int64 cuda
+    total: int = 0
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
+    """(pointer array uint64 [V], shapes) for a stacked tensor or a list (None entries -> 0)."""
+    if x is None:
+        return np.zeros(V, dtype=np.uint64), None
+    if isinstance(x, torch.Tensor):
+        assert x.is_contiguous() and x.shape[0] == V
+        stride = x[0].numel() * x.element_size() if V else 0
+        p = x.data_ptr() + np.arange(V, dtype=np.uint64) * np.uint64(stride)
+        return p.astype(np.uint64), [tuple(x.shape[1:])] * V
+    p = np.zeros(V, dtype=np.uint64)
+    shapes = []
+    for i, t in enumerate(x):
+        if t is None:
+            shapes.append(None)
+            continue
+        assert t.is_contiguous()
+        p[i] = t.data_ptr()
+        shapes.append(tuple(t.shape))
+    return p, shapes
+
+
+class Engine:
+    """Holds cached workspaces per device.  One instance per process / GPU."""
+
+    def __init__(self, device: "torch.device | str" = "cuda"):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.MdiError("the B200 path runs on a CUDA device only (no CPU fallback)")
+        self.lib = L.load()
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", idx)
+        L.check(self.lib.mdi_check_device(idx), "mdi_check_device")
+        self._ws: dict[str, torch.Tensor] = {}
+        self.launches = 0  # kernels launched through this engine (bench `gpu_launches`)
+
+    # cached, grow-only workspace buffers (never shrink: results that alias them are only
+    # valid until the next run() unless the caller asked for owned outputs)
+    def _buf(self, name: str, n: int, dtype: torch.dtype) -> torch.Tensor:
+        t = self._ws.get(name)
+        if t is None or t.numel() < n or t.dtype != dtype:
+            t = torch.empty(max(int(n * 1.25), 16), dtype=dtype, device=self.device)
+            self._ws[name] = t
+        return t[:n]
+
+    # ---- descriptor table ---------------------------------------------------------------------
+    def build_views(self, vin: ViewInputs, opt: RunOptions):
+        V = vin.K.shape[0]
+        dptr, dshapes = _ptrs(vin.depth, V)
+        mptr, _ = _ptrs(vin.mask, V)
+        iptr, _ = _ptrs(vin.image, V)
+        if isinstance(vin.depth, torch.Tensor):
+            assert vin.depth.dtype == torch.float32 and vin.depth.is_cuda
+        else:
+            for t in vin.depth:
+                assert t.dtype == torch.float32 and t.is_cuda
+        Hs = np.array([s[0] for s in dshapes], dtype=np.int64)
+        Ws = np.array([s[1] for s in dshapes], dtype=np.int64)
+        HW = Hs * Ws
+        desc = np.zeros(V, dtype=L.VIEW_DTYPE)
+        desc["depth"], desc["mask"], desc["image"] = dptr, mptr, iptr
+        desc["H"], desc["W"] = Hs, Ws
+        counts = (np.asarray(vin.sfm_counts, dtype=np.int64) if vin.sfm_counts is not None
+                  else np.zeros(V, dtype=np.int64))
+        padded = (counts + 3) & ~3  # 16-byte aligned slot ranges (bulk copies in mdi_ransac)
+        sfm_begin = np.zeros(V + 1, dtype=np.int64)
+        np.cumsum(padded, out=sfm_begin[1:])
+        desc["sfm_begin"], desc["sfm_count"] = sfm_begin[:-1], counts
+        px_begin = np.zeros(V + 1, dtype=np.int64)
+        np.cumsum(HW, out=px_begin[1:])
+        n_tiles = -(-HW // L.TILE_PX)
+        tile_begin = np.zeros(V + 1, dtype=np.int64)
+        np.cumsum(n_tiles, out=tile_begin[1:])
+        desc["px_begin"], desc["tile_begin"], desc["n_tiles"] = px_begin[:-1], tile_begin[:-1], n_tiles
+        if opt.use_patch_mask and V:
+            geo = {}
+            pg = np.empty((V, 4), dtype=np.int32)
+            for i, key in enumerate(zip(Hs.tolist(), Ws.tolist())):
+                g = geo.get(key)
+                if g is None:
+                    g = geo[key] = patch_geometry(key[0], key[1], opt.num_patches_small_axis)
+                    if g[2] * g[3] > L.PATCH_STRIDE:
+                        raise L.MdiError(f"patch grid {g[2]}x{g[3]} exceeds {L.PATCH_STRIDE} patches")
+                pg[i] = g
+            desc["patch_h"], desc["patch_w"], desc["grid_h"], desc["grid_w"] = pg.T
+        else:
+            desc["patch_h"] = desc["patch_w"] = 1
+        return desc, px_begin, tile_begin, sfm_begin
+
+    def _upload(self, name: str, host: torch.Tensor) -> torch.Tensor:
+        dev = self._buf(name, host.numel(), host.dtype)
+        dev.copy_(host.reshape(-1), non_blocking=True)
+        return dev
+
+    # ---- the pipeline -------------------------------------------------------------------------
+    def run(self, vin: ViewInputs, opt: RunOptions) -> RunResult:
+        lib, st = self.lib, _stream()
+        V = int(vin.K.shape[0])
+        desc, px_begin, tile_begin, sfm_begin = self.build_views(vin, opt)
+        total_tiles = int(tile_begin[-1])
+        max_tiles = int(desc["n_tiles"].max()) if V else 0
+        slots = int(sfm_begin[-1]) + 4
+        res = RunResult(n_views=V, px_begin=px_begin, sfm_begin=sfm_begin)
+        if V == 0:
+            return res
+        views = self._upload("views", torch.from_numpy(desc.view(np.uint8).reshape(-1)))
+        vp = views.data_ptr()
+
+        # a1: cameras
+        Kf = vin.K.detach().cpu().float().contiguous()
+        c2wf = vin.c2w.detach().cpu().float().contiguous()
+        Kinv = torch.linalg.inv(Kf)
+        cam = self._upload("cams", torch.cat([Kf.reshape(-1), c2wf.reshape(-1), Kinv.reshape(-1)]))
+        kp = cam.data_ptr()
+        c2wp = kp + 4 * 9 * V
+        kinvp = c2wp + 4 * 16 * V
+        res.P = torch.empty((V, 3, 4), dtype=torch.float32, device=self.device)
+        L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(), st), "mdi_setup_cameras")
+        self.launches += 1
+        if vin.P_override is not None:  # stage-wise parity: feed the oracle's P
+            res.P.copy_(vin.P_override.to(self.device, torch.float32))
+            host_desc = desc.copy()
+            host_desc["P"] = vin.P_override.reshape(V, 12).numpy()
+            host_desc["Kinv"] = Kinv.reshape(V, 9).numpy()
+            host_desc["c2w"] = c2wf[:, :3, :4].reshape(V, 12).numpy()
+            views = self._upload("views", torch.from_numpy(host_desc.view(np.uint8).reshape(-1)))
+            vp = views.data_ptr()
+
+        i32, f32 = torch.int32, torch.float32
+        res.status = torch.zeros(V, dtype=i32, device=self.device)
+        # a2: projection + filtering (or externally supplied coords)
+        if vin.uv is not None:
+            res.uv, res.z, res.n_valid = vin.uv, vin.z, vin.n_valid
+            assert res.uv.shape[1] >= slots - 4 and res.uv.dtype == i32
+            slots = int(res.uv.shape[1])
+        elif vin.sfm_xyz is not None:
+            res.uv = torch.empty((2, slots), dtype=i32, device=self.device)
+            res.z = torch.empty(slots, dtype=f32, device=self.device)
+            res.n_inbounds = torch.empty(V, dtype=i32, device=self.device)
+            res.n_valid = torch.empty(V, dtype=i32, device=self.device)
+            L.check(lib.mdi_project_filter(vp, V, vin.sfm_xyz.data_ptr(), L.ptr(vin.sfm_index), slots,
+                                           res.uv.data_ptr(), res.z.data_ptr(), res.n_inbounds.data_ptr(),
+                                           res.n_valid.data_ptr(), res.status.data_ptr(), st),
+                    "mdi_project_filter")
+            self.launches += 1
+        if opt.stop_after == "project":
+            return res
+
+        # a3 + a8: gather, normal equations, patch histogram
+        have_pts = res.uv is not None
+        use_patch = bool(opt.use_patch_mask and have_pts)
+        if have_pts:
+            res.d = torch.zeros(slots, dtype=f32, device=self.device)
+            res.sums = torch.empty((V, 5), dtype=torch.float64, device=self.device)
+            write_fit = opt.aligner == "lstsqrs"
+            if write_fit:
+                res.scale_shift = torch.empty((V, 2), dtype=f32, device=self.device)
+            if use_patch:
+                res.patch_blocked = torch.empty((V, L.PATCH_STRIDE), dtype=torch.uint8, device=self.device)
+            L.check(lib.mdi_gather_fit(vp, V, slots, res.uv.data_ptr(), res.z.data_ptr(), res.n_valid.data_ptr(),
+                                       res.d.data_ptr(), res.sums.data_ptr(), L.ptr(res.scale_shift),
+                                       1 if write_fit else 0, int(opt.patch_threshold),
+                                       L.ptr(res.patch_blocked), st), "mdi_gather_fit")
+            self.launches += 1
+        # a4: RANSAC / MSAC
+        if opt.aligner in ("ransac", "msac"):
+            assert have_pts, "RANSAC needs SfM points"
+            cfg = L.RansacConfigC(float(opt.ransac_threshold), int(opt.ransac_max_iters),
+                                  float(opt.ransac_confidence), int(opt.ransac_sample_size),
+                                  int(opt.ransac_min_iters),
+                                  L.LOSS_RANSAC if opt.aligner == "ransac" else L.LOSS_MSAC, 0,
+                                  int(opt.ransac_seed) & (2**64 - 1))
+            res.scale_shift = torch.empty((V, 2), dtype=f32, device=self.device)
+            res.ransac_iters = torch.empty(V, dtype=i32, device=self.device)
+            res.ransac_inliers = torch.empty(V, dtype=i32, device=self.device)
+            if opt.want_inliers:
+                res.inlier_mask = torch.zeros(slots, dtype=torch.uint8, device=self.device)
+            if opt.sample_idx is not None:
+                assert opt.sample_idx.dtype == i32 and opt.sample_idx.is_cuda and opt.sample_idx.is_contiguous()
+                assert tuple(opt.sample_idx.shape) == (V, opt.ransac_max_iters, opt.ransac_sample_size)
+            max_pts = int(desc["sfm_count"].max())
+            L.check(lib.mdi_ransac(vp, V, res.d.data_ptr(), res.z.data_ptr(), res.n_valid.data_ptr(),
+                                   res.status.data_ptr(), L.ptr(opt.sample_idx), C.byref(cfg), max_pts,
+                                   res.scale_shift.data_ptr(), L.ptr(res.inlier_mask),
+                                   res.ransac_iters.data_ptr(), res.ransac_inliers.data_ptr(), st),
+                    "mdi_ransac")
+            self.launches += 1
+        elif opt.aligner is None:
+            res.scale_shift = opt.scale_shift
+            if res.scale_shift is not None:
+                assert res.scale_shift.dtype == f32 and tuple(res.scale_shift.shape) == (V, 2)
+        elif opt.aligner != "lstsqrs":
+            raise NotImplementedError(f"aligner {opt.aligner!r} is not on the B200 path")
+        if opt.stop_after == "fit":
+            return res
+
+        # a7 / a9: per-view statistics
+        adaptive = opt.subsample == "adaptive"
+        if not adaptive and not isinstance(opt.subsample, int):
+            raise ValueError(f"Unsupported subsampling factor: {opt.subsample}")
+        flags = opt.flags
+        if use_patch:
+            flags |= L.KEEP_PATCH
+        ssp = L.ptr(res.scale_shift)
+        if adaptive and (flags & L.KEEP_SUBSAMPLE):
+            wsb = int(lib.mdi_depth_range_workspace_bytes(V))
+            ws = self._buf("stats_ws", wsb, torch.uint8)
+            res.lo_hi = torch.empty((V, 2), dtype=f32, device=self.device)
+            res.quantiles = torch.empty((V, 4), dtype=f32, device=self.device)
+            L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
+                                        flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL), ws.data_ptr(),
+                                        res.lo_hi.data_ptr(), res.quantiles.data_ptr(), st), "mdi_depth_range")
+            self.launches += 8
+        if opt.grad_thresh is not None:
+            flags |= L.KEEP_GRAD
+            res.grad_range = torch.empty((V, 2), dtype=f32, device=self.device)
+            L.check(lib.mdi_grad_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
+                                       res.grad_range.data_ptr(), st), "mdi_grad_range")
+            self.launches += 3
+
+        # a5-a10: keep mask, then order-preserving compaction + unprojection + RGB gather
+        scfg = L.SubsampleConfigC(L.SUBSAMPLE_ADAPTIVE if adaptive else L.SUBSAMPLE_STATIC,
+                                  0 if adaptive else int(opt.subsample), int(opt.factor_min),
+                                  int(opt.factor_max), int(flags),
+                                  float(opt.grad_thresh) if opt.grad_thresh is not None else 0.0)
+        if opt.want_keep_mask:
+            res.keep = torch.empty(int(px_begin[-1]), dtype=torch.uint8, device=self.device)
+        bits = self._buf("bits", total_tiles * L.TILE_WORDS, i32)
+        tile_counts = self._buf("tile_counts", total_tiles, i32)
+        L.check(lib.mdi_keep_mask(vp, V, total_tiles, ssp, res.status.data_ptr(), L.ptr(res.lo_hi),
+                                  L.ptr(res.grad_range), L.ptr(res.patch_blocked), C.byref(scfg),
+                                  L.ptr(res.keep), bits.data_ptr(), tile_counts.data_ptr(), st), "mdi_keep_mask")
+        tile_offsets = self._buf("tile_offsets", total_tiles, torch.int64)
+        meta = torch.empty(2 * V + 1, dtype=torch.int64, device=self.device)
+        res.view_counts, res.view_offsets = meta[:V], meta[V:2 * V]
+        L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
+                                   res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
+                                   meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
+        self.launches += 2
+        if opt.stop_after == "mask" or not (opt.want_xyz or opt.want_rgb):
+            res.total = int(meta[2 * V].item())
+            return res
+        # the output size is data dependent: one 8-byte read-back (the only sync of the pipeline)
+        res.total = int(meta[2 * V].item())
+        N = res.total
+        if opt.want_xyz:
+            res.xyz = torch.empty((N, 3), dtype=f32, device=self.device)
+        want_rgb = opt.want_rgb and vin.image is not None
+        if want_rgb:
+            res.rgb = torch.empty((N, 3), dtype=f32, device=self.device)
+        if N:
+            L.check(lib.mdi_emit_points(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
+                                        int(vin.image_kind), L.ptr(res.xyz), L.ptr(res.rgb), st),
+                    "mdi_emit_points")
+            self.launches += 1
+        return res
+
+
+_engines: dict[int, Engine] = {}
+
+
+def get_engine(device: "torch.device | str" = "cuda") -> Engine:
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise L.MdiError(f"device {device!r}: the B200 path has no CPU fallback")
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    eng = _engines.get(idx)
+    if eng is None:
+        with torch.cuda.device(idx):
+            eng = _engines[idx] = Engine(torch.device("cuda", idx))
+    return eng

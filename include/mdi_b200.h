@@ -10,6 +10,7 @@
  * layer turns them into the reference's exceptions.
  *
  * Reference interface replaced by each entry point (paths relative to the reference repo):
+ *   mdi_setup_cameras       gs_init_compare/depth_prediction/points_from_depth.py:229-243
  *   mdi_project_filter      gs_init_compare/depth_prediction/points_from_depth.py:111-142,145-162
  *   mdi_gather_fit          gs_init_compare/depth_alignment/alignment/lstsqrs.py:9-54
  *                           gs_init_compare/depth_subsampling/num_sfm_points_mask.py:7-64
@@ -125,6 +126,13 @@ int mdi_abi_version(void);
 int mdi_check_device(int device);
 /* sizeof(MdiView), so that the host-side struct packing can be asserted */
 int mdi_sizeof_view(void);
+
+/*
+ * a1: fills P, Kinv and c2w of every descriptor on the device.  K float32 [V,9], c2w float32
+ * [V,16] (row-major 4x4), Kinv float32 [V,9]; P_out float32 [V,12] or NULL.
+ */
+int mdi_setup_cameras(MdiView* views, int n_views, const float* K, const float* c2w,
+                      const float* Kinv, float* P_out, void* stream);
 
 /*
  * a2: project the SfM points of every view, filter, compact in order.
