@@ -84,7 +84,7 @@ def make_scene(n_views: int, H: int, W: int, n_sfm: int = 5000, seed: int = 2026
         image[v] = torch.randint(0, 256, (H, W, 3), generator=g, device=dev, dtype=torch.uint8)
         image[v, 0, 0, 0] = 255  # the reference asserts image.max() > 1
         # SfM points: half uniform, half in 8 blobs
-        n_own = n_sfm if v % max(low_conf_every, 1) != max(low_conf_every, 1) - 1 else n_sfm // 5
+        n_own = n_sfm if v % max(low_conf_every, 1) != max(low_conf_every, 1) - 1 else n_sfm // 8
         n_uni = n_own // 2
         px = rng.uniform(0, W - 1, n_uni)
         py = rng.uniform(0, H - 1, n_uni)
@@ -103,6 +103,11 @@ def make_scene(n_views: int, H: int, W: int, n_sfm: int = 5000, seed: int = 2026
         z = np.where(out, z * rng.uniform(1.3, 2.0, n_own), z)
         cam = np.linalg.inv(K) @ np.stack([px * z, py * z, z])
         world = (c2w[:3, :3] @ cam + c2w[:3, 3:4]).T
+        if n_own < n_sfm:  # low-confidence view: the rest of its points lie behind the camera
+            n_beh = n_sfm - n_own
+            cam_b = np.stack([rng.uniform(-1, 1, n_beh), rng.uniform(-1, 1, n_beh), -rng.uniform(1, 5, n_beh)])
+            world = np.concatenate([world, (c2w[:3, :3] @ cam_b + c2w[:3, 3:4]).T], 0)
+            n_own = n_sfm
         pts_all.append(world.astype(np.float32))
         own_idx = np.arange(n_pts, n_pts + n_own)
         n_pts += n_own
@@ -112,11 +117,11 @@ def make_scene(n_views: int, H: int, W: int, n_sfm: int = 5000, seed: int = 2026
         names.append(f"view_{v:05d}")
         true_h.append((s_true, t_true))
     points = np.concatenate(pts_all, 0) if pts_all else np.zeros((0, 3), np.float32)
-    # foreign points: 20 % extra indices from other views (80 % of M for low-confidence views)
+    # foreign points: 20 % extra indices drawn from all views' points
     point_indices = {}
     for v in range(n_views):
         own = idx_all[v]
-        n_for = n_sfm - len(own) if len(own) < n_sfm else n_sfm // 5
+        n_for = n_sfm // 5
         foreign = rng.integers(0, max(n_pts, 1), n_for)
         idx = np.concatenate([own, foreign])
         point_indices[names[v]] = idx[rng.permutation(len(idx))].astype(np.int64)

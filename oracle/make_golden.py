@@ -1,0 +1,188 @@
+"""TEST INFRASTRUCTURE.  Generates tests/golden/*.npz by running the UNMODIFIED reference
+(/root/reference, imported through oracle/ref_import.py) on CPU over seeded synthetic views.
+Run in the build container:  python oracle/make_golden.py
+The GPU box has no /root/reference; tests there compare against these committed fixtures.
+"""
+from __future__ import annotations
+
+import contextlib
+import importlib
+import io
+import json
+import re
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "oracle"))
+import ref_import  # noqa: E402
+
+GOLDEN = ROOT / "tests" / "golden"
+S = importlib.import_module("3dgs_monocular_depth_init_b200.synthetic")
+
+
+class _Parser:
+    def __init__(self, scene):
+        self.points = scene.points
+        self.point_indices = scene.point_indices
+
+
+def run_reference_view(R, scene, i, aligner, subsample, seed, grad=None, use_patch=True,
+                       fmin=5, fmax=15, n_small=20, thr=15):
+    cfg = R.Config()
+    cfg.mdi.alignment.aligner = R.DepthAlignmentStrategyEnum(aligner)
+    cfg.mdi.subsample_factor = subsample
+    cfg.mdi.depth_grad_mask_thresh = grad
+    cfg.mdi.use_num_sfm_points_mask = use_patch
+    cfg.mdi.adaptive_subsampling.factor_range_min = fmin
+    cfg.mdi.adaptive_subsampling.factor_range_max = fmax
+    cfg.mdi.num_sfm_points_mask.num_patches_small_axis = n_small
+    cfg.mdi.num_sfm_points_mask.threshold = thr
+    img01 = scene.image[i].float() / 255.0
+    depth, mask = scene.depth[i], scene.mask[i]
+    pred = R.PredictedDepth(depth.clone(), mask.clone())
+    image = R.InputImage(data=img01, name=scene.names[i], cam2world=scene.c2w[i], K=scene.K[i])
+    out = {"raised": 0}
+    torch.manual_seed(seed)
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            pts, keep, P = R.points_from_depth.get_pts_from_depth(pred, image, _Parser(scene), cfg, "cpu")
+    except R.LowDepthAlignmentConfidenceError:
+        out["raised"] = 1
+        return out
+    log = buf.getvalue()
+    out.update(pts=pts.numpy(), keep=np.packbits(keep.numpy()), P=P.numpy(),
+               rgb=img01.view(-1, 3)[keep].numpy())
+    # intermediate values, from the reference's own functions
+    sfm = torch.from_numpy(scene.points[scene.point_indices[scene.names[i]]]).float()
+    with contextlib.redirect_stdout(io.StringIO()):
+        uv, z = R.points_from_depth.project_and_filter_sfm_pts(img01, sfm, P, depth.T.shape, pred, None)
+    out.update(uv=uv.numpy(), z=z.numpy())
+    d = depth[uv[1], uv[0]].flatten()
+    if aligner == "lstsqrs":
+        s, t = R.lstsqrs.align_depth_least_squares(torch.vstack([d, torch.ones_like(d)]), z)
+        out.update(scale=np.float32(s), shift=np.float32(t))
+    else:
+        m = re.search(r"Iterations: (\d+), Inliers: (\d+)/(\d+), best scale: ([-\w.+]+), best shift: ([-\w.+]+)", log)
+        out.update(ransac_iters=int(m.group(1)), ransac_inliers=int(m.group(2)), ransac_n=int(m.group(3)))
+        # exact float32 scale / shift: rerun the aligner alone with the same RNG state
+        torch.manual_seed(seed)
+        with contextlib.redirect_stdout(io.StringIO()):
+            res = cfg.mdi.alignment.aligner.get_implementation().align(pred, uv, z, cfg, None)
+        # aligned = depth*s + t: recover (s, t) from the reference's own loop by replay
+        torch.manual_seed(seed)
+        with contextlib.redirect_stdout(buf):
+            # replay the loop through the reference helper functions to extract h exactly
+            h = _replay_reference_ransac(R, d, z, cfg.mdi.alignment.ransac, aligner)
+        assert torch.equal(res.aligned_depth, depth * h[0] + h[1])
+        out.update(scale=np.float32(h[0]), shift=np.float32(h[1]))
+    if subsample == "adaptive":
+        aligned = depth * float(out["scale"]) + float(out["shift"])
+        aligned = depth * torch.tensor(out["scale"]) + torch.tensor(out["shift"])
+        msk = (aligned != -42.0) & mask
+        vals = aligned[msk]
+        b = R.adaptive_subsampling.iqr_outlier_bounds(vals)
+        out.update(lo=np.float32(max(vals.min(), b[0])), hi=np.float32(min(vals.max(), b[1])),
+                   q1=np.float32(torch.quantile(vals, 0.25)), q3=np.float32(torch.quantile(vals, 0.75)))
+    return out
+
+
+def _replay_reference_ransac(R, d, g, p, aligner):
+    """Drives the reference's own helpers (align_depth_least_squares, _l2_dists_squared,
+    _ransac_loss/_msac_loss, _required_samples) in the loop order of ransacs.py:130-162 to
+    expose h_best (the reference function only returns the aligned map)."""
+    rs = R.ransacs
+    loss_func = rs._ransac_loss if aligner == "ransac" else rs._msac_loss
+    D = torch.vstack([d.reshape(-1), torch.ones(d.shape[0])])
+    h_best, n_best, l_best_lo, l_best_s = None, 0, float("inf"), float("inf")
+    for it in range(p.max_iters):
+        idx = torch.randperm(d.shape[0])[: p.sample_size]
+        h = rs.align_depth_least_squares(D[:, idx], g[idx])
+        r = rs._l2_dists_squared(h, D[0], g)
+        inl = r < p.inlier_threshold
+        ls = loss_func(r, p.inlier_threshold)
+        if ls < l_best_s:
+            h_lo = rs.align_depth_least_squares(D[:, inl], g[inl])
+            r_lo = rs._l2_dists_squared(h_lo, D[0], g)
+            l_lo = loss_func(r_lo, p.inlier_threshold)
+            if l_lo < l_best_lo:
+                h_best, l_best_lo, l_best_s = h_lo, l_lo, ls
+                n_best = torch.sum(r_lo < p.inlier_threshold)
+        if rs._required_samples(n_best, d.shape[0], p.sample_size, p.confidence) <= it and h_best is not None and it >= p.min_iters:
+            break
+    return h_best
+
+
+def save_case(name, scene, i, meta, out, store_inputs):
+    arrs = {k: np.asarray(v) for k, v in out.items()}
+    arrs["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+    if store_inputs:
+        arrs.update(in_depth=scene.depth[i].numpy(), in_mask=scene.mask[i].numpy(),
+                    in_image=scene.image[i].numpy(), in_K=scene.K[i].numpy(), in_c2w=scene.c2w[i].numpy(),
+                    in_sfm=scene.points[scene.point_indices[scene.names[i]]])
+    else:  # inputs are regenerated from the seed; a checksum guards against generator drift
+        arrs["in_checksum"] = np.array([float(scene.depth[i].double().sum()), float(scene.mask[i].sum()),
+                                        float(scene.image[i].double().sum()), float(scene.points.astype(np.float64).sum())])
+    np.savez_compressed(GOLDEN / f"{name}.npz", **arrs)
+    print(name, {k: (v.shape if hasattr(v, "shape") and v.ndim else v) for k, v in arrs.items() if not k.startswith("in_") and k != "meta"})
+
+
+def main():
+    R = ref_import.load()
+    GOLDEN.mkdir(parents=True, exist_ok=True)
+    small = dict(n_views=4, H=120, W=160, n_sfm=2500, seed=11, low_conf_every=4)
+    sc = S.make_scene(**small)
+    tall = dict(n_views=2, H=151, W=97, n_sfm=1500, seed=12, low_conf_every=50)
+    st = S.make_scene(**tall)
+    cases = [
+        ("small_lstsq_static4", sc, small, 0, dict(aligner="lstsqrs", subsample=4, seed=1)),
+        ("small_ransac_adaptive", sc, small, 1, dict(aligner="ransac", subsample="adaptive", seed=2)),
+        ("small_msac_static3_grad", sc, small, 2, dict(aligner="msac", subsample=3, seed=3, grad=0.05)),
+        ("small_lowconf", sc, small, 3, dict(aligner="lstsqrs", subsample=4, seed=4)),
+        ("small_ransac_nopatch", sc, small, 0, dict(aligner="ransac", subsample=7, seed=5, use_patch=False)),
+        ("small_adaptive_range_3_9", sc, small, 2, dict(aligner="lstsqrs", subsample="adaptive", seed=6, fmin=3, fmax=9, thr=5)),
+        ("tall_lstsq_adaptive", st, tall, 0, dict(aligner="lstsqrs", subsample="adaptive", seed=7, n_small=10)),
+        ("tall_msac_static5", st, tall, 1, dict(aligner="msac", subsample=5, seed=8, n_small=10, thr=8)),
+    ]
+    for name, scene, gen, i, kw in cases:
+        out = run_reference_view(R, scene, i, **kw)
+        save_case(name, scene, i, dict(gen=gen, view=i, **kw), out, store_inputs=True)
+    # full-size views of BASELINE configs C1 / C2 (inputs regenerated from the seed)
+    full = dict(n_views=2, H=840, W=1297, n_sfm=5000, seed=20261104, low_conf_every=50)
+    sf = S.make_scene(**full)
+    for name, i, kw in [("c1_lstsq_static10", 0, dict(aligner="lstsqrs", subsample=10, seed=21)),
+                        ("c2_ransac_adaptive", 1, dict(aligner="ransac", subsample="adaptive", seed=22))]:
+        out = run_reference_view(R, sf, i, **kw)
+        save_case(name, sf, i, dict(gen=full, view=i, **kw), out, store_inputs=False)
+    # known answers of the scalar helpers, computed by the reference functions
+    rs, ad, nm = R.ransacs, R.adaptive_subsampling, R.num_sfm_points_mask
+    ka = {}
+    ka["required_samples"] = [[n, tot, float(rs._required_samples(torch.tensor(n), tot, 4, 0.999))]
+                              for n, tot in [(4500, 5000), (0, 5000), (5000, 5000), (1, 5000), (3359, 5828), (17, 23), (2500, 5000), (4999, 5000)]]
+    ka["patch_sizes"] = [[h, w, n, *map(int, np.ravel(nm.calculate_patch_sizes((h, w), n)))]
+                         for h, w, n in [(840, 1297, 20), (1080, 1920, 20), (2160, 3840, 20), (1200, 1600, 20), (120, 160, 20), (151, 97, 10), (500, 500, 20), (1297, 840, 20)]]
+    deg = []
+    for dvals, gvals in [([2, 2, 2, 2], [3, 3.1, 2.9, 3]), ([1, 2, 3, 4], [2.1, 3.9, 6.2, 7.8]), ([0, 0, 0, 0], [1, 2, 3, 4]),
+                         ([1.5, 1.5000001, 1.5, 1.4999999], [3, 3, 3, 3]), ([5], [7]), ([1e-3, 2e-3], [1, 2])]:
+        d = torch.tensor(dvals, dtype=torch.float32)
+        g = torch.tensor(gvals, dtype=torch.float32)
+        h = R.lstsqrs.align_depth_least_squares(torch.vstack([d, torch.ones_like(d)]), g)
+        deg.append([dvals, gvals, float(h[0]), float(h[1])])
+    ka["lstsq"] = deg
+    qs = []
+    gq = torch.Generator().manual_seed(3)
+    for n in [1, 2, 5, 6, 101, 1000, 65537]:
+        x = torch.randn(n, generator=gq)
+        qs.append([n, x.numpy().tolist() if n <= 6 else int(n), float(torch.quantile(x, 0.25)), float(torch.quantile(x, 0.75))])
+    ka["quantile_seed3"] = qs
+    (GOLDEN / "known_answers.json").write_text(json.dumps(ka, indent=1))
+    print("known_answers.json written")
+
+
+if __name__ == "__main__":
+    main()
