@@ -1,0 +1,117 @@
+"""Scene-level entry point on the B200 (reference: gs_init_compare/monocular_depth_init.py:95-224).
+
+All views of the scene go through ONE batched kernel sequence (engine.Engine.run); views that the
+reference would skip with LowDepthAlignmentConfidenceError contribute no points and no K/P/size
+rows.  Depth predictors are out of scope: depth comes from `predict_fn(image, data) ->
+PredictedDepth` (cached depth, a predictor, or synthetic depth)."""
+from __future__ import annotations
+
+import logging
+from typing import Callable, List, Optional
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from ._single import options_from_config, ransac_seed
+from .engine import ViewInputs, get_engine
+from .point_cloud_postprocess.postprocess import postprocess_point_cloud
+from .types import InputImage
+
+_LOGGER = logging.getLogger(__name__)
+DEPTH_SOURCE: Optional[Callable] = None  # set by the caller: (InputImage, data dict, device) -> PredictedDepth
+
+
+def add_noise_to_point_cloud(pts: torch.Tensor, noise_std: float):
+    """monocular_depth_init.py:90-92."""
+    return pts + torch.randn_like(pts) * noise_std
+
+
+def gather_scene(parser, device, depth_source: Callable):
+    """Loads the train split into per-view lists (monocular_depth_init.py:110-139)."""
+    dataset = type(parser).DatasetCls(parser, split="train")
+    depths, masks, images, Ks, c2ws, names = [], [], [], [], [], []
+    for data in dataset:
+        assert data["image"].max() > 1  # image must be 0..255 (monocular_depth_init.py:122)
+        image = InputImage(name=data["image_name"], cam2world=data["camtoworld"], K=data["K"], data=data["image"])
+        pred = depth_source(image, data, device)
+        assert pred.depth.device == torch.device(device) or str(pred.depth.device).startswith(str(device))
+        depths.append(pred.depth.float().contiguous())
+        masks.append(pred.mask.contiguous())
+        images.append(data["image"])
+        Ks.append(data["K"]); c2ws.append(data["camtoworld"]); names.append(data["image_name"])
+    return depths, masks, images, torch.stack(Ks), torch.stack(c2ws), names
+
+
+@torch.no_grad()
+def points_from_views(config, depths, masks, images, K, c2w, names, points: np.ndarray, point_indices: dict,
+                      device, image_kind: int = L.IMAGE_F32_255, sample_idx: Optional[torch.Tensor] = None):
+    """The batched hot path.  images: per-view [H,W,3] tensors (float32 0..255 or uint8), on the
+    device or in pinned host memory.  Returns the engine RunResult (xyz / rgb on the device)."""
+    eng = get_engine(device)
+    dev = eng.device
+    counts = np.array([len(point_indices[n]) for n in names], dtype=np.int64)
+    padded = (counts + 3) & ~3
+    idx = np.zeros(int(padded.sum()) + 4, dtype=np.int32)
+    o = 0
+    for n, c, p in zip(names, counts, padded):
+        idx[o:o + c] = point_indices[n]
+        o += p
+    sfm_xyz = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float32)).to(dev)
+    sfm_index = torch.from_numpy(idx).to(dev)
+    opt = options_from_config(config)
+    if opt.aligner in ("ransac", "msac"):
+        if sample_idx is not None:
+            opt.sample_idx = sample_idx.to(device=dev, dtype=torch.int32).contiguous()
+        else:
+            opt.ransac_seed = ransac_seed()
+    vin = ViewInputs(depth=depths, mask=masks, image=images, image_kind=image_kind, K=K, c2w=c2w,
+                     sfm_xyz=sfm_xyz, sfm_index=sfm_index, sfm_counts=counts)
+    return eng.run(vin, opt)
+
+
+@torch.no_grad()
+def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth_source: Optional[Callable] = None):
+    """-> (pts float32 [N,3] on device, rgbs float32 [N,3] on CPU, scales [N,3] | None);
+    monocular_depth_init.py:95-224."""
+    depth_source = depth_source or DEPTH_SOURCE
+    if depth_source is None:
+        raise ValueError("no depth source: the depth predictors are outside the B200 path; pass "
+                         "depth_source=(image, data, device) -> PredictedDepth or set DEPTH_SOURCE")
+    eng = get_engine(device)
+    dev = eng.device
+    depths, masks, images, K, c2w, names = gather_scene(parser, dev, depth_source)
+    # images stay where the dataset put them (CPU in the reference): pin so the gather kernel
+    # reads only the kept pixels over PCIe instead of copying 12 B/px
+    imgs = [im if im.is_cuda else im.contiguous().pin_memory() for im in images]
+    kind = L.IMAGE_U8 if imgs and imgs[0].dtype == torch.uint8 else L.IMAGE_F32_255
+    res = points_from_views(config, depths, masks, imgs, K, c2w, names, parser.points, parser.point_indices, dev, kind)
+    status = res.status.cpu().numpy()
+    counts = res.view_counts.cpu().numpy()
+    for i in np.nonzero(status & L.STATUS_LOW_CONFIDENCE)[0]:
+        _LOGGER.warning("Low depth alignment confidence for image %s", names[i])
+    if (status & L.STATUS_EMPTY_STATS).any():
+        raise RuntimeError("quantile() input tensor must be non-empty")
+    pts, rgbs = res.xyz, res.rgb
+    if config.mdi.noise_std_scene_frac is not None:
+        pts = add_noise_to_point_cloud(pts, parser.scene_scale * config.mdi.noise_std_scene_frac)
+    rgbs = rgbs.cpu()
+    ok = (status & L.STATUS_LOW_CONFIDENCE) == 0
+    Kn = K.cpu().numpy()
+    Pn = res.P.cpu().numpy()
+    intrinsic_matrices = [Kn[i] for i in range(len(names)) if ok[i]]
+    proj_matrices = [Pn[i] for i in range(len(names)) if ok[i]]
+    # deviation from the reference: image_sizes is compacted to the kept views
+    image_sizes = np.array([[images[i].shape[1], images[i].shape[0]] for i in range(len(names)) if ok[i]],
+                           dtype=np.int32).reshape(-1, 2)
+    if config.mdi.include_sfm_points:
+        pts = torch.cat([pts, torch.from_numpy(parser.points).float().to(dev)], dim=0)
+        rgbs = torch.cat([rgbs, torch.from_numpy(parser.points_rgb / 255.0).float()], dim=0)
+    _LOGGER.info("Num points before postprocess: %d", pts.shape[0])
+    pts, rgbs = postprocess_point_cloud(pts, rgbs, intrinsic_matrices, proj_matrices, image_sizes,
+                                        config.mdi.postprocess, dev)
+    _LOGGER.info("Num points after postprocess: %d", pts.shape[0])
+    scales = None
+    if config.mdi.limit_init_scale:
+        raise NotImplementedError("limit_init_scale (kNN scales) is the next row of SURVEY.md 8f")
+    return pts, rgbs, scales
