@@ -86,10 +86,10 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
     if (xyz) {
       const float px = fmul(fadd((float)col, 0.5f), z);
       const float py = fmul(fadd((float)row, 0.5f), z);
-      // inv(K) @ pc and cam2world @ [cam;1]: FMA chains over k like the reference's sgemm
-      const float cx = dot3_fma(Ki[0], Ki[1], Ki[2], px, py, z);
-      const float cy = dot3_fma(Ki[3], Ki[4], Ki[5], px, py, z);
-      const float cz = dot3_fma(Ki[6], Ki[7], Ki[8], px, py, z);
+      // inv(K) @ pc (dot-product kernel) and cam2world @ [cam;1] (FMA chain), see mdi_math.cuh
+      const float cx = dot3_kinv(Ki[0], Ki[1], Ki[2], px, py, z);
+      const float cy = dot3_kinv(Ki[3], Ki[4], Ki[5], px, py, z);
+      const float cz = dot3_kinv(Ki[6], Ki[7], Ki[8], px, py, z);
       xyz[3 * out + 0] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
       xyz[3 * out + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
       xyz[3 * out + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);

@@ -68,6 +68,15 @@ MDI_HD float dot3_fma(float a, float b, float c, float x, float y, float z) {
 #endif
 }
 
+// inv(K) @ pc of points_from_depth.py:303.  inv() returns a column-major matrix and the
+// right operand is a transposed view, which sends sgemm down a dot-product kernel: three
+// separately rounded products summed as (p0 + p2) + p1.  (Measured against torch-CPU/MKL: exact
+// for every N on one thread; with several threads MKL switches to an FMA kernel above
+// N ~ 2-3e4 columns -- a thread-count dependent choice this build does not chase.)
+MDI_HD float dot3_kinv(float a, float b, float c, float x, float y, float z) {
+  return fadd(fadd(fmul(a, x), fmul(c, z)), fmul(b, y));
+}
+
 // aligned = depth * scale + shift, two roundings (lstsqrs.py:52, ransacs.py:187)
 MDI_HD float align_depth(float d, float s, float t) { return fadd(fmul(d, s), t); }
 
