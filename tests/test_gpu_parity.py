@@ -1,0 +1,182 @@
+"""GPU parity tests proper: the CUDA path, called through the drop-in API / C ABI, against the
+golden vectors of the unmodified reference and against the oracle on the same seeded inputs.
+
+Bars (north_star): keep masks, counts, indices, SfM filter: bit-exact.  RANSAC: identical
+iteration count and inlier set for identical sample indices.  scale/shift and xyz/rgb: 1e-5
+relative (FP32) -- REL below; xyz is compared against the point norm (a coordinate near zero has
+no meaningful relative error)."""
+import numpy as np
+import pytest
+import torch
+
+import mdi_oracle as O
+from helpers import FULL_CASES, SMALL_CASES, OneViewParser, case_config, load_case, mod, oracle_kwargs
+
+pytestmark = pytest.mark.gpu
+REL = 1e-5
+DEV = "cuda:0"
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-30))) if a.size else 0.0
+
+
+def xyz_err(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    if not a.size:
+        return 0.0
+    return float(np.max(np.linalg.norm(a - b, axis=1) / np.maximum(np.linalg.norm(b, axis=1), 1e-30)))
+
+
+def run_case(c, with_samples=True):
+    pfd = mod("depth_prediction.points_from_depth")
+    dpi = mod("depth_prediction.predictors.depth_predictor_interface")
+    types = mod("types")
+    cfg = case_config(c)
+    pred = dpi.PredictedDepth(c.depth.to(DEV), c.mask.to(DEV))
+    image = types.InputImage(data=c.image.float() / 255.0, name=c.name, cam2world=c.c2w, K=c.K)
+    sample_idx = None
+    if with_samples and c.meta["aligner"] in ("ransac", "msac") and not c.raised:
+        sample_idx = torch.from_numpy(O.draw_sample_idx(int(c.ref_uv.shape[1]), 2500, 4, c.meta["seed"]))
+    return pfd.get_pts_from_depth(pred, image, OneViewParser(c), cfg, DEV, sample_idx=sample_idx, return_result=True)
+
+
+@pytest.mark.parametrize("name", SMALL_CASES + FULL_CASES)
+def test_view_matches_reference_golden(name):
+    c = load_case(name)
+    if c.raised:
+        exc = mod("depth_alignment.exceptions").LowDepthAlignmentConfidenceError
+        with pytest.raises(exc):
+            run_case(c)
+        return
+    pts, keep, P, res = run_case(c)
+    assert pts.is_cuda and not keep.is_cuda and keep.dtype == torch.bool and P.is_cuda
+    # a1 / a2: projection matrix, SfM filter: bit-exact
+    assert np.array_equal(P.cpu().numpy(), c.ref_P)
+    n = int(res.n_valid[0])
+    assert n == c.ref_uv.shape[1]
+    assert np.array_equal(res.uv[:, :n].cpu().numpy(), c.ref_uv)
+    assert np.array_equal(res.z[:n].cpu().numpy(), c.ref_z)
+    # a3 / a4: scale, shift within 1e-5 relative; RANSAC trace identical
+    ss = res.scale_shift[0].cpu().numpy()
+    assert rel_err(ss[0], c.ref_scale) <= REL and rel_err(ss[1], c.ref_shift) <= REL, (ss, c.ref_scale, c.ref_shift)
+    if c.meta["aligner"] in ("ransac", "msac"):
+        assert int(res.ransac_iters[0]) == int(c.ref_ransac_iters)
+        assert int(res.ransac_inliers[0]) == int(c.ref_ransac_inliers)
+    # a5-a10: keep mask bit-exact, count, order
+    assert np.array_equal(keep.numpy(), c.ref_keep), f"{int((keep.numpy() != c.ref_keep).sum())} mask bits differ"
+    assert pts.shape[0] == c.ref_pts.shape[0] == int(c.ref_keep.sum())
+    assert xyz_err(pts.cpu().numpy(), c.ref_pts) <= REL
+    if "ref_lo" in c.__dict__:
+        lh = res.lo_hi[0].cpu().numpy()
+        assert rel_err(lh[0], c.ref_lo) <= REL and rel_err(lh[1], c.ref_hi) <= REL
+
+
+@pytest.mark.parametrize("name", ["small_lstsq_static4", "small_adaptive_range_3_9", "c1_lstsq_static10"])
+def test_stagewise_bit_exact_given_reference_fit(name):
+    """L1 parity: with the reference's (scale, shift) fed in, xyz must be bit-identical too."""
+    c = load_case(name)
+    eng_m = mod("engine")
+    single = mod("_single")
+    L = mod("_lib")
+    cfg = case_config(c)
+    opt = single.options_from_config(cfg, aligner=None, want_rgb=True,
+                                     scale_shift=torch.tensor([[float(c.ref_scale), float(c.ref_shift)]], device=DEV))
+    sfm = c.sfm.to(DEV).float().contiguous()
+    vin = single.single_view_inputs(c.depth.to(DEV), c.mask.to(DEV), DEV, K=c.K, c2w=c.c2w,
+                                    image=(c.image.to(DEV)), image_kind=L.IMAGE_U8,
+                                    sfm_xyz=sfm, sfm_counts=[len(sfm)])
+    res = eng_m.get_engine(DEV).run(vin, opt)
+    assert np.array_equal(res.keep.bool().cpu().numpy(), c.ref_keep)
+    assert np.array_equal(res.xyz.cpu().numpy(), c.ref_pts)
+    assert np.array_equal(res.rgb.cpu().numpy(), c.ref_rgb)
+    if "ref_lo" in c.__dict__:
+        assert np.float32(res.lo_hi[0, 0].item()) == c.ref_lo and np.float32(res.lo_hi[0, 1].item()) == c.ref_hi
+        assert np.float32(res.quantiles[0, 0].item()) == c.ref_q1 and np.float32(res.quantiles[0, 1].item()) == c.ref_q3
+
+
+def test_batched_scene_equals_per_view_oracle():
+    """Four views (one skipped for low confidence, one with an invalid rectangle) in ONE batch:
+    view-major, row-major order; identical counts; rgb gather from uint8 and float images."""
+    syn = mod("synthetic")
+    mdi = mod("monocular_depth_init")
+    L = mod("_lib")
+    sc = syn.make_scene(n_views=4, H=120, W=160, n_sfm=2500, seed=11, low_conf_every=4)
+    cfg = mod("config").Config()
+    cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum("lstsqrs")
+    cfg.mdi.subsample_factor = "adaptive"
+    pts_o, rgb_o, traces, kept = O.scene_points(sc, aligner="lstsqrs", subsample="adaptive", include_sfm_points=False)
+    assert kept == [0, 1, 2]
+    for kind, imgs in [(L.IMAGE_U8, [im.to(DEV) for im in sc.image]),
+                       (L.IMAGE_F32_255, [im.float().pin_memory() for im in sc.image])]:
+        res = mdi.points_from_views(cfg, [d.to(DEV) for d in sc.depth], [m.to(DEV) for m in sc.mask], imgs,
+                                    sc.K, sc.c2w, sc.names, sc.points, sc.point_indices, DEV, kind)
+        torch.cuda.synchronize()
+        assert res.status.cpu().tolist() == [0, 0, 0, 1]
+        counts = res.view_counts.cpu().tolist()
+        assert counts == [int(t.keep.sum()) for t in traces[:3]] + [0]
+        keep = res.keep.bool().cpu().view(4, -1)
+        for i in range(3):
+            assert torch.equal(keep[i], traces[i].keep)
+        assert not keep[3].any()
+        assert xyz_err(res.xyz.cpu().numpy(), pts_o.numpy()) <= REL
+        assert np.array_equal(res.rgb.cpu().numpy(), rgb_o.numpy())
+
+
+def test_subsampler_and_mask_apis_vs_oracle():
+    c = load_case("tall_lstsq_adaptive")
+    aligned = (c.depth * torch.tensor(c.ref_scale) + torch.tensor(c.ref_shift))
+    a_dev, m_dev = aligned.to(DEV), c.mask.to(DEV)
+    rgb = torch.zeros(*c.depth.shape, 3)
+    st = mod("depth_subsampling.static_subsampler").StaticDepthSubsampler(7)
+    assert torch.equal(st.get_mask(rgb, a_dev, m_dev).cpu(), O.static_mask(c.mask, 7))
+    ad_cfg = mod("depth_subsampling.config").AdaptiveSubsamplingConfig(4, 11)
+    ad = mod("depth_subsampling.adaptive_subsampling").AdaptiveDepthSubsampler(ad_cfg)
+    assert torch.equal(ad.get_mask(rgb, a_dev, m_dev).cpu(), O.adaptive_mask(aligned, c.mask, 4, 11))
+    nm = mod("depth_subsampling.num_sfm_points_mask")
+    uv = torch.from_numpy(c.ref_uv)
+    for n_small, thr in [(10, 8), (20, 2), (5, 30)]:
+        pc = mod("depth_subsampling.config").NumSfMPointsMaskConfig(n_small, thr)
+        got = nm.num_sfm_points_mask(uv.to(DEV), tuple(c.depth.shape), pc)
+        assert torch.equal(got, O.sfm_density_mask_loop(uv, tuple(c.depth.shape), n_small, thr))
+    gm = mod("depth_prediction.points_from_depth").depth_gradient_mask(a_dev, 0.03)
+    assert torch.equal(gm.cpu(), O.gradient_mask(aligned, 0.03))
+
+
+def test_alignment_strategy_api():
+    c = load_case("small_lstsq_static4")
+    dpi = mod("depth_prediction.predictors.depth_predictor_interface")
+    pred = dpi.PredictedDepth(c.depth.to(DEV), c.mask.to(DEV))
+    uv, z = torch.from_numpy(c.ref_uv).to(DEV), torch.from_numpy(c.ref_z).to(DEV)
+    cfg = case_config(c)
+    r = mod("depth_alignment.pipeline").DepthAlignmentPipeline.from_config(cfg).align(None, pred, uv, z, cfg, None)
+    ref_aligned = c.depth * torch.tensor(c.ref_scale) + torch.tensor(c.ref_shift)
+    assert rel_err(r.aligned_depth.cpu().numpy(), ref_aligned.numpy()) <= 4 * REL
+    assert torch.equal(r.mask.cpu(), c.mask & (r.aligned_depth.cpu() != -42.0))
+    d = c.depth[c.ref_uv[1], c.ref_uv[0]].to(DEV)
+    s, t = mod("depth_alignment.alignment.lstsqrs").align_depth_least_squares(torch.vstack([d, torch.ones_like(d)]), z)
+    assert rel_err(float(s), c.ref_scale) <= REL and rel_err(float(t), c.ref_shift) <= REL
+    # rank-deficient sample: pinv's minimum-norm answer
+    d4 = torch.tensor([2.0, 2, 2, 2], device=DEV)
+    s, t = mod("depth_alignment.alignment.lstsqrs").align_depth_least_squares(
+        torch.vstack([d4, torch.ones_like(d4)]), torch.tensor([3.0, 3.1, 2.9, 3.0], device=DEV))
+    assert abs(float(s) - 1.2) < 1e-5 and abs(float(t) - 0.6) < 1e-5
+
+
+def test_ransac_device_sampler_recovers_truth():
+    """Throughput mode (device-generated samples): the fit must land on the generating
+    scale/shift of the synthetic views and be reproducible under torch.manual_seed."""
+    syn = mod("synthetic")
+    mdi = mod("monocular_depth_init")
+    L = mod("_lib")
+    sc = syn.make_scene(n_views=6, H=240, W=320, n_sfm=3000, seed=5, low_conf_every=50)
+    cfg = mod("config").Config()
+    outs = []
+    for _ in range(2):
+        torch.manual_seed(1234)
+        res = mdi.points_from_views(cfg, sc.depth.to(DEV), sc.mask.to(DEV), sc.image.to(DEV), sc.K, sc.c2w,
+                                    sc.names, sc.points, sc.point_indices, DEV, L.IMAGE_U8)
+        outs.append((res.scale_shift.cpu().numpy().copy(), res.xyz.cpu().numpy().copy()))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert np.allclose(outs[0][0], sc.true_scale_shift, rtol=0.02, atol=0.02)
