@@ -131,8 +131,9 @@ gather_fit_kernel(const MdiView* __restrict__ views, int64_t slots,
 }
 
 // a1.  P = (K @ R^T... precisely the reference's `K @ R @ hstack([eye(3), -C[:, None]])` with
-// R = c2w[:3,:3].T, C = c2w[:3,3] (points_from_depth.py:231-233), each matmul an FMA chain over
-// k like the CPU sgemm that evaluates it.  Also copies Kinv and the top 3 rows of c2w into the
+// R = c2w[:3,:3].T, C = c2w[:3,3] (points_from_depth.py:231-233): the first product (right
+// operand a transposed view) as separately rounded products, the second as an FMA chain over k,
+// which is how the CPU sgemm evaluates them (bit-identical on every golden view).  Also copies Kinv and the top 3 rows of c2w into the
 // descriptors.  One thread per view.
 __global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
                                      const float* __restrict__ K, const float* __restrict__ c2w,
@@ -141,24 +142,8 @@ __global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
   if (v >= n_views) return;
   const float* k = K + 9 * (int64_t)v;
   const float* m = c2w + 16 * (int64_t)v;
-  float T[3][3];
-  for (int i = 0; i < 3; ++i)
-    for (int j = 0; j < 3; ++j)  // R[kk][j] = c2w[j][kk]
-      T[i][j] = __fmaf_rn(k[3 * i + 2], m[4 * j + 2],
-                          __fmaf_rn(k[3 * i + 1], m[4 * j + 1], fmul(k[3 * i + 0], m[4 * j + 0])));
   float P[12];
-  for (int i = 0; i < 3; ++i) {
-    for (int j = 0; j < 3; ++j) {  // columns of the identity block: chain of T*1 and T*0 terms
-      float acc = fmul(T[i][0], j == 0 ? 1.f : 0.f);
-      acc = __fmaf_rn(T[i][1], j == 1 ? 1.f : 0.f, acc);
-      acc = __fmaf_rn(T[i][2], j == 2 ? 1.f : 0.f, acc);
-      P[4 * i + j] = acc;
-    }
-    float acc = fmul(T[i][0], -m[3]);
-    acc = __fmaf_rn(T[i][1], -m[7], acc);
-    acc = __fmaf_rn(T[i][2], -m[11], acc);
-    P[4 * i + 3] = acc;
-  }
+  projection_matrix(k, m, P);
   for (int q = 0; q < 12; ++q) {
     views[v].P[q] = P[q];
     views[v].c2w[q] = m[q];

@@ -77,6 +77,22 @@ MDI_HD float dot3_kinv(float a, float b, float c, float x, float y, float z) {
   return fadd(fadd(fmul(a, x), fmul(c, z)), fmul(b, y));
 }
 
+// P = K @ R @ [I | -C], R = c2w[:3,:3].T, C = c2w[:3,3] (points_from_depth.py:231-233).
+// K row-major 3x3, c2w row-major 4x4, P row-major 3x4.  K @ R has a transposed view on the
+// right: dot-product sgemm kernel (dot3_kinv); T @ [I | -C] is an FMA chain over k.
+MDI_HD void projection_matrix(const float* k, const float* m, float* P) {
+  float T[3][3];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j)  // R[kk][j] = c2w[j][kk]
+      T[i][j] = dot3_kinv(k[3 * i], k[3 * i + 1], k[3 * i + 2], m[4 * j], m[4 * j + 1], m[4 * j + 2]);
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j)
+      P[4 * i + j] = dot3_fma(T[i][0], T[i][1], T[i][2], j == 0 ? 1.f : 0.f, j == 1 ? 1.f : 0.f,
+                              j == 2 ? 1.f : 0.f);
+    P[4 * i + 3] = dot3_fma(T[i][0], T[i][1], T[i][2], -m[3], -m[7], -m[11]);
+  }
+}
+
 // aligned = depth * scale + shift, two roundings (lstsqrs.py:52, ransacs.py:187)
 MDI_HD float align_depth(float d, float s, float t) { return fadd(fmul(d, s), t); }
 

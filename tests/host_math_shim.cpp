@@ -37,5 +37,6 @@ void t_unproject(const float* Ki, const float* M, const float* z, const int* row
       out[3 * i + r] = mdi::dot4_fma(M[4 * r], M[4 * r + 1], M[4 * r + 2], M[4 * r + 3], cx, cy, cz);
   }
 }
+void t_camera(const float* K, const float* c2w, float* P) { mdi::projection_matrix(K, c2w, P); }
 float t_residual(float h0, float h1, float d, float g) { return mdi::residual_sq(h0, h1, d, g); }
 }

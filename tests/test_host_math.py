@@ -35,6 +35,7 @@ def shim():
     lib.t_keys.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
     lib.t_project.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
     lib.t_unproject.argtypes = [C.c_void_p] * 5 + [C.c_longlong, C.c_void_p]
+    lib.t_camera.argtypes = [C.c_void_p] * 3
     return lib
 
 
@@ -141,3 +142,25 @@ def test_projection_and_unprojection_bit_exact_vs_reference(shim):
     shim.t_unproject(Ki.ctypes.data, M.ctypes.data, np.ascontiguousarray(z).ctypes.data, row.ctypes.data,
                      col.ctypes.data, len(idx), o.ctypes.data)
     assert np.array_equal(o, c.ref_pts)
+
+
+def test_projection_matrix_bit_exact_on_every_golden_view(shim):
+    from helpers import FULL_CASES, SMALL_CASES
+    for name in SMALL_CASES + FULL_CASES:
+        c = load_case(name)
+        if c.raised:
+            continue
+        K = np.ascontiguousarray(c.K.numpy()); M = np.ascontiguousarray(c.c2w.numpy())
+        P = np.zeros((3, 4), np.float32)
+        shim.t_camera(K.ctypes.data, M.ctypes.data, P.ctypes.data)
+        assert np.array_equal(P, c.ref_P), name
+    # and on random poses against the oracle
+    g = torch.Generator().manual_seed(0)
+    for _ in range(200):
+        Q, _r = torch.linalg.qr(torch.randn(3, 3, generator=g))
+        c2w = torch.eye(4); c2w[:3, :3] = Q; c2w[:3, 3] = torch.randn(3, generator=g) * 5
+        f = float(torch.rand(1, generator=g)) * 2000 + 300
+        K = torch.tensor([[f, 0, 640.5], [0, f * 1.01, 360.25], [0, 0, 1]])
+        P = np.zeros((3, 4), np.float32)
+        shim.t_camera(np.ascontiguousarray(K.numpy()).ctypes.data, np.ascontiguousarray(c2w.numpy()).ctypes.data, P.ctypes.data)
+        assert np.array_equal(P, O.projection_matrix(K, c2w).numpy())
