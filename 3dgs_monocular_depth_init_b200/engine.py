@@ -108,6 +108,7 @@ class RunResult:
     view_counts: Optional[torch.Tensor] = None   # [V] int64 cuda
     view_offsets: Optional[torch.Tensor] = None  # [V] int64 cuda
     total: int = 0
+    extras: dict = field(default_factory=dict)
 
 
 def _stream() -> int:
@@ -135,6 +136,44 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
     return p, shapes
 
 
+# kernels launched by each C-ABI entry point (for the bench's `gpu_launches` claim)
+KERNELS_PER_CALL = {
+    "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
+    "mdi_apply_scale_shift": 1, "mdi_depth_range": 7, "mdi_grad_range": 3, "mdi_keep_mask": 1,
+    "mdi_scan_tiles": 1, "mdi_emit_points": 1, "mdi_min_extents": 1,
+}
+
+
+class _CountingLib:
+    """Proxy over the ctypes library: counts kernel launches and, when the engine's `profile`
+    flag is set, brackets every launching call with CUDA events on the current stream."""
+
+    def __init__(self, lib, engine):
+        self._lib, self._engine = lib, engine
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+        n = KERNELS_PER_CALL.get(name)
+        if n is None:
+            return fn
+        eng = self._engine
+
+        def call(*args):
+            if eng.profile:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e1 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+                rc = fn(*args)
+                e1.record()
+                eng.events.append((name, e0, e1))
+            else:
+                rc = fn(*args)
+            eng.launches += n
+            return rc
+
+        return call
+
+
 class Engine:
     """Holds cached workspaces per device.  One instance per process / GPU."""
 
@@ -142,12 +181,25 @@ class Engine:
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise L.MdiError("the B200 path runs on a CUDA device only (no CPU fallback)")
-        self.lib = L.load()
+        self.lib = _CountingLib(L.load(), self)
         idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
         self.device = torch.device("cuda", idx)
         L.check(self.lib.mdi_check_device(idx), "mdi_check_device")
         self._ws: dict[str, torch.Tensor] = {}
-        self.launches = 0  # kernels launched through this engine (bench `gpu_launches`)
+        self.launches = 0   # kernels launched through this engine (bench `gpu_launches`)
+        self.profile = False
+        self.events: list = []  # (entry point, start event, end event) when profile is on
+
+    def kernel_times_ms(self) -> dict:
+        """Sums the recorded per-call device times by entry point and clears the record
+        (call after a synchronize)."""
+        out: dict = {}
+        for name, e0, e1 in self.events:
+            t = out.setdefault(name, [0.0, 0])
+            t[0] += e0.elapsed_time(e1)
+            t[1] += 1
+        self.events = []
+        return {k: {"ms": v[0], "calls": v[1]} for k, v in out.items()}
 
     # cached, grow-only workspace buffers (never shrink: results that alias them are only
     # valid until the next run() unless the caller asked for owned outputs)
@@ -231,7 +283,6 @@ class Engine:
         kinvp = c2wp + 4 * 16 * V
         res.P = torch.empty((V, 3, 4), dtype=torch.float32, device=self.device)
         L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(), st), "mdi_setup_cameras")
-        self.launches += 1
         if vin.P_override is not None:  # stage-wise parity: feed the oracle's P
             res.P.copy_(vin.P_override.to(self.device, torch.float32))
             host_desc = desc.copy()
@@ -257,7 +308,6 @@ class Engine:
                                            res.uv.data_ptr(), res.z.data_ptr(), res.n_inbounds.data_ptr(),
                                            res.n_valid.data_ptr(), res.status.data_ptr(), st),
                     "mdi_project_filter")
-            self.launches += 1
         if opt.stop_after == "project":
             return res
 
@@ -276,7 +326,6 @@ class Engine:
                                        res.d.data_ptr(), res.sums.data_ptr(), L.ptr(res.scale_shift),
                                        1 if write_fit else 0, int(opt.patch_threshold),
                                        L.ptr(res.patch_blocked), st), "mdi_gather_fit")
-            self.launches += 1
         # a4: RANSAC / MSAC
         if opt.aligner in ("ransac", "msac"):
             assert have_pts, "RANSAC needs SfM points"
@@ -299,7 +348,6 @@ class Engine:
                                    res.scale_shift.data_ptr(), L.ptr(res.inlier_mask),
                                    res.ransac_iters.data_ptr(), res.ransac_inliers.data_ptr(), st),
                     "mdi_ransac")
-            self.launches += 1
         elif opt.aligner is None:
             res.scale_shift = opt.scale_shift
             if res.scale_shift is not None:
@@ -325,13 +373,11 @@ class Engine:
             L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
                                         flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL), ws.data_ptr(),
                                         res.lo_hi.data_ptr(), res.quantiles.data_ptr(), st), "mdi_depth_range")
-            self.launches += 8
         if opt.grad_thresh is not None:
             flags |= L.KEEP_GRAD
             res.grad_range = torch.empty((V, 2), dtype=f32, device=self.device)
             L.check(lib.mdi_grad_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
                                        res.grad_range.data_ptr(), st), "mdi_grad_range")
-            self.launches += 3
 
         # a5-a10: keep mask, then order-preserving compaction + unprojection + RGB gather
         scfg = L.SubsampleConfigC(L.SUBSAMPLE_ADAPTIVE if adaptive else L.SUBSAMPLE_STATIC,
@@ -351,7 +397,6 @@ class Engine:
         L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
                                    res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
                                    meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
-        self.launches += 2
         if opt.stop_after == "mask" or not (opt.want_xyz or opt.want_rgb):
             res.total = int(meta[2 * V].item())
             return res
@@ -367,7 +412,6 @@ class Engine:
             L.check(lib.mdi_emit_points(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
                                         int(vin.image_kind), L.ptr(res.xyz), L.ptr(res.rgb), st),
                     "mdi_emit_points")
-            self.launches += 1
         return res
 
 

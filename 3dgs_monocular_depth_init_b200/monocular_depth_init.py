@@ -115,3 +115,34 @@ def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth
     if config.mdi.limit_init_scale:
         raise NotImplementedError("limit_init_scale (kNN scales) is the next row of SURVEY.md 8f")
     return pts, rgbs, scales
+
+
+@torch.no_grad()
+def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, points, point_indices, device,
+                           image_kind: int = L.IMAGE_U8, sample_idx: Optional[torch.Tensor] = None):
+    """End-to-end form of the hot path for HOST inputs (what a dataset loader hands over):
+    depth [V,H,W] float32 and mask [V,H,W] bool in pinned host memory are copied to the device,
+    the image [V,H,W,3] stays in pinned host memory and only its kept pixels are read over PCIe by
+    the gather kernel; rgb comes back to the host (the reference returns rgbs on the CPU,
+    monocular_depth_init.py:168), xyz stays on the device.
+    Returns (RunResult, rgb_host, h2d_bytes, d2h_bytes)."""
+    eng = get_engine(device)
+    dev = eng.device
+    assert depth_h.is_pinned() and mask_h.is_pinned() and image_h.is_pinned()
+    depth_d = eng._buf("e2e_depth", depth_h.numel(), torch.float32).view(depth_h.shape)
+    mask_d = eng._buf("e2e_mask", mask_h.numel(), torch.uint8).view(mask_h.shape)
+    depth_d.copy_(depth_h, non_blocking=True)
+    mask_d.copy_(mask_h.view(torch.uint8), non_blocking=True)
+    res = points_from_views(config, depth_d, mask_d, image_h, K, c2w, names, points, point_indices, dev,
+                            image_kind, sample_idx)
+    rgb_h = torch.empty(res.rgb.shape, dtype=torch.float32, pin_memory=True)
+    rgb_h.copy_(res.rgb, non_blocking=True)
+    counts_h = torch.empty(res.view_counts.shape, dtype=torch.int64, pin_memory=True)
+    counts_h.copy_(res.view_counts, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    n_sfm = sum(len(point_indices[n]) for n in names)
+    h2d = depth_h.numel() * 4 + mask_h.numel() + res.total * 3 * image_h.element_size() \
+        + points.shape[0] * 12 + n_sfm * 4 + len(names) * (L.VIEW_DTYPE.itemsize + 34 * 4)
+    d2h = res.total * 12 + counts_h.numel() * 8 + 8
+    res.extras = {"counts_host": counts_h}
+    return res, rgb_h, int(h2d), int(d2h)

@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py -- monocular-depth init hot path (align + subsample + unproject) on N B200s.
+
+A "step" is one pass of the hot path over one batch of synthetic views (BASELINE.json config 2:
+Mip-NeRF-360-shaped, 200 views of 1297x840, 5000 SfM points per view + 20 % foreign, RANSAC
+alignment + adaptive subsampling + default SfM-density patch mask).  N > 1 is weak scaling:
+every rank owns its own 200 views (no data-path collective) and the per-view point clouds are
+concatenated in view order by one NCCL all-gather per step.
+
+  python bench.py [--gpus N --steps K --warmup W]            our arm (CUDA kernels)
+  python bench.py --impl reference [...]                     the reference's CPU path (oracle port)
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+PKG = "3dgs_monocular_depth_init_b200"
+
+WORKLOADS = {
+    # name: (views per GPU, H, W, sfm points per view, aligner, subsample)
+    "c2_mipnerf360_200x1297x840_ransac_adaptive": (200, 840, 1297, 5000, "ransac", "adaptive"),
+    "c1_single_1297x840_lstsq_stride10": (1, 840, 1297, 5000, "lstsqrs", 10),
+    "c3_tanks_300x1920x1080_ransac_adaptive": (300, 1080, 1920, 5000, "ransac", "adaptive"),
+    "c4_4k_500x3840x2160_ransac_adaptive": (500, 2160, 3840, 5000, "ransac", "adaptive"),
+}
+DEFAULT_WORKLOAD = "c2_mipnerf360_200x1297x840_ransac_adaptive"
+
+
+def mod(name=""):
+    return importlib.import_module(PKG + ("." + name if name else ""))
+
+
+def make_config(aligner, subsample):
+    cfg = mod("config").Config()
+    cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum(aligner)
+    cfg.mdi.subsample_factor = subsample
+    return cfg
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(call: str, HW: int, V: int, n_kept: int, n_sfm_slots: int, adaptive: bool) -> float:
+    """Algorithmic bytes of one launch group, per SURVEY.md 8(d): per view
+    B = P*HW*5 + HW + 36*Nk + 16*M, split over the entry points that move them."""
+    return {
+        "mdi_depth_range": V * HW * 5.0,              # the one statistics read of depth + mask
+        "mdi_keep_mask": V * HW * 6.0,                # depth + mask read, keep mask written
+        "mdi_emit_points": 36.0 * n_kept,             # rgb read, xyz + rgb written
+        "mdi_project_filter": 16.0 * n_sfm_slots,     # sfm xyz + index
+    }.get(call, 0.0)
+
+
+def cpu_reference_run(workload: str, n_views_sample: int, seed: int = 20261104):
+    """The reference's CPU path (oracle port: same torch ops, same python loops, including the
+    per-patch loop of num_sfm_points_mask) on a bounded sample of the workload's views."""
+    import torch
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import mdi_oracle as O
+
+    V, H, W, n_sfm, aligner, subsample = WORKLOADS[workload]
+    n = min(V, n_views_sample)
+    torch.set_num_threads(os.cpu_count() or 1)
+    sc = mod("synthetic").make_scene(n_views=n, H=H, W=W, n_sfm=n_sfm, seed=seed, device="cpu", low_conf_every=50)
+    O.scene_points(sc, aligner=aligner, subsample=subsample, include_sfm_points=False, views=[0],
+                   seed=1, slow_patch_loop=True)  # warm-up (thread pools, allocator)
+    t0 = time.perf_counter()
+    pts, rgbs, traces, kept = O.scene_points(sc, aligner=aligner, subsample=subsample, include_sfm_points=False,
+                                             seed=1, slow_patch_loop=True)
+    dt = time.perf_counter() - t0
+    return n, dt, int(pts.shape[0]), torch.get_num_threads()
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    V, H, W, n_sfm, aligner, subsample = WORKLOADS[args.workload]
+    times, kept_pts, nv, cores = [], 0, 0, 1
+    for i in range(args.warmup + args.steps):
+        nv, dt, kept_pts, cores = cpu_reference_run(args.workload, args.cpu_views, seed=20261104 + i)
+        if i >= args.warmup:
+            times.append(dt)
+    t = sum(times) / max(len(times), 1)
+    vps = nv / t
+    sample = f"{nv} of {V} views of {args.workload} per step (views are independent; views/s is per view)"
+    print(json.dumps({
+        "impl": "reference", "metric": "init views/sec (align+subsample+unproject)", "value": vps, "unit": "views/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "views_per_step": nv, "H": H, "W": W, "sfm_points_per_view": n_sfm,
+                   "aligner": aligner, "subsample": subsample},
+        "mpts_per_s": kept_pts / t / 1e6,
+        "cpu_baseline": {"value": vps, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": vps, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = mod("_lib")
+    mdi = mod("monocular_depth_init")
+    eng = mod("engine").get_engine(dev)
+    dmod = mod("distributed")
+
+    V, H, W, n_sfm, aligner, subsample = WORKLOADS[args.workload]
+    cfg = make_config(aligner, subsample)
+    sc = mod("synthetic").make_scene(n_views=V, H=H, W=W, n_sfm=n_sfm, seed=20261104 + 7919 * rank,
+                                     device=str(dev), low_conf_every=50)
+    depth, mask, image = sc.depth, sc.mask, sc.image   # resident in HBM before the timed region
+    HW = H * W
+    input_bytes = depth.numel() * 4 + mask.numel() + image.numel()
+
+    def step():
+        torch.manual_seed(1234)
+        res = mdi.points_from_views(cfg, depth, mask, image, sc.K, sc.c2w, sc.names, sc.points,
+                                    sc.point_indices, dev, L.IMAGE_U8)
+        if world > 1:
+            xyz, rgb, _ = dmod.allgather_points(res.xyz, res.rgb)
+        return res
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        res = step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    eng.profile = True
+    eng.events = []
+    launches0 = eng.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        res = step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms)
+    eng.profile = False
+    ktimes = eng.kernel_times_ms()
+    launches = eng.launches - launches0
+    n_kept = int(res.total)
+    n_ok = int((res.status == 0).sum())
+
+    # ---- end to end: host buffers in, rgb out, through the public API --------------------------
+    depth_h = depth.cpu().pin_memory(); mask_h = mask.cpu().pin_memory(); image_h = image.cpu().pin_memory()
+    h2d = d2h = 0
+    for _ in range(2):
+        mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names, sc.points,
+                                   sc.point_indices, dev, L.IMAGE_U8)
+    barrier()
+    t0 = time.perf_counter()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        torch.manual_seed(1234)
+        r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names,
+                                                         sc.points, sc.point_indices, dev, L.IMAGE_U8)
+        if world > 1:
+            dmod.allgather_points(r2.xyz, r2.rgb)
+    f1.record()
+    barrier()
+    e2e_ms = torch.tensor([max(f0.elapsed_time(f1), 1e3 * (time.perf_counter() - t0))], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    clk = clocks.stop() if rank == 0 else None
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    ms_step = ms_total / args.steps
+    views_per_s = world * V / (ms_step * 1e-3)
+    e2e_views_per_s = world * V / (float(e2e_ms) / e2e_steps * 1e-3)
+    # ---- roofline of the dominant launch group ---------------------------------------------------
+    peaks_path = ROOT / "MEASURED_PEAKS.json"
+    if peaks_path.exists():
+        peak, peak_src = float(json.loads(peaks_path.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    n_slots = sum(len(sc.point_indices[n]) for n in sc.names)
+    hbm_calls = {k: v for k, v in ktimes.items() if algorithmic_bytes(k, HW, V, n_kept, n_slots, subsample == "adaptive") > 0}
+    dom = max(hbm_calls, key=lambda k: hbm_calls[k]["ms"]) if hbm_calls else None
+    roof = None
+    breakdown = {}
+    for k, v in ktimes.items():
+        per = v["ms"] / v["calls"]
+        b = algorithmic_bytes(k, HW, V, n_kept, n_slots, subsample == "adaptive")
+        breakdown[k] = {"ms_per_call": round(per, 4), "share": round(v["ms"] / ms_total, 4),
+                        "algorithmic_GBps": round(b / (per * 1e-3) / 1e9, 1) if b else None}
+    if dom:
+        per = ktimes[dom]["ms"] / ktimes[dom]["calls"]
+        ach = algorithmic_bytes(dom, HW, V, n_kept, n_slots, subsample == "adaptive") / (per * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src}
+    # whole-step algorithmic bytes: P*HW*5 + HW + 36*Nk + 16*M per view
+    P = 2 if subsample == "adaptive" else 1
+    step_bytes = V * (P * HW * 5 + HW) + 36 * n_kept + 16 * n_slots
+    nv, dt, kept_cpu, cores = cpu_reference_run(args.workload, args.cpu_views)
+    out = {
+        "metric": "init views/sec (align+subsample+unproject)", "value": views_per_s, "unit": "views/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "views_per_gpu": V, "H": H, "W": W, "sfm_points_per_view": n_sfm,
+                   "aligner": aligner, "subsample": subsample, "patch_mask": True,
+                   "l2": f"inputs {input_bytes / 1e6:.0f} MB per step > 126 MB L2, no flush needed",
+                   "views_ok": n_ok, "kept_points_per_gpu": n_kept},
+        "mpts_per_s": world * n_kept / (ms_step * 1e-3) / 1e6,
+        "step_algorithmic_GBps": step_bytes / (ms_step * 1e-3) / 1e9,
+        "step_frac_of_peak": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
+        "roofline": roof, "kernels": breakdown,
+        "cpu_baseline": {"value": nv / dt, "unit": "views/s", "cores": cores, "kind": "port",
+                         "sample": f"{nv} of {V} views of the same workload, oracle port of the reference loop on the host"},
+        "e2e": {"value": e2e_views_per_s, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps},
+        "gpu_launches": launches, "clocks": clk,
+    }
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--cpu-views", type=int, default=12, help="views in the bounded CPU sample")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
