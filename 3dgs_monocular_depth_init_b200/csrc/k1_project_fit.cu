@@ -149,7 +149,16 @@ __global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
     views[v].c2w[q] = m[q];
     if (P_out) P_out[12 * (int64_t)v + q] = P[q];
   }
-  for (int q = 0; q < 9; ++q) views[v].Kinv[q] = Kinv[9 * (int64_t)v + q];
+  if (Kinv) {
+    for (int q = 0; q < 9; ++q) views[v].Kinv[q] = Kinv[9 * (int64_t)v + q];
+  } else {
+    // zero-skew pinhole K: torch.linalg.inv (LU + back substitution) is exactly
+    // [[1/fx, 0, -cx/fx], [0, 1/fy, -cy/fy], [0, 0, 1]] with true divisions (pinned on the CPU
+    // against torch for 5000 random intrinsics, tests/test_host_math.py)
+    float ki[9];
+    pinhole_inverse(k, ki);
+    for (int q = 0; q < 9; ++q) views[v].Kinv[q] = ki[q];
+  }
 }
 
 __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_t n,
@@ -167,7 +176,7 @@ extern "C" int mdi_setup_cameras(MdiView* views, int n_views, const float* K, co
                                  const float* Kinv, float* P_out, void* stream) {
   MDI_REQUIRE(n_views >= 0, "mdi_setup_cameras: negative size");
   if (n_views == 0) return MDI_OK;
-  MDI_REQUIRE(views && K && c2w && Kinv, "mdi_setup_cameras: null pointer");
+  MDI_REQUIRE(views && K && c2w, "mdi_setup_cameras: null pointer");
   mdi::setup_cameras_kernel<<<(n_views + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
       views, n_views, K, c2w, Kinv, P_out);
   MDI_CHECK_LAUNCH("mdi_setup_cameras");

@@ -93,6 +93,13 @@ MDI_HD void projection_matrix(const float* k, const float* m, float* P) {
   }
 }
 
+// inverse of a zero-skew pinhole K = [[fx,0,cx],[0,fy,cy],[0,0,1]] as torch.linalg.inv returns it
+MDI_HD void pinhole_inverse(const float* k, float* ki) {
+  ki[0] = fdiv(1.0f, k[0]); ki[1] = 0.f; ki[2] = fdiv(-k[2], k[0]);
+  ki[3] = 0.f; ki[4] = fdiv(1.0f, k[4]); ki[5] = fdiv(-k[5], k[4]);
+  ki[6] = 0.f; ki[7] = 0.f; ki[8] = 1.0f;
+}
+
 // aligned = depth * scale + shift, two roundings (lstsqrs.py:52, ransacs.py:187)
 MDI_HD float align_depth(float d, float s, float t) { return fadd(fmul(d, s), t); }
 

@@ -129,7 +129,8 @@ int mdi_sizeof_view(void);
 
 /*
  * a1: fills P, Kinv and c2w of every descriptor on the device.  K float32 [V,9], c2w float32
- * [V,16] (row-major 4x4), Kinv float32 [V,9]; P_out float32 [V,12] or NULL.
+ * [V,16] (row-major 4x4), Kinv float32 [V,9] (inv(K) computed by the caller) or NULL when every K
+ * is a zero-skew pinhole matrix (then the closed form is used); P_out float32 [V,12] or NULL.
  */
 int mdi_setup_cameras(MdiView* views, int n_views, const float* K, const float* c2w,
                       const float* Kinv, float* P_out, void* stream);

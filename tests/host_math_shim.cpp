@@ -38,5 +38,6 @@ void t_unproject(const float* Ki, const float* M, const float* z, const int* row
   }
 }
 void t_camera(const float* K, const float* c2w, float* P) { mdi::projection_matrix(K, c2w, P); }
+void t_pinhole_inv(const float* K, long long n, float* out) { for (long long i = 0; i < n; ++i) mdi::pinhole_inverse(K + 9 * i, out + 9 * i); }
 float t_residual(float h0, float h1, float d, float g) { return mdi::residual_sq(h0, h1, d, g); }
 }

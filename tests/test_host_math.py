@@ -36,6 +36,7 @@ def shim():
     lib.t_project.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
     lib.t_unproject.argtypes = [C.c_void_p] * 5 + [C.c_longlong, C.c_void_p]
     lib.t_camera.argtypes = [C.c_void_p] * 3
+    lib.t_pinhole_inv.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p]
     return lib
 
 
@@ -164,3 +165,14 @@ def test_projection_matrix_bit_exact_on_every_golden_view(shim):
         P = np.zeros((3, 4), np.float32)
         shim.t_camera(np.ascontiguousarray(K.numpy()).ctypes.data, np.ascontiguousarray(c2w.numpy()).ctypes.data, P.ctypes.data)
         assert np.array_equal(P, O.projection_matrix(K, c2w).numpy())
+
+
+def test_pinhole_inverse_equals_torch_inv(shim):
+    rng = np.random.default_rng(0)
+    n = 5000
+    K = np.zeros((n, 3, 3), np.float32)
+    K[:, 0, 0] = rng.uniform(300, 4000, n); K[:, 1, 1] = K[:, 0, 0] * rng.uniform(0.99, 1.01, n)
+    K[:, 0, 2] = rng.uniform(100, 2000, n); K[:, 1, 2] = rng.uniform(100, 1200, n); K[:, 2, 2] = 1
+    out = np.zeros_like(K)
+    shim.t_pinhole_inv(K.ctypes.data, n, out.ctypes.data)
+    assert np.array_equal(out, torch.linalg.inv(torch.from_numpy(K)).numpy())
