@@ -137,13 +137,18 @@ gather_fit_kernel(const MdiView* __restrict__ views, int64_t slots,
 // descriptors.  One thread per view.
 __global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
                                      const float* __restrict__ K, const float* __restrict__ c2w,
-                                     const float* __restrict__ Kinv, float* __restrict__ P_out) {
+                                     const float* __restrict__ Kinv, float* __restrict__ P_out,
+                                     int keep_P) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n_views) return;
   const float* k = K + 9 * (int64_t)v;
   const float* m = c2w + 16 * (int64_t)v;
   float P[12];
-  projection_matrix(k, m, P);
+  if (keep_P) {  // the caller filled the descriptors' P already
+    for (int q = 0; q < 12; ++q) P[q] = views[v].P[q];
+  } else {
+    projection_matrix(k, m, P);
+  }
   for (int q = 0; q < 12; ++q) {
     views[v].P[q] = P[q];
     views[v].c2w[q] = m[q];
@@ -173,12 +178,12 @@ __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_
 }  // namespace mdi
 
 extern "C" int mdi_setup_cameras(MdiView* views, int n_views, const float* K, const float* c2w,
-                                 const float* Kinv, float* P_out, void* stream) {
+                                 const float* Kinv, float* P_out, int keep_P, void* stream) {
   MDI_REQUIRE(n_views >= 0, "mdi_setup_cameras: negative size");
   if (n_views == 0) return MDI_OK;
   MDI_REQUIRE(views && K && c2w, "mdi_setup_cameras: null pointer");
   mdi::setup_cameras_kernel<<<(n_views + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      views, n_views, K, c2w, Kinv, P_out);
+      views, n_views, K, c2w, Kinv, P_out, keep_P);
   MDI_CHECK_LAUNCH("mdi_setup_cameras");
   return MDI_OK;
 }

@@ -276,21 +276,25 @@ class Engine:
         # a1: cameras
         Kf = vin.K.detach().cpu().float().contiguous()
         c2wf = vin.c2w.detach().cpu().float().contiguous()
-        Kinv = torch.linalg.inv(Kf)
-        cam = self._upload("cams", torch.cat([Kf.reshape(-1), c2wf.reshape(-1), Kinv.reshape(-1)]))
+        kn = Kf.numpy()
+        pinhole = bool(((kn[:, 0, 1] == 0) & (kn[:, 1, 0] == 0) & (kn[:, 2, 0] == 0) & (kn[:, 2, 1] == 0)
+                        & (kn[:, 2, 2] == 1)).all())
+        # zero-skew pinhole intrinsics: inv(K) in closed form on the device (bit-identical to
+        # torch.linalg.inv); anything else: batched LU inverse on the host like the reference
+        parts = [Kf.reshape(-1), c2wf.reshape(-1)]
+        if not pinhole:
+            parts.append(torch.linalg.inv(Kf).reshape(-1))
+        cam = self._upload("cams", torch.cat(parts))
         kp = cam.data_ptr()
         c2wp = kp + 4 * 9 * V
-        kinvp = c2wp + 4 * 16 * V
+        kinvp = None if pinhole else c2wp + 4 * 16 * V
         res.P = torch.empty((V, 3, 4), dtype=torch.float32, device=self.device)
-        L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(), st), "mdi_setup_cameras")
-        if vin.P_override is not None:  # stage-wise parity: feed the oracle's P
-            res.P.copy_(vin.P_override.to(self.device, torch.float32))
-            host_desc = desc.copy()
-            host_desc["P"] = vin.P_override.reshape(V, 12).numpy()
-            host_desc["Kinv"] = Kinv.reshape(V, 9).numpy()
-            host_desc["c2w"] = c2wf[:, :3, :4].reshape(V, 12).numpy()
-            views = self._upload("views", torch.from_numpy(host_desc.view(np.uint8).reshape(-1)))
+        if vin.P_override is not None:  # stage-wise parity / project_and_filter_sfm_pts: P as given
+            desc["P"] = vin.P_override.reshape(V, 12).numpy()
+            views = self._upload("views", torch.from_numpy(desc.view(np.uint8).reshape(-1)))
             vp = views.data_ptr()
+        L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(),
+                                      0 if vin.P_override is None else 1, st), "mdi_setup_cameras")
 
         i32, f32 = torch.int32, torch.float32
         res.status = torch.zeros(V, dtype=i32, device=self.device)

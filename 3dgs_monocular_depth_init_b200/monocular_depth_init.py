@@ -43,22 +43,40 @@ def gather_scene(parser, device, depth_source: Callable):
     return depths, masks, images, torch.stack(Ks), torch.stack(c2ws), names
 
 
+class SfmTable:
+    """Device-resident SfM inputs of a scene: parser.points and the per-view index lists
+    (parser.point_indices) concatenated into 16-byte aligned slot ranges."""
+
+    def __init__(self, points: np.ndarray, point_indices: dict, names, device):
+        lists = [np.asarray(point_indices[n]) for n in names]
+        counts = np.fromiter((len(a) for a in lists), dtype=np.int64, count=len(lists))
+        padded = (counts + 3) & ~3
+        begin = np.zeros(len(lists) + 1, dtype=np.int64)
+        np.cumsum(padded, out=begin[1:])
+        idx = np.zeros(int(begin[-1]) + 4, dtype=np.int32)
+        if len(lists):
+            flat = np.concatenate(lists)
+            # destination slot of every index: slot begin of its view + position within the view
+            pos = np.arange(flat.shape[0], dtype=np.int64) + np.repeat(begin[:-1] - (np.cumsum(counts) - counts), counts)
+            idx[pos] = flat
+        self.counts = counts
+        self.host_bytes = int(points.shape[0]) * 12 + idx.nbytes
+        self.xyz = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float32)).to(device, non_blocking=True)
+        self.index = torch.from_numpy(idx).to(device, non_blocking=True)
+
+
 @torch.no_grad()
 def points_from_views(config, depths, masks, images, K, c2w, names, points: np.ndarray, point_indices: dict,
-                      device, image_kind: int = L.IMAGE_F32_255, sample_idx: Optional[torch.Tensor] = None):
-    """The batched hot path.  images: per-view [H,W,3] tensors (float32 0..255 or uint8), on the
-    device or in pinned host memory.  Returns the engine RunResult (xyz / rgb on the device)."""
+                      device, image_kind: int = L.IMAGE_F32_255, sample_idx: Optional[torch.Tensor] = None,
+                      sfm: Optional[SfmTable] = None):
+    """The batched hot path.  depths / masks / images: stacked tensors or per-view lists; images
+    are [H,W,3] float32 0..255 or uint8, on the device or in pinned host memory.  `sfm` is an
+    already uploaded SfmTable of (points, point_indices, names); built here when omitted.
+    Returns the engine RunResult (xyz / rgb on the device)."""
     eng = get_engine(device)
     dev = eng.device
-    counts = np.array([len(point_indices[n]) for n in names], dtype=np.int64)
-    padded = (counts + 3) & ~3
-    idx = np.zeros(int(padded.sum()) + 4, dtype=np.int32)
-    o = 0
-    for n, c, p in zip(names, counts, padded):
-        idx[o:o + c] = point_indices[n]
-        o += p
-    sfm_xyz = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float32)).to(dev)
-    sfm_index = torch.from_numpy(idx).to(dev)
+    if sfm is None:
+        sfm = SfmTable(points, point_indices, names, dev)
     opt = options_from_config(config)
     if opt.aligner in ("ransac", "msac"):
         if sample_idx is not None:
@@ -66,7 +84,7 @@ def points_from_views(config, depths, masks, images, K, c2w, names, points: np.n
         else:
             opt.ransac_seed = ransac_seed()
     vin = ViewInputs(depth=depths, mask=masks, image=images, image_kind=image_kind, K=K, c2w=c2w,
-                     sfm_xyz=sfm_xyz, sfm_index=sfm_index, sfm_counts=counts)
+                     sfm_xyz=sfm.xyz, sfm_index=sfm.index, sfm_counts=sfm.counts)
     return eng.run(vin, opt)
 
 
@@ -133,16 +151,16 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     mask_d = eng._buf("e2e_mask", mask_h.numel(), torch.uint8).view(mask_h.shape)
     depth_d.copy_(depth_h, non_blocking=True)
     mask_d.copy_(mask_h.view(torch.uint8), non_blocking=True)
+    sfm = SfmTable(points, point_indices, names, dev)
     res = points_from_views(config, depth_d, mask_d, image_h, K, c2w, names, points, point_indices, dev,
-                            image_kind, sample_idx)
+                            image_kind, sample_idx, sfm=sfm)
     rgb_h = torch.empty(res.rgb.shape, dtype=torch.float32, pin_memory=True)
     rgb_h.copy_(res.rgb, non_blocking=True)
     counts_h = torch.empty(res.view_counts.shape, dtype=torch.int64, pin_memory=True)
     counts_h.copy_(res.view_counts, non_blocking=True)
     torch.cuda.current_stream().synchronize()
-    n_sfm = sum(len(point_indices[n]) for n in names)
     h2d = depth_h.numel() * 4 + mask_h.numel() + res.total * 3 * image_h.element_size() \
-        + points.shape[0] * 12 + n_sfm * 4 + len(names) * (L.VIEW_DTYPE.itemsize + 34 * 4)
+        + sfm.host_bytes + len(names) * (L.VIEW_DTYPE.itemsize + 25 * 4)
     d2h = res.total * 12 + counts_h.numel() * 8 + 8
     res.extras = {"counts_host": counts_h}
     return res, rgb_h, int(h2d), int(d2h)

@@ -164,17 +164,20 @@ def run_ours(args):
     dmod = mod("distributed")
 
     V, H, W, n_sfm, aligner, subsample = WORKLOADS[args.workload]
+    if args.views:
+        V = args.views
     cfg = make_config(aligner, subsample)
     sc = mod("synthetic").make_scene(n_views=V, H=H, W=W, n_sfm=n_sfm, seed=20261104 + 7919 * rank,
                                      device=str(dev), low_conf_every=50)
     depth, mask, image = sc.depth, sc.mask, sc.image   # resident in HBM before the timed region
+    sfm = mdi.SfmTable(sc.points, sc.point_indices, sc.names, dev)
     HW = H * W
     input_bytes = depth.numel() * 4 + mask.numel() + image.numel()
 
     def step():
         torch.manual_seed(1234)
         res = mdi.points_from_views(cfg, depth, mask, image, sc.K, sc.c2w, sc.names, sc.points,
-                                    sc.point_indices, dev, L.IMAGE_U8)
+                                    sc.point_indices, dev, L.IMAGE_U8, sfm=sfm)
         if world > 1:
             xyz, rgb, _ = dmod.allgather_points(res.xyz, res.rgb)
         return res
@@ -184,7 +187,8 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    n_warm = args.warmup if args.profile_mode else max(args.warmup, 3)
+    for _ in range(n_warm):
         res = step()
     barrier()
     clocks = ClockSampler(local)
@@ -210,6 +214,14 @@ def run_ours(args):
     n_kept = int(res.total)
     n_ok = int((res.status == 0).sum())
 
+    if args.profile_mode:
+        if rank == 0:
+            clocks.stop()
+            print(json.dumps({"profile_mode": True, "ms_per_step": ms_total / args.steps, "kernels": ktimes,
+                              "kept": n_kept, "views": V}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
     # ---- end to end: host buffers in, rgb out, through the public API --------------------------
     depth_h = depth.cpu().pin_memory(); mask_h = mask.cpu().pin_memory(); image_h = image.cpu().pin_memory()
     h2d = d2h = 0
@@ -268,7 +280,7 @@ def run_ours(args):
     nv, dt, kept_cpu, cores = cpu_reference_run(args.workload, args.cpu_views)
     out = {
         "metric": "init views/sec (align+subsample+unproject)", "value": views_per_s, "unit": "views/s",
-        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+        "n_gpus": world, "steps": args.steps, "warmup": n_warm, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "views_per_gpu": V, "H": H, "W": W, "sfm_points_per_view": n_sfm,
                    "aligner": aligner, "subsample": subsample, "patch_mask": True,
@@ -297,6 +309,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
     ap.add_argument("--cpu-views", type=int, default=12, help="views in the bounded CPU sample")
+    ap.add_argument("--views", type=int, default=0, help="override views per GPU (profiling runs only)")
+    ap.add_argument("--profile-mode", action="store_true",
+                    help="short run for ncu: warm-up as given, no e2e / CPU legs (not a bench value)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -131,9 +131,10 @@ int mdi_sizeof_view(void);
  * a1: fills P, Kinv and c2w of every descriptor on the device.  K float32 [V,9], c2w float32
  * [V,16] (row-major 4x4), Kinv float32 [V,9] (inv(K) computed by the caller) or NULL when every K
  * is a zero-skew pinhole matrix (then the closed form is used); P_out float32 [V,12] or NULL.
+ * keep_P != 0: the descriptors already hold P (it is kept and copied to P_out).
  */
 int mdi_setup_cameras(MdiView* views, int n_views, const float* K, const float* c2w,
-                      const float* Kinv, float* P_out, void* stream);
+                      const float* Kinv, float* P_out, int keep_P, void* stream);
 
 /*
  * a2: project the SfM points of every view, filter, compact in order.
