@@ -15,10 +15,11 @@ PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libmdi_b200.so"
 
 # ---- constants mirrored from include/mdi_b200.h ------------------------------------------------
-ABI_VERSION = 1
+ABI_VERSION = 2
 TILE_PX = 4096
 TILE_WORDS = TILE_PX // 32
 PATCH_STRIDE = 2048
+FACTOR_TABLE_STRIDE = 40
 STATUS_OK, STATUS_LOW_CONFIDENCE, STATUS_EMPTY_STATS = 0, 1, 2
 IMAGE_F32_UNIT, IMAGE_F32_255, IMAGE_U8 = 0, 1, 2
 SUBSAMPLE_STATIC, SUBSAMPLE_ADAPTIVE = 0, 1
@@ -75,7 +76,8 @@ _SIGNATURES = {
     "mdi_depth_range_workspace_bytes": (_I64, [_INT]),
     "mdi_depth_range": (_INT, [_P, _INT, _I64, _P, _P, _INT, _P, _P, _P, _P]),
     "mdi_grad_range": (_INT, [_P, _INT, _I64, _P, _P, _P, _P]),
-    "mdi_keep_mask": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),
+    "mdi_factor_table": (_INT, [_INT, _P, _INT, _INT, _P, _P]),
+    "mdi_keep_mask": (_INT, [_P, _INT, _I64, _I64, _INT, _P, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),
     "mdi_scan_tiles": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P]),
     "mdi_emit_points": (_INT, [_P, _INT, _I64, _P, _P, _P, _INT, _P, _P, _P]),
     "mdi_min_extents": (_INT, [_P, _I64, _P, _P, _P, _INT, _P, _P]),

@@ -1,59 +1,68 @@
 // k3_mask.cu -- keep-mask predicate (a5-a10): alignment applied on the fly, sentinel / >= 0 /
 // predicted-mask tests, SfM-density patch lookup, optional gradient mask, static or adaptive
-// stride test.  One CTA per 4096-pixel tile; every lane owns 4 consecutive pixels per step
-// (one 128-bit depth load + one 32-bit mask load), the warp assembles 4 bit words per step
-// with redux.or, the tile count feeds the order-preserving compaction (mdi_scan_tiles /
-// mdi_emit_points).  HBM-bound: 5 B/px read, 1 B/px (+1/8 B/px bits) written.
-#include <mutex>
-
+// stride test.
+//
+// A pixel can only be kept if its stride f divides BOTH its row and its column, so the kept
+// pixels of stride f lie on the lattice (f i, f j).  Instead of testing every pixel, the hot
+// kernel (keep_lattice_kernel) zero-fills the outputs at copy speed and then walks the lattices
+// of the strides of the configured range: sum_f (H/f)(W/f) = 16 % of the pixels for the default
+// 5..15 range, 1 % for stride 10; rows that hold no lattice point are never read.  At a lattice
+// point of stride f the pixel is kept iff its own stride equals f.  The adaptive stride f(a) is a
+// non-increasing step function of the aligned depth a (every fp32 operation of
+// adaptive_subsampling.py:12-17,89-120 is monotone), so `f(a) == f` is two comparisons against
+// per-view breakpoints found by bisection over the float keys with the exact arithmetic
+// (factor_table_kernel); irregular views (NaN bounds, hi <= lo) evaluate the exact arithmetic at
+// the lattice points instead.  Kept pixels set their keep byte, their bit in the tile bit words
+// and bump the tile count that the order-preserving compaction consumes (mdi_scan_tiles /
+// mdi_emit_points).  Configurations without a stride test run the per-pixel kernel.
 #include "common.cuh"
 
 namespace mdi {
 
 constexpr int kMaskThreads = 256;
-constexpr int kDivTabSize = 1 << 16;
 
-// divtab[x] bit k (1 <= k <= 31) = (x % k == 0)
-__global__ void build_divtab_kernel(uint32_t* tab, int n) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= n) return;
-  uint32_t m = 0;
-  for (int k = 1; k < 32; ++k) m |= ((x % k) == 0 ? 1u : 0u) << k;
-  tab[x] = m;
-}
-
-static std::mutex g_tab_mutex;
-static uint32_t* g_divtab[64] = {nullptr};
-
-// lazily built per device; contents are a pure function of the index, so sharing is safe
-static int get_divtab(cudaStream_t stream, const uint32_t** out) {
-  int dev = 0;
-  MDI_CUDA(cudaGetDevice(&dev), "divtab");
-  MDI_REQUIRE(dev >= 0 && dev < 64, "divtab: device ordinal %d out of range", dev);
-  std::lock_guard<std::mutex> lock(g_tab_mutex);
-  if (!g_divtab[dev]) {
-    uint32_t* p = nullptr;
-    MDI_CUDA(cudaMalloc(&p, sizeof(uint32_t) * kDivTabSize), "divtab alloc");
-    build_divtab_kernel<<<kDivTabSize / 256, 256, 0, stream>>>(p, kDivTabSize);
-    MDI_CHECK_LAUNCH("divtab build");
-    MDI_CUDA(cudaStreamSynchronize(stream), "divtab sync");
-    g_divtab[dev] = p;
+// a7 breakpoints.  Row v of `table` (MDI_FACTOR_TABLE_STRIDE floats): [0] = 1 if the fast path is
+// valid for the view; [1 + j], j = 0 .. n (n = fmax - fmin + 1): B[0] = NaN, B[j] = A_{fmin+j-1},
+// A_k = smallest float with adaptive_factor(.) <= k, so that
+//     adaptive_factor(a) == k   <=>   a >= B[k - fmin + 1]  &&  !(a >= B[k - fmin]).
+__global__ void factor_table_kernel(int n_views, const float* __restrict__ lo_hi, int fmin,
+                                    int fmax, float* __restrict__ table) {
+  const int v = blockIdx.x * (blockDim.x >> 5) + warp_id();
+  if (v >= n_views) return;
+  const int lane = lane_id();
+  float* row = table + (int64_t)v * MDI_FACTOR_TABLE_STRIDE;
+  const float lo = lo_hi[2 * v], hi = lo_hi[2 * v + 1];
+  const float den = fsub(hi, lo);
+  const int n = fmax - fmin + 1;
+  const bool valid = (lo == lo) && (hi == hi) && (fabsf(lo) <= 3.4028234e38f) &&
+                     (fabsf(den) <= 3.4028234e38f) && (den > 0.f) && fmin >= 1 && fmax >= fmin &&
+                     n <= 31;
+  if (lane == 0) { row[0] = valid ? 1.f : 0.f; row[1] = NAN; }
+  if (!valid) return;
+  // lane j (0 <= j < n) owns A_k for k = fmin + j
+  if (lane < n) {
+    const int k = fmin + lane;
+    float A;
+    if (k == fmax) {
+      A = -INFINITY;
+    } else {
+      uint32_t klo = float_to_key(-INFINITY), khi = float_to_key(INFINITY);
+      while (klo < khi) {
+        const uint32_t mid = klo + ((khi - klo) >> 1);
+        if (adaptive_factor(key_to_float(mid), lo, hi, fmin, fmax) <= k) khi = mid; else klo = mid + 1;
+      }
+      A = key_to_float(klo);
+    }
+    row[2 + lane] = A;
   }
-  *out = g_divtab[dev];
-  return MDI_OK;
-}
-
-__device__ __forceinline__ bool divides_tab(const uint32_t* __restrict__ tab, int idx, int f) {
-  if (f > 0 && f < 32 && idx < kDivTabSize) return (__ldg(&tab[idx]) >> f) & 1u;
-  return divides(idx, f);
 }
 
 // |d(r,c) - d(r,c-1)| + |d(r,c) - d(r-1,c)| on the aligned depth (points_from_depth.py:205-209)
-__device__ __forceinline__ float grad_at(const MdiView& vw, int64_t p, int row, int col, float a,
-                                         float s, float t) {
+__device__ __forceinline__ float grad_at(const float* __restrict__ depth, int W, int64_t p, int row,
+                                         int col, float a, float s, float t) {
   float g = 0.f;
-  if (col >= 1) g = fadd(g, fabsf(fsub(a, align_depth(__ldg(&vw.depth[p - 1]), s, t))));
-  if (row >= 1) g = fadd(g, fabsf(fsub(a, align_depth(__ldg(&vw.depth[p - vw.W]), s, t))));
+  if (col >= 1) g = fadd(g, fabsf(fsub(a, align_depth(__ldg(&depth[p - 1]), s, t))));
+  if (row >= 1) g = fadd(g, fabsf(fsub(a, align_depth(__ldg(&depth[p - W]), s, t))));
   return g;
 }
 
@@ -62,154 +71,204 @@ struct MaskParams {
   float grad_thresh;
 };
 
-__global__ void __launch_bounds__(kMaskThreads)
-keep_mask_kernel(const MdiView* __restrict__ views, int n_views,
-                 const float* __restrict__ scale_shift, const int32_t* __restrict__ status,
-                 const float* __restrict__ lo_hi, const float* __restrict__ grad_range,
-                 const uint8_t* __restrict__ patch_blocked, const uint32_t* __restrict__ divtab,
-                 MaskParams prm, uint8_t* __restrict__ keep, uint32_t* __restrict__ bits,
-                 int32_t* __restrict__ tile_counts) {
-  __shared__ int s_count;
-  const int64_t tile = blockIdx.x;
-  const int v = find_view(views, n_views, tile);
-  const MdiView vw = views[v];
-  const int64_t HW = (int64_t)vw.H * vw.W;
-  const int64_t tile_px0 = (tile - vw.tile_begin) * MDI_TILE_PX;
-  const bool skip = status && status[v] != MDI_STATUS_OK;
+// every test but the stride test, for one pixel q = (r, c) with aligned depth a
+struct RestCtx {
+  const float* depth; const uint8_t* pmask; const uint8_t* pb; const float* grad_range;
+  int W, patch_h, patch_w, grid_h, grid_w, flags, v;
+  float s, t, grad_thresh;
+};
+__device__ __forceinline__ bool rest_ok(const RestCtx& x, int64_t q, int r, int c, float a) {
+  bool ok = true;
+  if (x.flags & MDI_KEEP_PRED_MASK) ok = x.pmask ? (__ldg(&x.pmask[q]) != 0) : true;
+  if (x.flags & MDI_KEEP_SENTINEL) ok = ok && (a != -42.0f);
+  if (x.flags & MDI_KEEP_NONNEG) ok = ok && (a >= 0.f);
+  if (ok && x.pb) {
+    const int pr = r / x.patch_h, pc = c / x.patch_w;
+    if (pr < x.grid_h && pc < x.grid_w && __ldg(&x.pb[pr * x.grid_w + pc])) ok = false;
+  }
+  if (ok && (x.flags & MDI_KEEP_GRAD)) {
+    const float gmin = x.grad_range[2 * x.v];
+    // (g - min) / ((max - min) + 1e-8)   (points_from_depth.py:210-211)
+    const float gden = fadd(fsub(x.grad_range[2 * x.v + 1], gmin), 1e-8f);
+    const float g = grad_at(x.depth, x.W, q, r, c, a, x.s, x.t);
+    ok = fdiv(fsub(g, gmin), gden) <= x.grad_thresh;
+  }
+  return ok;
+}
+
+__device__ __forceinline__ RestCtx make_ctx(const MdiView* vp, int v, const MaskParams& prm,
+                                            const uint8_t* patch_blocked, const float* grad_range,
+                                            float s, float t) {
+  RestCtx x;
+  x.depth = vp->depth; x.pmask = vp->mask;
+  x.pb = (prm.flags & MDI_KEEP_PATCH) && patch_blocked ? patch_blocked + (int64_t)v * MDI_PATCH_STRIDE : nullptr;
+  x.grad_range = grad_range;
+  x.W = vp->W; x.patch_h = vp->patch_h; x.patch_w = vp->patch_w; x.grid_h = vp->grid_h; x.grid_w = vp->grid_w;
+  x.flags = prm.flags; x.v = v; x.s = s; x.t = t; x.grad_thresh = prm.grad_thresh;
+  return x;
+}
+
+// mark pixel q of the view as kept (outputs were zero-filled before the launch)
+__device__ __forceinline__ void mark_kept(const MdiView* vp, int64_t q, uint8_t* __restrict__ keep,
+                                          uint32_t* __restrict__ bits, int32_t* __restrict__ tile_counts) {
+  if (keep) keep[vp->px_begin + q] = 1;
+  const int64_t tile = vp->tile_begin + (q >> 12);
+  const int local = (int)(q & (MDI_TILE_PX - 1));
+  atomicOr(&bits[tile * MDI_TILE_WORDS + (local >> 5)], 1u << (local & 31));
+  atomicAdd(&tile_counts[tile], 1);
+}
+
+constexpr int kLatticeWarps = 8;
+
+// One warp per (view, stride f, lattice row i): pixels (f i, f j), j = lane, lane + 32, ...
+// grid = (ceil(max_rows / kLatticeWarps), n_strides, n_views)
+__global__ void __launch_bounds__(kLatticeWarps * 32)
+keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
+                    const int32_t* __restrict__ status, const float* __restrict__ lo_hi,
+                    const float* __restrict__ grad_range, const uint8_t* __restrict__ patch_blocked,
+                    const float* __restrict__ factor_table, MaskParams prm,
+                    uint8_t* __restrict__ keep, uint32_t* __restrict__ bits,
+                    int32_t* __restrict__ tile_counts) {
+  const int v = blockIdx.z;
+  if (status && status[v] != MDI_STATUS_OK) return;
+  const bool adaptive = prm.mode == MDI_SUBSAMPLE_ADAPTIVE;
+  const int f = adaptive ? prm.fmin + (int)blockIdx.y : prm.static_factor;
+  const int i = blockIdx.x * kLatticeWarps + warp_id();
+  const MdiView* vp = views + v;
+  const int H = vp->H, W = vp->W;
+  const int64_t r64 = (int64_t)i * f;
+  if (r64 >= H) return;
+  const int r = (int)r64;
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
-  float lo = 0.f, hi = 0.f, gmin = 0.f, gden = 1.f;
-  if (prm.mode == MDI_SUBSAMPLE_ADAPTIVE && lo_hi) { lo = lo_hi[2 * v]; hi = lo_hi[2 * v + 1]; }
-  if ((prm.flags & MDI_KEEP_GRAD) && grad_range) {
-    gmin = grad_range[2 * v];
-    // (g - min) / ((max - min) + 1e-8)   (points_from_depth.py:210-211)
-    gden = fadd(fsub(grad_range[2 * v + 1], gmin), 1e-8f);
+  const float* __restrict__ depth = vp->depth;
+  // stride test: f(a) == f  <=>  a >= b_lo && !(a >= b_hi) when the view has a breakpoint table
+  bool table = false;
+  float b_lo = 0.f, b_hi = 0.f, lo = 0.f, hi = 0.f;
+  if (adaptive) {
+    const float* row = factor_table ? factor_table + (int64_t)v * MDI_FACTOR_TABLE_STRIDE : nullptr;
+    table = row && row[0] != 0.f;
+    if (table) { b_lo = row[1 + (f - prm.fmin + 1)]; b_hi = row[1 + (f - prm.fmin)]; }
+    else { lo = lo_hi[2 * v]; hi = lo_hi[2 * v + 1]; }
   }
-  const uint8_t* pb = (prm.flags & MDI_KEEP_PATCH) && patch_blocked
-                          ? patch_blocked + (int64_t)v * MDI_PATCH_STRIDE : nullptr;
-  uint8_t* keep_v = keep ? keep + vw.px_begin : nullptr;
-  const bool vec_ok = ((reinterpret_cast<uintptr_t>(vw.depth) & 15) == 0) &&
-                      (!vw.mask || (reinterpret_cast<uintptr_t>(vw.mask) & 3) == 0) &&
-                      (!keep_v || (reinterpret_cast<uintptr_t>(keep_v) & 3) == 0);
-  if (threadIdx.x == 0) s_count = 0;
-  __syncthreads();
+  const RestCtx ctx = make_ctx(vp, v, prm, patch_blocked, grad_range, s, t);
+  const int64_t row0 = (int64_t)r * W;
+  for (int64_t c64 = (int64_t)lane_id() * f; c64 < W; c64 += 32LL * f) {
+    const int c = (int)c64;
+    const int64_t q = row0 + c;
+    const float a = align_depth(__ldg(&depth[q]), s, t);
+    bool hit = true;
+    if (adaptive) {
+      if (table && a == a) {
+        hit = (a >= b_lo) && !(a >= b_hi);
+      } else {
+        // exact arithmetic; a NaN stride (INT32_MIN) keeps index 0 only: visit it once, at fmin
+        const int fa = adaptive_factor(a, table ? lo_hi[2 * v] : lo, table ? lo_hi[2 * v + 1] : hi,
+                                       prm.fmin, prm.fmax);
+        hit = (fa == INT32_MIN) ? (r == 0 && c == 0 && f == prm.fmin) : (fa == f);
+      }
+    }
+    if (hit && rest_ok(ctx, q, r, c, a)) mark_kept(vp, q, keep, bits, tile_counts);
+  }
+}
 
-  const int lane = lane_id(), warp = warp_id();
-  int my_count = 0;
+// Per-pixel predicate for configurations the lattice walk does not cover (no stride test,
+// strides outside 1..max).  One CTA per 4096-pixel tile, one lane per pixel.
+__global__ void __launch_bounds__(kMaskThreads)
+keep_pixel_kernel(const MdiView* __restrict__ views, int n_views,
+                  const float* __restrict__ scale_shift, const int32_t* __restrict__ status,
+                  const float* __restrict__ lo_hi, const float* __restrict__ grad_range,
+                  const uint8_t* __restrict__ patch_blocked, MaskParams prm,
+                  uint8_t* __restrict__ keep, uint32_t* __restrict__ bits,
+                  int32_t* __restrict__ tile_counts) {
+  const int64_t tile = blockIdx.x;
+  const int v = find_view(views, n_views, tile);
+  if (status && status[v] != MDI_STATUS_OK) return;
+  const MdiView* vp = views + v;
+  const int W = vp->W;
+  const int64_t HW = (int64_t)vp->H * W;
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  float lo = 0.f, hi = 0.f;
+  if (prm.mode == MDI_SUBSAMPLE_ADAPTIVE && lo_hi) { lo = lo_hi[2 * v]; hi = lo_hi[2 * v + 1]; }
+  const RestCtx ctx = make_ctx(vp, v, prm, patch_blocked, grad_range, s, t);
+  const int64_t q0 = (tile - vp->tile_begin) * MDI_TILE_PX;
 #pragma unroll 1
-  for (int it = 0; it < 4; ++it) {
-    const int local = warp * 512 + it * 128 + lane * 4;
-    const int64_t p0 = tile_px0 + local;
-    uint32_t nib = 0;
-    if (!skip && p0 < HW) {
-      float dv[4];
-      uint32_t mk = 0x01010101u;
-      const bool full = (p0 + 4 <= HW);
-      if (full && vec_ok) {
-        const float4 d4 = __ldg(reinterpret_cast<const float4*>(vw.depth + p0));
-        dv[0] = d4.x; dv[1] = d4.y; dv[2] = d4.z; dv[3] = d4.w;
-        if (vw.mask) mk = __ldg(reinterpret_cast<const uint32_t*>(vw.mask + p0));
-      } else {
-        mk = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const bool in = (p0 + k < HW);
-          dv[k] = in ? __ldg(&vw.depth[p0 + k]) : 0.f;
-          const uint32_t m = in ? (vw.mask ? (uint32_t)__ldg(&vw.mask[p0 + k]) : 1u) : 0u;
-          mk |= (m ? 1u : 0u) << (8 * k);
-        }
-      }
-      int row = (int)(p0 / vw.W);
-      int col = (int)(p0 - (int64_t)row * vw.W);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        if (p0 + k < HW) {
-          const float a = align_depth(dv[k], s, t);
-          bool ok = true;
-          if (prm.flags & MDI_KEEP_PRED_MASK) ok = ((mk >> (8 * k)) & 0xffu) != 0;
-          if (prm.flags & MDI_KEEP_SENTINEL) ok = ok && (a != -42.0f);
-          const bool in_pop = ok;  // population of the subsampler's `mask` argument
-          if (prm.flags & MDI_KEEP_NONNEG) ok = ok && (a >= 0.f);
-          if (ok && pb) {
-            const int pr = row / vw.patch_h, pc = col / vw.patch_w;
-            if (pr < vw.grid_h && pc < vw.grid_w && __ldg(&pb[pr * vw.grid_w + pc])) ok = false;
-          }
-          if (ok && (prm.flags & MDI_KEEP_GRAD)) {
-            const float g = grad_at(vw, p0 + k, row, col, a, s, t);
-            ok = fdiv(fsub(g, gmin), gden) <= prm.grad_thresh;
-          }
-          if (ok && (prm.flags & MDI_KEEP_SUBSAMPLE)) {
-            int f;
-            if (prm.mode == MDI_SUBSAMPLE_STATIC) {
-              f = prm.static_factor;
-            } else {
-              // invalid pixels get multiplier 0.5 but are removed by `& mask` anyway
-              f = in_pop ? adaptive_factor(a, lo, hi, prm.fmin, prm.fmax) : 1;
-            }
-            ok = divides_tab(divtab, row, f) && divides_tab(divtab, col, f);
-          }
-          nib |= (ok ? 1u : 0u) << k;
-        }
-        if (++col == vw.W) { col = 0; ++row; }
-      }
+  for (int k = threadIdx.x; k < MDI_TILE_PX; k += kMaskThreads) {
+    const int64_t q = q0 + k;
+    if (q >= HW) break;
+    const int r = (int)(q / W), c = (int)(q - (int64_t)r * W);
+    const float a = align_depth(__ldg(&vp->depth[q]), s, t);
+    bool ok = rest_ok(ctx, q, r, c, a);
+    if (ok && (prm.flags & MDI_KEEP_SUBSAMPLE)) {
+      const int f = (prm.mode == MDI_SUBSAMPLE_STATIC)
+                        ? prm.static_factor : adaptive_factor(a, lo, hi, prm.fmin, prm.fmax);
+      ok = divides(r, f) && divides(c, f);
     }
-    // keep bytes
-    if (keep_v && p0 < HW) {
-      if (vec_ok && p0 + 4 <= HW) {
-        const uint32_t bytes = (nib & 1u) | ((nib & 2u) << 7) | ((nib & 4u) << 14) | ((nib & 8u) << 21);
-        *reinterpret_cast<uint32_t*>(keep_v + p0) = bytes;
-      } else {
-        for (int k = 0; k < 4; ++k)
-          if (p0 + k < HW) keep_v[p0 + k] = (nib >> k) & 1u;
-      }
-    }
-    // 4 bit words of this 128-pixel step: word j <- nibbles of lanes 8j .. 8j+7
-    const uint32_t shifted = nib << (4 * (lane & 7));
-    uint32_t mine = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t w = __reduce_or_sync(0xffffffffu, (lane >> 3) == j ? shifted : 0u);
-      if (lane == j) mine = w;
-    }
-    if (lane < 4) {
-      bits[tile * MDI_TILE_WORDS + warp * 16 + it * 4 + lane] = mine;
-      my_count += __popc(mine);
-    }
+    if (ok) mark_kept(vp, q, keep, bits, tile_counts);
   }
-  my_count = warp_sum_i32(my_count);
-  if (lane == 0 && my_count) atomicAdd(&s_count, my_count);
-  __syncthreads();
-  if (threadIdx.x == 0) tile_counts[tile] = s_count;
 }
 
 }  // namespace mdi
 
+extern "C" int mdi_factor_table(int n_views, const float* lo_hi, int factor_min, int factor_max,
+                                float* table, void* stream) {
+  MDI_REQUIRE(n_views >= 0, "mdi_factor_table: negative size");
+  if (n_views == 0) return MDI_OK;
+  MDI_REQUIRE(lo_hi && table, "mdi_factor_table: null pointer");
+  mdi::factor_table_kernel<<<(n_views + 3) / 4, 128, 0, (cudaStream_t)stream>>>(
+      n_views, lo_hi, factor_min, factor_max, table);
+  MDI_CHECK_LAUNCH("mdi_factor_table");
+  return MDI_OK;
+}
+
 extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_tiles,
-                             const float* scale_shift, const int32_t* status, const float* lo_hi,
-                             const float* grad_range, const uint8_t* patch_blocked,
+                             int64_t total_px, int max_height, const float* scale_shift,
+                             const int32_t* status, const float* lo_hi, const float* grad_range,
+                             const uint8_t* patch_blocked, const float* factor_table,
                              const MdiSubsampleConfig* cfg, uint8_t* keep, uint32_t* bits,
                              int32_t* tile_counts, void* stream) {
-  MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_keep_mask: negative size");
+  using namespace mdi;
+  MDI_REQUIRE(n_views >= 0 && total_tiles >= 0 && total_px >= 0, "mdi_keep_mask: negative size");
   if (n_views == 0 || total_tiles == 0) return MDI_OK;
   MDI_REQUIRE(views && cfg && bits && tile_counts, "mdi_keep_mask: null pointer");
   MDI_REQUIRE(total_tiles < (1LL << 31), "mdi_keep_mask: too many tiles");
-  mdi::MaskParams prm{cfg->mode, cfg->static_factor, cfg->factor_min, cfg->factor_max, cfg->flags,
-                      cfg->grad_thresh};
+  MDI_REQUIRE(n_views <= 65535, "mdi_keep_mask: more than 65535 views per call");
+  MaskParams prm{cfg->mode, cfg->static_factor, cfg->factor_min, cfg->factor_max, cfg->flags,
+                 cfg->grad_thresh};
+  bool lattice = false;
+  int n_strides = 1, min_stride = 1;
   if (prm.flags & MDI_KEEP_SUBSAMPLE) {
-    if (prm.mode == MDI_SUBSAMPLE_STATIC)
+    if (prm.mode == MDI_SUBSAMPLE_STATIC) {
       MDI_REQUIRE(prm.static_factor != 0, "mdi_keep_mask: static_factor == 0 (modulo by zero)");
-    else {
+      // row % f == 0 depends on |f| only (|INT32_MIN| overflows: per-pixel path)
+      lattice = prm.static_factor != INT32_MIN;
+      if (lattice && prm.static_factor < 0) prm.static_factor = -prm.static_factor;
+      min_stride = lattice ? prm.static_factor : 1;
+    } else {
       MDI_REQUIRE(prm.mode == MDI_SUBSAMPLE_ADAPTIVE, "mdi_keep_mask: unknown mode %d", prm.mode);
       MDI_REQUIRE(lo_hi, "mdi_keep_mask: adaptive mode needs lo_hi");
+      lattice = prm.fmin >= 1 && prm.fmax >= prm.fmin && prm.fmax - prm.fmin < 4096;
+      n_strides = prm.fmax - prm.fmin + 1;
+      min_stride = prm.fmin;
     }
   }
   MDI_REQUIRE(!(prm.flags & MDI_KEEP_GRAD) || grad_range, "mdi_keep_mask: grad flag needs grad_range");
-  const uint32_t* tab = nullptr;
-  int rc = mdi::get_divtab((cudaStream_t)stream, &tab);
-  if (rc != MDI_OK) return rc;
-  mdi::keep_mask_kernel<<<(unsigned)total_tiles, mdi::kMaskThreads, 0, (cudaStream_t)stream>>>(
-      views, n_views, scale_shift, status, lo_hi, grad_range, patch_blocked, tab, prm, keep, bits,
-      tile_counts);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (keep) MDI_CUDA(cudaMemsetAsync(keep, 0, (size_t)total_px, st), "mdi_keep_mask memset");
+  MDI_CUDA(cudaMemsetAsync(bits, 0, (size_t)total_tiles * MDI_TILE_WORDS * 4, st), "mdi_keep_mask memset");
+  MDI_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)total_tiles * 4, st), "mdi_keep_mask memset");
+  if (lattice && max_height > 0) {
+    const int max_rows = (max_height + min_stride - 1) / min_stride;
+    dim3 grid((max_rows + kLatticeWarps - 1) / kLatticeWarps, n_strides, n_views);
+    keep_lattice_kernel<<<grid, kLatticeWarps * 32, 0, st>>>(
+        views, scale_shift, status, lo_hi, grad_range, patch_blocked, factor_table, prm, keep, bits,
+        tile_counts);
+  } else {
+    keep_pixel_kernel<<<(unsigned)total_tiles, kMaskThreads, 0, st>>>(
+        views, n_views, scale_shift, status, lo_hi, grad_range, patch_blocked, prm, keep, bits,
+        tile_counts);
+  }
   MDI_CHECK_LAUNCH("mdi_keep_mask");
   return MDI_OK;
 }

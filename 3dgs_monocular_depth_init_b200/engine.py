@@ -139,7 +139,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 # kernels launched by each C-ABI entry point (for the bench's `gpu_launches` claim)
 KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
-    "mdi_apply_scale_shift": 1, "mdi_depth_range": 7, "mdi_grad_range": 3, "mdi_keep_mask": 1,
+    "mdi_apply_scale_shift": 1, "mdi_depth_range": 7, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 1, "mdi_emit_points": 1, "mdi_min_extents": 1,
 }
 
@@ -362,6 +362,7 @@ class Engine:
             return res
 
         # a7 / a9: per-view statistics
+        ftab = None
         adaptive = opt.subsample == "adaptive"
         if not adaptive and not isinstance(opt.subsample, int):
             raise ValueError(f"Unsupported subsampling factor: {opt.subsample}")
@@ -377,6 +378,9 @@ class Engine:
             L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
                                         flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL), ws.data_ptr(),
                                         res.lo_hi.data_ptr(), res.quantiles.data_ptr(), st), "mdi_depth_range")
+            ftab = self._buf("factor_table", V * L.FACTOR_TABLE_STRIDE, f32)
+            L.check(lib.mdi_factor_table(V, res.lo_hi.data_ptr(), int(opt.factor_min), int(opt.factor_max),
+                                         ftab.data_ptr(), st), "mdi_factor_table")
         if opt.grad_thresh is not None:
             flags |= L.KEEP_GRAD
             res.grad_range = torch.empty((V, 2), dtype=f32, device=self.device)
@@ -392,8 +396,8 @@ class Engine:
             res.keep = torch.empty(int(px_begin[-1]), dtype=torch.uint8, device=self.device)
         bits = self._buf("bits", total_tiles * L.TILE_WORDS, i32)
         tile_counts = self._buf("tile_counts", total_tiles, i32)
-        L.check(lib.mdi_keep_mask(vp, V, total_tiles, ssp, res.status.data_ptr(), L.ptr(res.lo_hi),
-                                  L.ptr(res.grad_range), L.ptr(res.patch_blocked), C.byref(scfg),
+        L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), ssp, res.status.data_ptr(), L.ptr(res.lo_hi),
+                                  L.ptr(res.grad_range), L.ptr(res.patch_blocked), L.ptr(ftab), C.byref(scfg),
                                   L.ptr(res.keep), bits.data_ptr(), tile_counts.data_ptr(), st), "mdi_keep_mask")
         tile_offsets = self._buf("tile_offsets", total_tiles, torch.int64)
         meta = torch.empty(2 * V + 1, dtype=torch.int64, device=self.device)

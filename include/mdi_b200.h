@@ -18,6 +18,7 @@
  *   mdi_apply_scale_shift   lstsqrs.py:51-54 / ransacs.py:186-189 (aligned_depth = depth*s + t)
  *   mdi_depth_range         gs_init_compare/depth_subsampling/adaptive_subsampling.py:82-98
  *   mdi_grad_range          points_from_depth.py:192-212 (min / max of the gradient map)
+ *   mdi_factor_table        adaptive_subsampling.py:12-17,89-120 (stride as a function of depth)
  *   mdi_keep_mask           static_subsampler.py:11-22, adaptive_subsampling.py:48-79,105-122,
  *                           pipeline.py:285-288, points_from_depth.py:268-290
  *   mdi_scan_tiles          points_from_depth.py:292-297 (boolean-index compaction order),
@@ -37,7 +38,7 @@
 extern "C" {
 #endif
 
-#define MDI_ABI_VERSION 1
+#define MDI_ABI_VERSION 2
 
 /* error codes */
 #define MDI_OK 0
@@ -56,6 +57,9 @@ extern "C" {
 
 /* max patches of the SfM-density grid per view (20 on the small axis, <= 102 on the large) */
 #define MDI_PATCH_STRIDE 2048
+
+/* floats per view of the adaptive-stride breakpoint table (mdi_factor_table) */
+#define MDI_FACTOR_TABLE_STRIDE 40
 
 /* image element kinds for the RGB gather */
 #define MDI_IMAGE_F32_UNIT 0 /* float32 already in 0..1 (InputImage.data)          */
@@ -196,14 +200,29 @@ int mdi_grad_range(const MdiView* views, int n_views, int64_t max_tiles_per_view
                    void* stream);
 
 /*
+ * a7 (breakpoints): the adaptive stride f(a) = trunc(clamp((fmax-fmin) * (1 - clamp((a-lo)/(hi-lo)))
+ * + fmin)) is a non-increasing step function of the aligned depth a; this finds, per view, the
+ * exact fp32 breakpoints of every stride by bisection with the reference's arithmetic, so that
+ * mdi_keep_mask decides `f(a) == k` with two comparisons.  table float32
+ * [V, MDI_FACTOR_TABLE_STRIDE]; entry 0 of a row is 0 when the view is irregular (NaN / empty
+ * range, strides > 31) and mdi_keep_mask then evaluates the arithmetic per pixel.
+ */
+int mdi_factor_table(int n_views, const float* lo_hi, int factor_min, int factor_max,
+                     float* table, void* stream);
+
+/*
  * a5-a10 (predicate): composes the keep mask of every pixel.
+ *   factor_table: output of mdi_factor_table for the same lo_hi / factor range, or NULL.
+ *   total_px = sum H*W (size of keep), max_height = max H: the outputs are zero-filled and the
+ *   stride lattices (f i, f j) of the configured strides are walked, one warp per lattice row.
  *   keep      uint8 [sum H*W] at px_begin (may be NULL), bits uint32 [total_tiles*128] (bit i of
  *   word w of tile t = pixel t*4096 + 32*w + i), tile_counts int32 [total_tiles].
  */
-int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_tiles,
-                  const float* scale_shift, const int32_t* status, const float* lo_hi,
+int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_tiles, int64_t total_px,
+                  int max_height, const float* scale_shift, const int32_t* status, const float* lo_hi,
                   const float* grad_range, const uint8_t* patch_blocked,
-                  const MdiSubsampleConfig* cfg, uint8_t* keep, uint32_t* bits,
+                  const float* factor_table, const MdiSubsampleConfig* cfg, uint8_t* keep,
+                  uint32_t* bits,
                   int32_t* tile_counts, void* stream);
 
 /*
