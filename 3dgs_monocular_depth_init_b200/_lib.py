@@ -20,7 +20,8 @@ TILE_PX = 4096
 TILE_WORDS = TILE_PX // 32
 PATCH_STRIDE = 2048
 FACTOR_TABLE_STRIDE = 40
-STATUS_OK, STATUS_LOW_CONFIDENCE, STATUS_EMPTY_STATS = 0, 1, 2
+STATUS_OK, STATUS_LOW_CONFIDENCE, STATUS_EMPTY_STATS, STATUS_STATS_RETRY = 0, 1, 2, 4
+STATS_EXACT, STATS_RETRY_FLAGGED = 64, 128
 IMAGE_F32_UNIT, IMAGE_F32_255, IMAGE_U8 = 0, 1, 2
 SUBSAMPLE_STATIC, SUBSAMPLE_ADAPTIVE = 0, 1
 KEEP_PRED_MASK, KEEP_SENTINEL, KEEP_NONNEG, KEEP_PATCH, KEEP_GRAD, KEEP_SUBSAMPLE = 1, 2, 4, 8, 16, 32
@@ -73,8 +74,8 @@ _SIGNATURES = {
     "mdi_gather_fit": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P, _INT, _INT, _P, _P]),
     "mdi_ransac": (_INT, [_P, _INT, _P, _P, _P, _P, _P, C.POINTER(RansacConfigC), _INT, _P, _P, _P, _P, _P]),
     "mdi_apply_scale_shift": (_INT, [_P, _I64, _P, _P, _P]),
-    "mdi_depth_range_workspace_bytes": (_I64, [_INT]),
-    "mdi_depth_range": (_INT, [_P, _INT, _I64, _P, _P, _INT, _P, _P, _P, _P]),
+    "mdi_depth_range_workspace_bytes": (_I64, [_INT, _I64]),
+    "mdi_depth_range": (_INT, [_P, _INT, _I64, _P, _P, _INT, _P, _P, _P, _P, _P]),
     "mdi_grad_range": (_INT, [_P, _INT, _I64, _P, _P, _P, _P]),
     "mdi_factor_table": (_INT, [_INT, _P, _INT, _INT, _P, _P]),
     "mdi_keep_mask": (_INT, [_P, _INT, _I64, _I64, _INT, _P, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),

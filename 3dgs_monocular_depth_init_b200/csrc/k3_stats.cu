@@ -1,8 +1,24 @@
-// k3_stats.cu -- per-view statistics of the aligned depth for adaptive subsampling (a7):
-// masked min / max and the exact order statistics behind torch.quantile(x, 0.25 / 0.75)
-// (adaptive_subsampling.py:82-95), by a 12/12/8-bit radix select on order-preserving keys.
-// Three streaming passes over depth + mask (HBM/L2-bound, shared-memory histograms), each
-// followed by a one-CTA-per-view bin search.  Also the gradient-map range for a9.
+// k3_stats.cu -- per-view statistics of the aligned depth for adaptive subsampling (a7): masked
+// min / max and the exact order statistics behind torch.quantile(x, 0.25 / 0.75)
+// (adaptive_subsampling.py:82-95).  Also the gradient-map range for a9.
+//
+// Fast path ("sample-select", ONE streaming pass over depth + mask, HBM-bound):
+//   1. stats_sample_kernel   reads one hashed 32-byte sector (8 pixels) out of every 16: HW/16 keys
+//   2. stats_bracket_kernel  radix-selects, in that sample, key brackets [L, U] around each
+//                            quantile wide enough to hold the true order statistics
+//   3. stats_main_kernel     the one full pass: min / max / count, the number of keys below each
+//                            bracket, a 2048-bin histogram of the keys inside each bracket, and
+//                            those keys (a few %) appended to a per-view candidate list through a
+//                            shared-memory stage
+//   4. stats_finish_kernel   rank - #below located in the bracket histogram, the candidates of
+//                            that one bin gathered into shared memory and ranked exactly, then
+//                            torch.quantile's fp32 rank / lerp arithmetic
+// The result is exact whenever step 4 verifies; if a bracket missed (or a list overflowed, e.g. a
+// constant depth map) the view is flagged MDI_STATUS_STATS_RETRY and the host re-runs it through
+// the exact path below.
+//
+// Exact path (three streaming passes): 12/12/8-bit radix select on order-preserving keys over
+// all pixels, shared-memory histograms, one-CTA-per-view bin search after each pass.
 #include "common.cuh"
 
 namespace mdi {
@@ -11,18 +27,61 @@ constexpr int kStatsThreads = 256;
 constexpr int kStatsTilesPerCta = 16;  // 64K pixels per CTA amortise histogram zero/flush
 constexpr int kBins = 4096;
 constexpr int kTargets = 4;            // q1.lo, q1.hi, q3.lo, q3.hi
+constexpr int kSampleGroup = 128;      // one 8-pixel sector sampled per group of 128 pixels
+constexpr int kBrBins = 2048;          // histogram bins per quantile bracket
+constexpr int kListCap = 2048;         // keys of one bracket bin ranked in shared memory
+constexpr int kSelThreads = 1024;
+constexpr int kSelBins = 2048;
 
-struct StatsView {
-  uint32_t hist[kTargets][kBins];
-  uint32_t min_key, max_key, count, n_slots;
+struct StatsHdr {
+  // sample-select path
+  uint32_t n_sample, n_cand;
+  uint32_t min_key, max_key, count;
+  uint32_t below[2];
+  uint32_t br_lo[2], br_hi[2], br_shift[2];
+  uint32_t run_exact;  // this view goes through the exact path in this call
+  // exact path
+  uint32_t x_min_key, x_max_key, x_count, n_slots;
   uint32_t slot_prefix[kTargets];  // prefix each histogram slot selects on
   uint32_t tgt_prefix[kTargets];
   uint32_t tgt_slot[kTargets];
+  uint32_t _pad[3];
   long long tgt_rank[kTargets];
   float w[2];
-  uint32_t gmin_key, gmax_key;     // gradient range (mdi_grad_range)
-  uint32_t _pad[2];
+  uint32_t gmin_key, gmax_key;
 };
+
+struct StatsWs {
+  StatsHdr* hdr;       // [V]
+  uint32_t* hist;      // [V][kTargets][kBins]   (exact path)
+  uint32_t* sample;    // [V][s_cap]
+  uint32_t* cand;      // [V][c_cap]
+  int64_t s_cap, c_cap;
+};
+
+static int64_t sample_cap(int64_t max_tiles) {
+  return max_tiles * (MDI_TILE_PX / kSampleGroup) * 8;
+}
+static int64_t cand_cap(int64_t max_tiles) {
+  const int64_t px = max_tiles * MDI_TILE_PX;
+  int64_t c = px / 4;
+  const int64_t floor_c = px < 16384 ? px : 16384;
+  return c > floor_c ? c : floor_c;
+}
+static StatsWs carve(void* workspace, int n_views, int64_t max_tiles) {
+  StatsWs w;
+  char* p = reinterpret_cast<char*>(workspace);
+  w.hdr = reinterpret_cast<StatsHdr*>(p);
+  p += ((sizeof(StatsHdr) * (size_t)n_views + 255) / 256) * 256;
+  w.hist = reinterpret_cast<uint32_t*>(p);
+  p += sizeof(uint32_t) * kTargets * kBins * (size_t)n_views;
+  w.s_cap = sample_cap(max_tiles);
+  w.c_cap = cand_cap(max_tiles);
+  w.sample = reinterpret_cast<uint32_t*>(p);
+  p += sizeof(uint32_t) * (size_t)w.s_cap * n_views;
+  w.cand = reinterpret_cast<uint32_t*>(p);
+  return w;
+}
 
 __device__ __forceinline__ bool in_population(uint32_t maskbyte, float a, int flags) {
   bool ok = true;
@@ -31,13 +90,439 @@ __device__ __forceinline__ bool in_population(uint32_t maskbyte, float a, int fl
   return ok;
 }
 
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+
+// ---- generic block-wide radix select over a key list -------------------------------------------
+// Among keys[0..n) with flo[j] <= key <= fhi[j], finds the key of (0-based, ascending) rank
+// rank[j], for j < kTargets.  11/11/10-bit passes, histogram updates aggregated per warp with
+// match.any (depth keys cluster in a handful of top-digit bins).  Returns a bit mask of the
+// targets whose rank lies outside their filtered population.  All kSelThreads threads call it.
+struct SelShared {
+  uint32_t hist[kTargets][kSelBins];
+  int scan[33];
+  uint32_t pre[kTargets];
+  uint32_t bin[kTargets];
+  long long rank[kTargets];
+  long long newrank[kTargets];
+  uint32_t fail;
+};
+
+__device__ uint32_t block_select(const uint32_t* __restrict__ keys, uint32_t n,
+                                 const uint32_t* flo, const uint32_t* fhi, const long long* rank,
+                                 uint32_t* out, SelShared& sh) {
+  const int tid = threadIdx.x, lane = tid & 31;
+  uint32_t lo[kTargets], hi[kTargets];
+#pragma unroll
+  for (int j = 0; j < kTargets; ++j) { lo[j] = flo[j]; hi[j] = fhi[j]; }
+  if (tid < kTargets) { sh.pre[tid] = 0; sh.rank[tid] = rank[tid]; }
+  if (tid == 0) sh.fail = 0;
+  __syncthreads();
+#pragma unroll 1
+  for (int pass = 0; pass < 3; ++pass) {
+    const int pshift = pass == 0 ? 32 : (pass == 1 ? 21 : 10);   // bits above the digit
+    const int dshift = pass == 0 ? 21 : (pass == 1 ? 10 : 0);
+    const uint32_t dmask = pass == 2 ? 0x3ffu : 0x7ffu;
+    for (int i = tid; i < kTargets * kSelBins; i += kSelThreads) (&sh.hist[0][0])[i] = 0;
+    uint32_t pre[kTargets];
+    int slot[kTargets];
+#pragma unroll
+    for (int j = 0; j < kTargets; ++j) {
+      pre[j] = sh.pre[j];
+      slot[j] = j;
+      for (int i = 0; i < j; ++i)
+        if (slot[j] == j && lo[i] == lo[j] && hi[i] == hi[j] && pre[i] == pre[j]) slot[j] = i;
+    }
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += kSelThreads) {
+      const uint32_t i = base + tid;
+      const bool in = i < n;
+      const uint32_t key = in ? keys[i] : 0u;
+      const uint32_t top = pass == 0 ? 0u : (key >> pshift);
+      const uint32_t b = (key >> dshift) & dmask;
+#pragma unroll
+      for (int j = 0; j < kTargets; ++j) {
+        if (slot[j] != j) continue;  // uniform
+        const bool p = in && key >= lo[j] && key <= hi[j] && top == pre[j];
+        const uint32_t act = __ballot_sync(0xffffffffu, p);
+        if (p) {
+          const uint32_t peers = __match_any_sync(act, b);
+          if (lane == __ffs(peers) - 1) atomicAdd(&sh.hist[j][b], (uint32_t)__popc(peers));
+        }
+      }
+    }
+    __syncthreads();
+    // locate each rank in its histogram: 2 bins per thread
+#pragma unroll 1
+    for (int j = 0; j < kTargets; ++j) {
+      const uint32_t* h = sh.hist[slot[j]];
+      const uint32_t c0 = h[2 * tid], c1 = h[2 * tid + 1];
+      int tot;
+      const long long cum = block_excl_scan((int)(c0 + c1), sh.scan, &tot);
+      const long long r = sh.rank[j];
+      if (r >= cum && r < cum + c0) { sh.bin[j] = 2 * tid; sh.newrank[j] = r - cum; }
+      else if (r >= cum + c0 && r < cum + c0 + c1) { sh.bin[j] = 2 * tid + 1; sh.newrank[j] = r - cum - c0; }
+      if (tid == 0 && (r < 0 || r >= tot)) { atomicOr(&sh.fail, 1u << j); sh.bin[j] = 0; sh.newrank[j] = 0; }
+      __syncthreads();
+    }
+    if (tid < kTargets) {
+      const int bits = pass == 2 ? 10 : 11;
+      sh.pre[tid] = (sh.pre[tid] << bits) | sh.bin[tid];
+      sh.rank[tid] = sh.newrank[tid];
+    }
+    __syncthreads();
+  }
+  if (tid < kTargets) out[tid] = sh.pre[tid];
+  __syncthreads();
+  return sh.fail;
+}
+
+// ---- sample-select path --------------------------------------------------------------------------
+__global__ void stats_init_kernel(StatsHdr* hdr, int n_views, const int32_t* status, int mode) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_views) return;
+  hdr[v].min_key = 0xFFFFFFFFu; hdr[v].x_min_key = 0xFFFFFFFFu;
+  // mode 0: sample-select for everybody; 1: exact for everybody; 2: exact for views flagged RETRY
+  const bool retry = status && (status[v] & MDI_STATUS_STATS_RETRY);
+  hdr[v].run_exact = mode == 1 ? 1u : (mode == 2 ? (retry ? 1u : 0u) : 0u);
+}
+
+// One thread per group of 128 pixels: a hashed 8-pixel sector of the group is sampled (32 B of
+// depth, 8 B of mask), so the sample is spread over the whole image at sector granularity.
+__global__ void __launch_bounds__(256)
+stats_sample_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
+                    const int32_t* __restrict__ status, int flags, StatsWs ws) {
+  const int v = blockIdx.y;
+  const MdiView* vp = views + v;
+  const int64_t HW = (int64_t)vp->H * vp->W;
+  const int64_t group = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((int64_t)blockIdx.x * blockDim.x * kSampleGroup >= HW) return;
+  if (status && (status[v] & MDI_STATUS_LOW_CONFIDENCE)) return;
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const float* __restrict__ depth = vp->depth;
+  const uint8_t* __restrict__ pmask = vp->mask;
+  const int64_t p0 = group * kSampleGroup + (hash32((uint32_t)group * 2654435761u + (uint32_t)v) & 15u) * 8;
+  uint32_t keys[8];
+  int c = 0;
+  if (p0 < HW) {
+    float dv[8];
+    uint32_t mb[8];
+    if (p0 + 8 <= HW && (reinterpret_cast<uintptr_t>(depth) & 15) == 0) {
+      const float4 x = __ldg(reinterpret_cast<const float4*>(depth + p0));
+      const float4 y = __ldg(reinterpret_cast<const float4*>(depth + p0 + 4));
+      dv[0] = x.x; dv[1] = x.y; dv[2] = x.z; dv[3] = x.w; dv[4] = y.x; dv[5] = y.y; dv[6] = y.z; dv[7] = y.w;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mb[k] = pmask ? (uint32_t)__ldg(&pmask[p0 + k]) : 1u;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const bool in = p0 + k < HW;
+        dv[k] = in ? __ldg(&depth[p0 + k]) : 0.f;
+        mb[k] = in ? (pmask ? (uint32_t)__ldg(&pmask[p0 + k]) : 1u) : 0u;
+        if (!in) mb[k] = 0xFFFFFFFFu;  // marks "outside"
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (mb[k] == 0xFFFFFFFFu) continue;
+      const float a = align_depth(dv[k], s, t);
+      if (in_population(mb[k], a, flags)) keys[c++] = float_to_key(a);
+    }
+  }
+  // warp-aggregated append
+  const int incl = warp_incl_scan(c);
+  const int tot = __shfl_sync(0xffffffffu, incl, 31);
+  if (tot) {
+    uint32_t base = 0;
+    if (lane_id() == 31) base = atomicAdd(&ws.hdr[v].n_sample, (uint32_t)tot);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    uint32_t* dst = ws.sample + (int64_t)v * ws.s_cap + base + (incl - c);
+    for (int k = 0; k < c; ++k) dst[k] = keys[k];
+  }
+}
+
+__global__ void __launch_bounds__(kSelThreads)
+stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
+  __shared__ SelShared sh;
+  __shared__ uint32_t s_flo[kTargets], s_fhi[kTargets], s_out[kTargets];
+  __shared__ long long s_rank[kTargets];
+  const int v = blockIdx.x;
+  StatsHdr* h = ws.hdr + v;
+  if (status && (status[v] & MDI_STATUS_LOW_CONFIDENCE)) return;
+  const uint32_t ns = h->n_sample;
+  if (ns < 1024) {  // too small to bracket: everything is a candidate (tiny images fit the list)
+    if (threadIdx.x == 0) {
+      for (int g = 0; g < 2; ++g) { h->br_lo[g] = 0; h->br_hi[g] = 0xFFFFFFFFu; h->br_shift[g] = 21; }
+    }
+    return;
+  }
+  // half-width of the rank bracket: the sample is ns / 8 sectors of 8 adjacent (correlated) pixels,
+  // so 4.5 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
+  const double delta = 0.005 + 4.5 * sqrt(0.1875 * 8.0 / (double)ns);
+  bool open_lo[2], open_hi[2];
+  if (threadIdx.x == 0) {
+    for (int g = 0; g < 2; ++g) {
+      const double q = g == 0 ? 0.25 : 0.75;
+      long long rl = (long long)floor((q - delta) * (double)ns);
+      long long rh = (long long)ceil((q + delta) * (double)ns);
+      s_rank[2 * g] = rl < 0 ? 0 : rl;
+      s_rank[2 * g + 1] = rh > (long long)ns - 1 ? (long long)ns - 1 : rh;
+    }
+    for (int j = 0; j < kTargets; ++j) { s_flo[j] = 0; s_fhi[j] = 0xFFFFFFFFu; }
+  }
+  __syncthreads();
+  for (int g = 0; g < 2; ++g) {
+    const double q = g == 0 ? 0.25 : 0.75;
+    open_lo[g] = (q - delta) * (double)ns < 1.0;
+    open_hi[g] = (q + delta) * (double)ns > (double)ns - 2.0;
+  }
+  block_select(ws.sample + (int64_t)v * ws.s_cap, ns, s_flo, s_fhi, s_rank, s_out, sh);
+  if (threadIdx.x == 0) {
+    for (int g = 0; g < 2; ++g) {
+      const uint32_t L = open_lo[g] ? 0u : s_out[2 * g];
+      const uint32_t U = open_hi[g] ? 0xFFFFFFFFu : s_out[2 * g + 1];
+      uint32_t sft = 0;
+      while (((U - L) >> sft) >= (uint32_t)kBrBins) ++sft;
+      h->br_lo[g] = L; h->br_hi[g] = U; h->br_shift[g] = sft;
+    }
+  }
+}
+
+constexpr int kStageCap = MDI_TILE_PX;
+
+__global__ void __launch_bounds__(kStatsThreads)
+stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
+                  const int32_t* __restrict__ status, int flags, StatsWs ws) {
+  __shared__ uint32_t s_stage[kStageCap];
+  __shared__ uint32_t s_brhist[2][kBrBins];
+  __shared__ uint32_t s_n, s_base;
+  __shared__ uint32_t s_min, s_max, s_cnt, s_below[2];
+  const int v = blockIdx.y;
+  const MdiView* vp = views + v;
+  const int first_tile = blockIdx.x * kStatsTilesPerCta;
+  if (first_tile >= vp->n_tiles) return;
+  if (status && (status[v] & MDI_STATUS_LOW_CONFIDENCE)) return;
+  StatsHdr* h = ws.hdr + v;
+  const uint32_t L0 = h->br_lo[0], L1 = h->br_lo[1];
+  const uint32_t W0 = h->br_hi[0] - L0, W1 = h->br_hi[1] - L1;  // bracket widths (unsigned)
+  const uint32_t sh0 = h->br_shift[0], sh1 = h->br_shift[1];
+  for (int i = threadIdx.x; i < 2 * kBrBins; i += kStatsThreads) (&s_brhist[0][0])[i] = 0;
+  if (threadIdx.x == 0) { s_n = 0; s_min = 0xFFFFFFFFu; s_max = 0u; s_cnt = 0u; s_below[0] = 0; s_below[1] = 0; }
+  __syncthreads();
+  const float* __restrict__ depth = vp->depth;
+  const uint8_t* __restrict__ pmask = vp->mask;
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const int64_t HW = (int64_t)vp->H * vp->W;
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(depth) & 15) == 0) &&
+                      (!pmask || (reinterpret_cast<uintptr_t>(pmask) & 3) == 0);
+  uint32_t kmin = 0xFFFFFFFFu, kmax = 0u, cnt = 0, below0 = 0, below1 = 0;
+  uint32_t* cand = ws.cand + (int64_t)v * ws.c_cap;
+
+  auto feed = [&](float dv, uint32_t mbyte) {
+    const float a = align_depth(dv, s, t);
+    if (!in_population(mbyte, a, flags)) return;
+    const uint32_t key = float_to_key(a);
+    kmin = min(kmin, key); kmax = max(kmax, key); ++cnt;
+    below0 += key < L0 ? 1u : 0u;
+    below1 += key < L1 ? 1u : 0u;
+    const uint32_t o0 = key - L0, o1 = key - L1;
+    const bool in0 = o0 <= W0, in1 = o1 <= W1;
+    if (in0 || in1) {
+      if (in0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
+      if (in1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
+      const uint32_t slot = atomicAdd(&s_n, 1u);
+      s_stage[slot] = key;  // <= 4096 candidates per tile by construction
+    }
+  };
+
+  const int last_tile = min(first_tile + kStatsTilesPerCta, (int)vp->n_tiles);
+#pragma unroll 1
+  for (int tile = first_tile; tile < last_tile; ++tile) {
+    const int64_t px0 = (int64_t)tile * MDI_TILE_PX;
+    if (vec_ok && px0 + MDI_TILE_PX <= HW) {
+      // 4 x (128-bit depth + 32-bit mask) loads in flight per thread, then the arithmetic
+      float4 d4[4];
+      uint32_t mk[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int64_t p = px0 + (int64_t)(k * kStatsThreads + threadIdx.x) * 4;
+        d4[k] = __ldg(reinterpret_cast<const float4*>(depth + p));
+        mk[k] = pmask ? __ldg(reinterpret_cast<const uint32_t*>(pmask + p)) : 0x01010101u;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        feed(d4[k].x, mk[k] & 0xffu); feed(d4[k].y, (mk[k] >> 8) & 0xffu);
+        feed(d4[k].z, (mk[k] >> 16) & 0xffu); feed(d4[k].w, mk[k] >> 24);
+      }
+    } else {
+      for (int k = threadIdx.x; k < MDI_TILE_PX; k += kStatsThreads) {
+        const int64_t p = px0 + k;
+        if (p < HW) feed(__ldg(&depth[p]), pmask ? (uint32_t)__ldg(&pmask[p]) : 1u);
+      }
+    }
+    __syncthreads();
+    // flush the stage: one reservation per tile, coalesced copy
+    const uint32_t n = s_n;
+    if (n) {
+      if (threadIdx.x == 0) s_base = atomicAdd(&h->n_cand, n);
+      __syncthreads();
+      const uint32_t base = s_base;
+      for (uint32_t i = threadIdx.x; i < n; i += kStatsThreads)
+        if ((int64_t)base + i < ws.c_cap) cand[base + i] = s_stage[i];
+      __syncthreads();
+      if (threadIdx.x == 0) s_n = 0;
+      __syncthreads();
+    }
+  }
+  kmin = __reduce_min_sync(0xffffffffu, kmin);
+  kmax = __reduce_max_sync(0xffffffffu, kmax);
+  cnt = __reduce_add_sync(0xffffffffu, cnt);
+  below0 = __reduce_add_sync(0xffffffffu, below0);
+  below1 = __reduce_add_sync(0xffffffffu, below1);
+  if (lane_id() == 0 && cnt) {
+    atomicMin(&s_min, kmin); atomicMax(&s_max, kmax); atomicAdd(&s_cnt, cnt);
+    atomicAdd(&s_below[0], below0); atomicAdd(&s_below[1], below1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_cnt) {
+    atomicMin(&h->min_key, s_min); atomicMax(&h->max_key, s_max); atomicAdd(&h->count, s_cnt);
+    atomicAdd(&h->below[0], s_below[0]); atomicAdd(&h->below[1], s_below[1]);
+  }
+  uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;  // [2][kBrBins] of it
+  for (int i = threadIdx.x; i < 2 * kBrBins; i += kStatsThreads) {
+    const uint32_t c = (&s_brhist[0][0])[i];
+    if (c) atomicAdd(&ghist[i], c);
+  }
+}
+
+// quantiles -> iqr range, written to the outputs (shared by both paths)
+__device__ __forceinline__ void write_range(int v, const float val[kTargets], float w1, float w3,
+                                            uint32_t min_key, uint32_t max_key,
+                                            float* __restrict__ lo_hi, float* __restrict__ quantiles) {
+  const bool has_nan = max_key == 0xFFFFFFFFu;
+  float q1 = torch_lerp(val[0], val[1], w1);
+  float q3 = torch_lerp(val[2], val[3], w3);
+  float mn = key_to_float(min_key), mx = key_to_float(max_key);
+  if (has_nan) { q1 = q3 = mn = mx = NAN; }
+  float lo, hi;
+  iqr_range(q1, q3, mn, mx, &lo, &hi);
+  if (lo_hi) { lo_hi[2 * v] = lo; lo_hi[2 * v + 1] = hi; }
+  if (quantiles) { quantiles[4 * v] = q1; quantiles[4 * v + 1] = q3; quantiles[4 * v + 2] = mn; quantiles[4 * v + 3] = mx; }
+}
+
+__global__ void __launch_bounds__(kSelThreads)
+stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict__ lo_hi,
+                    float* __restrict__ quantiles, int64_t* __restrict__ retry_flag) {
+  __shared__ uint32_t s_list[kTargets][kListCap];
+  __shared__ int scan_smem[33];
+  __shared__ uint32_t s_len[kTargets], s_bin[kTargets], s_out[kTargets], s_fail;
+  __shared__ long long s_rank[kTargets];
+  const int v = blockIdx.x, tid = threadIdx.x;
+  StatsHdr* h = ws.hdr + v;
+  const bool low_conf = status && (status[v] & MDI_STATUS_LOW_CONFIDENCE);
+  const uint32_t n = h->count;
+  if (low_conf || n == 0) {
+    if (tid == 0) {
+      if (lo_hi) { lo_hi[2 * v] = 0.f; lo_hi[2 * v + 1] = 0.f; }
+      if (quantiles) for (int k = 0; k < 4; ++k) quantiles[4 * v + k] = 0.f;
+      if (!low_conf && status) status[v] |= MDI_STATUS_EMPTY_STATS;
+    }
+    return;
+  }
+  const QuantileRank r1 = quantile_rank(0.25f, (int64_t)n);
+  const QuantileRank r3 = quantile_rank(0.75f, (int64_t)n);
+  const uint32_t n_cand = h->n_cand;
+  const bool has_nan = h->max_key == 0xFFFFFFFFu;
+  const uint32_t L[2] = {h->br_lo[0], h->br_lo[1]};
+  const uint32_t Wd[2] = {h->br_hi[0] - L[0], h->br_hi[1] - L[1]};
+  const uint32_t sft[2] = {h->br_shift[0], h->br_shift[1]};
+  if (tid < kTargets) { s_len[tid] = 0; s_bin[tid] = 0xFFFFFFFFu; s_out[tid] = 0; }
+  if (tid == 0) s_fail = (int64_t)n_cand > ws.c_cap ? 1u : 0u;
+  __syncthreads();
+  if (!has_nan && !s_fail) {
+    // 1. bin of each target rank in its bracket histogram (2 bins per thread)
+    const uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;
+#pragma unroll 1
+    for (int j = 0; j < kTargets; ++j) {
+      const int g = j >> 1;
+      const long long r = ((j & 1) ? (j < 2 ? r1.hi : r3.hi) : (j < 2 ? r1.lo : r3.lo)) - (long long)h->below[g];
+      const uint32_t c0 = ghist[g * kBrBins + 2 * tid], c1 = ghist[g * kBrBins + 2 * tid + 1];
+      int tot;
+      const long long cum = block_excl_scan((int)(c0 + c1), scan_smem, &tot);
+      if (r >= cum && r < cum + c0) { s_bin[j] = 2 * tid; s_rank[j] = r - cum; }
+      else if (r >= cum + c0 && r < cum + c0 + c1) { s_bin[j] = 2 * tid + 1; s_rank[j] = r - cum - c0; }
+      if (tid == 0 && (r < 0 || r >= tot)) s_fail = 1u;
+      __syncthreads();
+    }
+  }
+  if (!has_nan && !s_fail) {
+    // 2. gather the candidates of those bins (targets sharing a bin share list `slot`)
+    int slot[kTargets];
+    uint32_t bin[kTargets];
+#pragma unroll
+    for (int j = 0; j < kTargets; ++j) {
+      bin[j] = s_bin[j];
+      slot[j] = j;
+      for (int i = 0; i < j; ++i)
+        if (slot[j] == j && (i >> 1) == (j >> 1) && bin[i] == bin[j]) slot[j] = i;
+    }
+    const uint32_t* cand = ws.cand + (int64_t)v * ws.c_cap;
+    for (uint32_t i = tid; i < n_cand; i += kSelThreads) {
+      const uint32_t key = cand[i];
+#pragma unroll
+      for (int j = 0; j < kTargets; ++j) {
+        if (slot[j] != j) continue;
+        const uint32_t o = key - L[j >> 1];
+        if (o <= Wd[j >> 1] && (o >> sft[j >> 1]) == bin[j]) {
+          const uint32_t at = atomicAdd(&s_len[j], 1u);
+          if (at < (uint32_t)kListCap) s_list[j][at] = key;
+        }
+      }
+    }
+    __syncthreads();
+    // 3. exact rank inside the list: position = #smaller + #equal with a lower index
+#pragma unroll 1
+    for (int j = 0; j < kTargets; ++j) {
+      const uint32_t m = s_len[slot[j]];
+      if (m > (uint32_t)kListCap || (long long)m <= s_rank[j]) { if (tid == 0) s_fail = 1u; continue; }
+      const uint32_t* lst = s_list[slot[j]];
+      for (uint32_t a = tid; a < m; a += kSelThreads) {
+        const uint32_t key = lst[a];
+        uint32_t pos = 0;
+        for (uint32_t b = 0; b < m; ++b) {
+          const uint32_t x = lst[b];
+          pos += (x < key || (x == key && b < a)) ? 1u : 0u;
+        }
+        if ((long long)pos == s_rank[j]) s_out[j] = key;
+      }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    if (s_fail) {
+      if (lo_hi) { lo_hi[2 * v] = NAN; lo_hi[2 * v + 1] = NAN; }
+      if (status) status[v] |= MDI_STATUS_STATS_RETRY;
+      if (retry_flag) *retry_flag = 1;
+    } else {
+      float val[kTargets];
+      for (int j = 0; j < kTargets; ++j) val[j] = key_to_float(s_out[j]);
+      write_range(v, val, r1.w, r3.w, h->min_key, h->max_key, lo_hi, quantiles);
+    }
+  }
+}
+
+// ---- exact path: radix select over all pixels ------------------------------------------------------
 // PASS 0: bin = key >> 20 over everything (+ min / max / count)
 // PASS 1: bin = (key >> 8) & 0xfff over keys whose top 12 bits match a slot prefix
 // PASS 2: bin = key & 0xff over keys whose top 24 bits match a slot prefix
 template <int PASS>
 __global__ void __launch_bounds__(kStatsThreads)
 stats_pass_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
-                  const int32_t* __restrict__ status, int flags, StatsView* __restrict__ ws) {
+                  const int32_t* __restrict__ status, int flags, StatsWs ws) {
   extern __shared__ uint32_t s_hist[];  // n_slots * bins
   __shared__ uint32_t s_min, s_max, s_cnt;
   const int v = blockIdx.y;
@@ -45,7 +530,9 @@ stats_pass_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   const int first_tile = blockIdx.x * kStatsTilesPerCta;
   if (first_tile >= vw.n_tiles) return;
   if (status && (status[v] & MDI_STATUS_LOW_CONFIDENCE)) return;
-  StatsView* sv = ws + v;
+  StatsHdr* sv = ws.hdr + v;
+  if (!sv->run_exact) return;
+  uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;
   constexpr int bins = (PASS == 2) ? 256 : kBins;
   const int n_slots = (PASS == 0) ? 1 : (int)sv->n_slots;
   if (PASS != 0 && n_slots == 0) return;
@@ -108,10 +595,10 @@ stats_pass_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   __syncthreads();
   for (int i = threadIdx.x; i < n_slots * bins; i += blockDim.x) {
     const uint32_t c = s_hist[i];
-    if (c) atomicAdd(&sv->hist[i / bins][i % bins], c);
+    if (c) atomicAdd(&ghist[(i / bins) * kBins + (i % bins)], c);
   }
   if (PASS == 0 && threadIdx.x == 0 && s_cnt) {
-    atomicMin(&sv->min_key, s_min); atomicMax(&sv->max_key, s_max); atomicAdd(&sv->count, s_cnt);
+    atomicMin(&sv->x_min_key, s_min); atomicMax(&sv->x_max_key, s_max); atomicAdd(&sv->x_count, s_cnt);
   }
 }
 
@@ -120,24 +607,27 @@ stats_pass_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
 // prefixes are the keys of the order statistics: finish the quantiles and the range.
 template <int PASS>
 __global__ void __launch_bounds__(kStatsThreads)
-stats_select_kernel(int32_t* __restrict__ status, StatsView* __restrict__ ws,
-                    float* __restrict__ lo_hi, float* __restrict__ quantiles) {
+stats_select_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict__ lo_hi,
+                    float* __restrict__ quantiles) {
   __shared__ int scan_smem[33];
   __shared__ uint32_t s_bin[kTargets];
   __shared__ long long s_rank[kTargets];
   const int v = blockIdx.x;
-  StatsView* sv = ws + v;
+  StatsHdr* sv = ws.hdr + v;
+  if (!sv->run_exact) return;
+  uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;
   constexpr int bins = (PASS == 2) ? 256 : kBins;
   constexpr int shift = (PASS == 2) ? 8 : 12;
   constexpr int per_thread = bins / kStatsThreads;  // 16 or 1
   const bool low_conf = status && (status[v] & MDI_STATUS_LOW_CONFIDENCE);
-  const uint32_t n = sv->count;
+  const uint32_t n = sv->x_count;
   if (low_conf || n == 0) {
     if (threadIdx.x == 0) {
       sv->n_slots = 0;
       if (PASS == 2) {
         if (lo_hi) { lo_hi[2 * v] = 0.f; lo_hi[2 * v + 1] = 0.f; }
         if (quantiles) for (int k = 0; k < 4; ++k) quantiles[4 * v + k] = 0.f;
+        if (status) status[v] &= ~MDI_STATUS_STATS_RETRY;
         if (!low_conf && status) status[v] |= MDI_STATUS_EMPTY_STATS;
       }
     }
@@ -152,7 +642,7 @@ stats_select_kernel(int32_t* __restrict__ status, StatsView* __restrict__ ws,
   }
   __syncthreads();
   for (int j = 0; j < kTargets; ++j) {
-    const uint32_t* h = sv->hist[sv->tgt_slot[j]];
+    const uint32_t* h = ghist + (int64_t)sv->tgt_slot[j] * kBins;
     const long long rank = sv->tgt_rank[j];
     uint32_t c[per_thread];
     int mine = 0;
@@ -170,7 +660,7 @@ stats_select_kernel(int32_t* __restrict__ status, StatsView* __restrict__ ws,
     __syncthreads();
   }
   // all reads of the histograms are done: clear them for the next pass
-  for (int i = threadIdx.x; i < kTargets * kBins; i += blockDim.x) (&sv->hist[0][0])[i] = 0;
+  for (int i = threadIdx.x; i < kTargets * kBins; i += blockDim.x) ghist[i] = 0;
   if (threadIdx.x == 0) {
     uint32_t pre[kTargets];
     for (int j = 0; j < kTargets; ++j) {
@@ -187,17 +677,10 @@ stats_select_kernel(int32_t* __restrict__ status, StatsView* __restrict__ ws,
     }
     sv->n_slots = ns;
     if (PASS == 2) {
-      const bool has_nan = sv->max_key == 0xFFFFFFFFu;
       float val[kTargets];
       for (int j = 0; j < kTargets; ++j) val[j] = key_to_float(pre[j]);
-      float q1 = torch_lerp(val[0], val[1], sv->w[0]);
-      float q3 = torch_lerp(val[2], val[3], sv->w[1]);
-      float mn = key_to_float(sv->min_key), mx = key_to_float(sv->max_key);
-      if (has_nan) { q1 = q3 = mn = mx = NAN; }
-      float lo, hi;
-      iqr_range(q1, q3, mn, mx, &lo, &hi);
-      if (lo_hi) { lo_hi[2 * v] = lo; lo_hi[2 * v + 1] = hi; }
-      if (quantiles) { quantiles[4 * v] = q1; quantiles[4 * v + 1] = q3; quantiles[4 * v + 2] = mn; quantiles[4 * v + 3] = mx; }
+      write_range(v, val, sv->w[0], sv->w[1], sv->x_min_key, sv->x_max_key, lo_hi, quantiles);
+      if (status) status[v] &= ~MDI_STATUS_STATS_RETRY;
     }
   }
 }
@@ -247,48 +730,62 @@ __global__ void grad_range_finish_kernel(float* out, int n_views) {
   out[2 * v] = mn; out[2 * v + 1] = mx;
 }
 
-__global__ void stats_init_kernel(StatsView* ws, int n_views) {
-  int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v < n_views) { ws[v].min_key = 0xFFFFFFFFu; ws[v].max_key = 0u; }
-}
-
-static unsigned max_chunks(const MdiView* views_host_unused, int64_t total_tiles) {
-  // upper bound usable without reading device descriptors: no view has more tiles than the total
-  int64_t c = (total_tiles + kStatsTilesPerCta - 1) / kStatsTilesPerCta;
+static unsigned max_chunks(int64_t tiles) {
+  int64_t c = (tiles + kStatsTilesPerCta - 1) / kStatsTilesPerCta;
   return (unsigned)(c < 1 ? 1 : c);
 }
 
 }  // namespace mdi
 
-extern "C" int64_t mdi_depth_range_workspace_bytes(int n_views) {
-  return (int64_t)sizeof(mdi::StatsView) * (n_views > 0 ? n_views : 0);
+extern "C" int64_t mdi_depth_range_workspace_bytes(int n_views, int64_t max_tiles_per_view) {
+  using namespace mdi;
+  if (n_views <= 0) return 0;
+  if (max_tiles_per_view < 1) max_tiles_per_view = 1;
+  const int64_t hdr = ((int64_t)(sizeof(StatsHdr) * (size_t)n_views + 255) / 256) * 256;
+  return hdr + (int64_t)n_views * 4 * ((int64_t)kTargets * kBins + sample_cap(max_tiles_per_view) +
+                                       cand_cap(max_tiles_per_view));
 }
 
 extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_tiles_per_view,
                                const float* scale_shift, int32_t* status, int flags,
-                               void* workspace, float* lo_hi, float* quantiles, void* stream) {
+                               void* workspace, float* lo_hi, float* quantiles,
+                               int64_t* retry_flag, void* stream) {
   using namespace mdi;
   MDI_REQUIRE(n_views >= 0 && max_tiles_per_view >= 0, "mdi_depth_range: negative size");
   if (n_views == 0) return MDI_OK;
   MDI_REQUIRE(views && workspace && (lo_hi || quantiles), "mdi_depth_range: null pointer");
   MDI_REQUIRE(n_views <= 65535, "mdi_depth_range: more than 65535 views per call");
+  if (max_tiles_per_view < 1) max_tiles_per_view = 1;
   cudaStream_t st = (cudaStream_t)stream;
-  StatsView* ws = reinterpret_cast<StatsView*>(workspace);
-  MDI_CUDA(cudaMemsetAsync(ws, 0, sizeof(StatsView) * (size_t)n_views, st), "mdi_depth_range");
-  stats_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(ws, n_views);
-  static bool attr_done = false;
-  if (!attr_done) {
-    MDI_CUDA(cudaFuncSetAttribute(stats_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  kTargets * kBins * 4), "mdi_depth_range attr");
-    attr_done = true;
+  const StatsWs ws = carve(workspace, n_views, max_tiles_per_view);
+  const int mode = (flags & MDI_STATS_EXACT) ? 1 : ((flags & MDI_STATS_RETRY_FLAGGED) ? 2 : 0);
+  const int pop = flags & (MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL);
+  MDI_CUDA(cudaMemsetAsync(ws.hdr, 0, sizeof(StatsHdr) * (size_t)n_views, st), "mdi_depth_range");
+  stats_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(ws.hdr, n_views, status, mode);
+  dim3 grid(max_chunks(max_tiles_per_view), (unsigned)n_views);
+  MDI_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(uint32_t) * kTargets * kBins * (size_t)n_views, st),
+           "mdi_depth_range");
+  if (mode == 0) {
+    const int64_t groups = max_tiles_per_view * (MDI_TILE_PX / kSampleGroup);
+    stats_sample_kernel<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n_views), 256, 0, st>>>(
+        views, scale_shift, status, pop, ws);
+    stats_bracket_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws);
+    stats_main_kernel<<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, pop, ws);
+    stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
+  } else {
+    static bool attr_done = false;
+    if (!attr_done) {
+      MDI_CUDA(cudaFuncSetAttribute(stats_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    kTargets * kBins * 4), "mdi_depth_range attr");
+      attr_done = true;
+    }
+    stats_pass_kernel<0><<<grid, kStatsThreads, kBins * 4, st>>>(views, scale_shift, status, pop, ws);
+    stats_select_kernel<0><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
+    stats_pass_kernel<1><<<grid, kStatsThreads, kTargets * kBins * 4, st>>>(views, scale_shift, status, pop, ws);
+    stats_select_kernel<1><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
+    stats_pass_kernel<2><<<grid, kStatsThreads, kTargets * 256 * 4, st>>>(views, scale_shift, status, pop, ws);
+    stats_select_kernel<2><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
   }
-  dim3 grid(max_chunks(views, max_tiles_per_view), (unsigned)n_views);
-  stats_pass_kernel<0><<<grid, kStatsThreads, kBins * 4, st>>>(views, scale_shift, status, flags, ws);
-  stats_select_kernel<0><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
-  stats_pass_kernel<1><<<grid, kStatsThreads, kTargets * kBins * 4, st>>>(views, scale_shift, status, flags, ws);
-  stats_select_kernel<1><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
-  stats_pass_kernel<2><<<grid, kStatsThreads, kTargets * 256 * 4, st>>>(views, scale_shift, status, flags, ws);
-  stats_select_kernel<2><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
   MDI_CHECK_LAUNCH("mdi_depth_range");
   return MDI_OK;
 }
@@ -304,7 +801,7 @@ extern "C" int mdi_grad_range(const MdiView* views, int n_views, int64_t max_til
   cudaStream_t st = (cudaStream_t)stream;
   uint32_t* keys = reinterpret_cast<uint32_t*>(grad_range);
   grad_range_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(keys, n_views);
-  dim3 grid(max_chunks(views, max_tiles_per_view), (unsigned)n_views);
+  dim3 grid(max_chunks(max_tiles_per_view), (unsigned)n_views);
   grad_range_kernel<<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, keys);
   grad_range_finish_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(grad_range, n_views);
   MDI_CHECK_LAUNCH("mdi_grad_range");

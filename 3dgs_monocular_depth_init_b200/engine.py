@@ -79,6 +79,7 @@ class RunOptions:
     want_rgb: bool = True
     want_inliers: bool = False
     stop_after: Optional[str] = None             # "project" | "fit" | "mask": partial pipelines
+    stats_exact: bool = False                    # force the three-pass exact quantile select
 
 
 @dataclass
@@ -139,7 +140,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 # kernels launched by each C-ABI entry point (for the bench's `gpu_launches` claim)
 KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
-    "mdi_apply_scale_shift": 1, "mdi_depth_range": 7, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
+    "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 1, "mdi_emit_points": 1, "mdi_min_extents": 1,
 }
 
@@ -370,24 +371,21 @@ class Engine:
         if use_patch:
             flags |= L.KEEP_PATCH
         ssp = L.ptr(res.scale_shift)
-        if adaptive and (flags & L.KEEP_SUBSAMPLE):
-            wsb = int(lib.mdi_depth_range_workspace_bytes(V))
+        # [view counts V][view offsets V][total][stats retry flag]
+        meta = torch.zeros(2 * V + 2, dtype=torch.int64, device=self.device)
+        res.view_counts, res.view_offsets = meta[:V], meta[V:2 * V]
+        use_stats = bool(adaptive and (flags & L.KEEP_SUBSAMPLE))
+        if use_stats:
+            wsb = int(lib.mdi_depth_range_workspace_bytes(V, max_tiles))
             ws = self._buf("stats_ws", wsb, torch.uint8)
             res.lo_hi = torch.empty((V, 2), dtype=f32, device=self.device)
             res.quantiles = torch.empty((V, 4), dtype=f32, device=self.device)
-            L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
-                                        flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL), ws.data_ptr(),
-                                        res.lo_hi.data_ptr(), res.quantiles.data_ptr(), st), "mdi_depth_range")
             ftab = self._buf("factor_table", V * L.FACTOR_TABLE_STRIDE, f32)
-            L.check(lib.mdi_factor_table(V, res.lo_hi.data_ptr(), int(opt.factor_min), int(opt.factor_max),
-                                         ftab.data_ptr(), st), "mdi_factor_table")
         if opt.grad_thresh is not None:
             flags |= L.KEEP_GRAD
             res.grad_range = torch.empty((V, 2), dtype=f32, device=self.device)
             L.check(lib.mdi_grad_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
                                        res.grad_range.data_ptr(), st), "mdi_grad_range")
-
-        # a5-a10: keep mask, then order-preserving compaction + unprojection + RGB gather
         scfg = L.SubsampleConfigC(L.SUBSAMPLE_ADAPTIVE if adaptive else L.SUBSAMPLE_STATIC,
                                   0 if adaptive else int(opt.subsample), int(opt.factor_min),
                                   int(opt.factor_max), int(flags),
@@ -396,20 +394,38 @@ class Engine:
             res.keep = torch.empty(int(px_begin[-1]), dtype=torch.uint8, device=self.device)
         bits = self._buf("bits", total_tiles * L.TILE_WORDS, i32)
         tile_counts = self._buf("tile_counts", total_tiles, i32)
-        L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), ssp, res.status.data_ptr(), L.ptr(res.lo_hi),
-                                  L.ptr(res.grad_range), L.ptr(res.patch_blocked), L.ptr(ftab), C.byref(scfg),
-                                  L.ptr(res.keep), bits.data_ptr(), tile_counts.data_ptr(), st), "mdi_keep_mask")
         tile_offsets = self._buf("tile_offsets", total_tiles, torch.int64)
-        meta = torch.empty(2 * V + 1, dtype=torch.int64, device=self.device)
-        res.view_counts, res.view_offsets = meta[:V], meta[V:2 * V]
-        L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
-                                   res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
-                                   meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
+
+        def mask_stage(stats_mode: int):
+            """a7 statistics -> a5-a10 keep mask -> compaction offsets; returns (total, retry)."""
+            if use_stats:
+                L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
+                                            (flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)) | stats_mode,
+                                            ws.data_ptr(), res.lo_hi.data_ptr(), res.quantiles.data_ptr(),
+                                            meta[2 * V + 1:].data_ptr(), st), "mdi_depth_range")
+                L.check(lib.mdi_factor_table(V, res.lo_hi.data_ptr(), int(opt.factor_min), int(opt.factor_max),
+                                             ftab.data_ptr(), st), "mdi_factor_table")
+            L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), ssp,
+                                      res.status.data_ptr(), L.ptr(res.lo_hi), L.ptr(res.grad_range),
+                                      L.ptr(res.patch_blocked), L.ptr(ftab), C.byref(scfg), L.ptr(res.keep),
+                                      bits.data_ptr(), tile_counts.data_ptr(), st), "mdi_keep_mask")
+            L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
+                                       res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
+                                       meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
+            # the output size is data dependent: one 16-byte read-back (the only sync of the pipeline)
+            tail = meta[2 * V:].cpu()
+            return int(tail[0]), bool(tail[1])
+
+        res.total, retry = mask_stage(L.STATS_EXACT if opt.stats_exact else 0)
+        if retry:
+            # a view's one-pass quantile brackets could not be certified (e.g. a constant depth
+            # map): exact three-pass select for the flagged views, then mask + scan again
+            meta[2 * V + 1] = 0
+            res.extras["stats_retry"] = True
+            res.total, retry = mask_stage(L.STATS_RETRY_FLAGGED)
+            assert not retry
         if opt.stop_after == "mask" or not (opt.want_xyz or opt.want_rgb):
-            res.total = int(meta[2 * V].item())
             return res
-        # the output size is data dependent: one 8-byte read-back (the only sync of the pipeline)
-        res.total = int(meta[2 * V].item())
         N = res.total
         if opt.want_xyz:
             res.xyz = torch.empty((N, 3), dtype=f32, device=self.device)

@@ -50,6 +50,8 @@ extern "C" {
 #define MDI_STATUS_OK 0
 #define MDI_STATUS_LOW_CONFIDENCE 1 /* < 1/4 of SfM points in bounds (points_from_depth.py:124) */
 #define MDI_STATUS_EMPTY_STATS 2    /* adaptive subsampling over zero valid pixels (torch raises) */
+#define MDI_STATUS_STATS_RETRY 4    /* mdi_depth_range's one-pass path could not certify the order
+                                       statistics of this view: re-run with MDI_STATS_RETRY_FLAGGED */
 
 /* pixels per tile of the mask / compaction kernels (one CTA per tile) */
 #define MDI_TILE_PX 4096
@@ -77,6 +79,10 @@ extern "C" {
 #define MDI_KEEP_PATCH 8      /* & SfM-density patch mask               (points_from_depth.py:276) */
 #define MDI_KEEP_GRAD 16      /* & depth-gradient mask                  (points_from_depth.py:271) */
 #define MDI_KEEP_SUBSAMPLE 32 /* & subsampler mask                      (points_from_depth.py:290) */
+
+/* mdi_depth_range algorithm selection (OR-ed into its flags) */
+#define MDI_STATS_EXACT 64          /* three-pass radix select over all pixels, every view      */
+#define MDI_STATS_RETRY_FLAGGED 128 /* the same, only for views flagged MDI_STATUS_STATS_RETRY  */
 
 /* RANSAC loss kinds */
 #define MDI_LOSS_RANSAC 0 /* outlier count       (ransacs.py:60) */
@@ -185,14 +191,20 @@ int mdi_apply_scale_shift(const float* depth, int64_t n, const float* scale_shif
  * a7 (statistics): per view, over pixels with mask & (aligned != -42): min, max and the exact
  * order statistics torch.quantile(., 0.25 / 0.75) needs; writes lo_hi float32 [V,2] =
  * (max(min, q1 - 1.5 iqr), min(max, q3 + 1.5 iqr)) and ORs MDI_STATUS_EMPTY_STATS into status.
- *   workspace: mdi_depth_range_workspace_bytes(n_views) bytes, zeroed by the call itself.
- *   flags: MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL select the population.
+ *   flags: MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL select the population; MDI_STATS_* the algorithm.
+ *   Default algorithm: ONE streaming pass over depth + mask (key brackets around each quantile
+ *   from a 1/16 sample, exact select among the bracketed keys, verified by rank counting).  A
+ *   view whose brackets cannot be certified (constant depth maps, adversarial layouts) gets
+ *   MDI_STATUS_STATS_RETRY in status, NaN in lo_hi and *retry_flag = 1 (int64, device, may be
+ *   NULL; never cleared here); the caller then repeats the call with MDI_STATS_RETRY_FLAGGED,
+ *   which runs the three-pass exact radix select for the flagged views and clears the bit.
+ *   workspace: mdi_depth_range_workspace_bytes(n_views, max_tiles_per_view) bytes.
  */
-int64_t mdi_depth_range_workspace_bytes(int n_views);
+int64_t mdi_depth_range_workspace_bytes(int n_views, int64_t max_tiles_per_view);
 int mdi_depth_range(const MdiView* views, int n_views, int64_t max_tiles_per_view,
                     const float* scale_shift, int32_t* status, int flags, void* workspace,
                     float* lo_hi, float* quantiles /* [V,4] q1,q3,min,max or NULL */,
-                    void* stream);
+                    int64_t* retry_flag, void* stream);
 
 /* a9 (statistics): min and max of |dx|+|dy| of the aligned depth per view -> grad_range [V,2] */
 int mdi_grad_range(const MdiView* views, int n_views, int64_t max_tiles_per_view,

@@ -228,3 +228,46 @@ def test_ransac_device_sampler_recovers_truth():
         outs.append((res.scale_shift.cpu().numpy().copy(), res.xyz.cpu().numpy().copy()))
     assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
     assert np.allclose(outs[0][0], sc.true_scale_shift, rtol=0.02, atol=0.02)
+
+
+def _range_via_engine(aligned, mask, exact):
+    L = mod("_lib")
+    single = mod("_single")
+    eng = mod("engine").get_engine(DEV)
+    vin = single.single_view_inputs(aligned.to(DEV), mask.to(DEV), DEV)
+    opt = mod("engine").RunOptions(aligner=None, subsample="adaptive", use_patch_mask=False,
+                                   flags=L.KEEP_PRED_MASK | L.KEEP_SUBSAMPLE, want_xyz=False, want_rgb=False,
+                                   stop_after="mask", stats_exact=exact)
+    res = eng.run(vin, opt)
+    return res
+
+
+def test_quantile_one_pass_path_equals_exact_path_and_torch():
+    """a7: the one-pass (sample bracket + certified select) statistics, the three-pass radix
+    select and torch.quantile on the CPU agree bit for bit; degenerate inputs that cannot be
+    bracketed (constant / few-valued depth) go through the retry path and still agree."""
+    g = torch.Generator().manual_seed(7)
+    H, W = 600, 800
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    smooth = 4 + 1.5 * torch.sin(xx / 123.0) + torch.cos(yy / 107.0) + 0.01 * torch.randn(H, W, generator=g)
+    mask_all = torch.ones(H, W, dtype=torch.bool)
+    mask_rect = mask_all.clone(); mask_rect[100:300, 200:700] = False
+    heavy = smooth.clone(); heavy[: H // 2] = 300.0          # half the image clamped to one value
+    const = torch.full((H, W), 2.5)
+    few = torch.randint(0, 3, (H, W), generator=g).float() + 1.0
+    neg = -smooth
+    cases = [("smooth", smooth, mask_all, False), ("rect", smooth, mask_rect, False), ("neg", neg, mask_all, False),
+             ("heavy", heavy, mask_all, None), ("const", const, mask_all, True), ("few", few, mask_rect, True)]
+    for name, a, m, expect_retry in cases:
+        lo, hi = O.adaptive_range(a, m)[:2]
+        keep_ref = O.adaptive_mask(a, m, 5, 15)
+        fast = _range_via_engine(a, m, exact=False)
+        exact = _range_via_engine(a, m, exact=True)
+        for tag, r in (("fast", fast), ("exact", exact)):
+            lh = r.lo_hi[0].cpu()
+            assert float(lh[0]) == float(lo) and float(lh[1]) == float(hi), (name, tag, lh, lo, hi)
+            assert torch.equal(r.keep.view(-1).bool().cpu(), keep_ref), (name, tag)
+        assert torch.equal(fast.quantiles.cpu(), exact.quantiles.cpu()), name
+        if expect_retry is not None:
+            assert bool(fast.extras.get("stats_retry", False)) == expect_retry, name
+        assert not exact.extras.get("stats_retry", False)
