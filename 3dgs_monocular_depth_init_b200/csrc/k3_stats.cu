@@ -45,7 +45,7 @@ struct StatsHdr {
   uint32_t slot_prefix[kTargets];  // prefix each histogram slot selects on
   uint32_t tgt_prefix[kTargets];
   uint32_t tgt_slot[kTargets];
-  uint32_t _pad[3];
+  uint32_t smp_min, smp_max, _pad;
   long long tgt_rank[kTargets];
   float w[2];
   uint32_t gmin_key, gmax_key;
@@ -183,7 +183,7 @@ __device__ uint32_t block_select(const uint32_t* __restrict__ keys, uint32_t n,
 __global__ void stats_init_kernel(StatsHdr* hdr, int n_views, const int32_t* status, int mode) {
   int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n_views) return;
-  hdr[v].min_key = 0xFFFFFFFFu; hdr[v].x_min_key = 0xFFFFFFFFu;
+  hdr[v].min_key = 0xFFFFFFFFu; hdr[v].x_min_key = 0xFFFFFFFFu; hdr[v].smp_min = 0xFFFFFFFFu;
   // mode 0: sample-select for everybody; 1: exact for everybody; 2: exact for views flagged RETRY
   const bool retry = status && (status[v] & MDI_STATUS_STATS_RETRY);
   hdr[v].run_exact = mode == 1 ? 1u : (mode == 2 ? (retry ? 1u : 0u) : 0u);
@@ -206,64 +206,129 @@ stats_sample_kernel(const MdiView* __restrict__ views, const float* __restrict__
   const uint8_t* __restrict__ pmask = vp->mask;
   const int64_t p0 = group * kSampleGroup + (hash32((uint32_t)group * 2654435761u + (uint32_t)v) & 15u) * 8;
   uint32_t keys[8];
-  int c = 0;
+  uint32_t valid = 0;  // bit k: keys[k] is in the population
   if (p0 < HW) {
     float dv[8];
-    uint32_t mb[8];
-    if (p0 + 8 <= HW && (reinterpret_cast<uintptr_t>(depth) & 15) == 0) {
+    uint32_t mlo = 0x01010101u, mhi = 0x01010101u;  // mask bytes of pixels 0-3 / 4-7
+    uint32_t inside = 0xFFu;
+    if (p0 + 8 <= HW && (reinterpret_cast<uintptr_t>(depth) & 15) == 0 &&
+        (!pmask || (reinterpret_cast<uintptr_t>(pmask) & 3) == 0)) {
       const float4 x = __ldg(reinterpret_cast<const float4*>(depth + p0));
       const float4 y = __ldg(reinterpret_cast<const float4*>(depth + p0 + 4));
+      if (pmask) {
+        mlo = __ldg(reinterpret_cast<const uint32_t*>(pmask + p0));
+        mhi = __ldg(reinterpret_cast<const uint32_t*>(pmask + p0 + 4));
+      }
       dv[0] = x.x; dv[1] = x.y; dv[2] = x.z; dv[3] = x.w; dv[4] = y.x; dv[5] = y.y; dv[6] = y.z; dv[7] = y.w;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) mb[k] = pmask ? (uint32_t)__ldg(&pmask[p0 + k]) : 1u;
     } else {
+      inside = 0; mlo = 0; mhi = 0;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const bool in = p0 + k < HW;
         dv[k] = in ? __ldg(&depth[p0 + k]) : 0.f;
-        mb[k] = in ? (pmask ? (uint32_t)__ldg(&pmask[p0 + k]) : 1u) : 0u;
-        if (!in) mb[k] = 0xFFFFFFFFu;  // marks "outside"
+        const uint32_t mb = in ? (pmask ? (__ldg(&pmask[p0 + k]) ? 1u : 0u) : 1u) : 0u;
+        if (k < 4) mlo |= mb << (8 * k); else mhi |= mb << (8 * (k - 4));
+        inside |= (in ? 1u : 0u) << k;
       }
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      if (mb[k] == 0xFFFFFFFFu) continue;
       const float a = align_depth(dv[k], s, t);
-      if (in_population(mb[k], a, flags)) keys[c++] = float_to_key(a);
+      const uint32_t mb = ((k < 4 ? mlo : mhi) >> (8 * (k & 3))) & 0xffu;
+      keys[k] = float_to_key(a);
+      if (((inside >> k) & 1u) && in_population(mb, a, flags)) valid |= 1u << k;
     }
   }
+  uint32_t kmin = 0xFFFFFFFFu, kmax = 0u;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if ((valid >> k) & 1u) { kmin = min(kmin, keys[k]); kmax = max(kmax, keys[k]); }
   // warp-aggregated append
+  const int c = __popc(valid);
   const int incl = warp_incl_scan(c);
   const int tot = __shfl_sync(0xffffffffu, incl, 31);
   if (tot) {
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
     uint32_t base = 0;
-    if (lane_id() == 31) base = atomicAdd(&ws.hdr[v].n_sample, (uint32_t)tot);
+    if (lane_id() == 31) {
+      base = atomicAdd(&ws.hdr[v].n_sample, (uint32_t)tot);
+      atomicMin(&ws.hdr[v].smp_min, kmin);
+      atomicMax(&ws.hdr[v].smp_max, kmax);
+    }
     base = __shfl_sync(0xffffffffu, base, 31);
     uint32_t* dst = ws.sample + (int64_t)v * ws.s_cap + base + (incl - c);
-    for (int k = 0; k < c; ++k) dst[k] = keys[k];
+    int o = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if ((valid >> k) & 1u) dst[o++] = keys[k];
   }
 }
 
-__global__ void __launch_bounds__(kSelThreads)
+// Brackets from the sample, one CTA per view.  A 1024-key sub-sample is sorted in shared memory
+// to get a robust range [R_lo, R_hi] ~ (q 0.10, q 0.90) of the keys; one pass over the sample
+// then builds a 2048-bin linear histogram of that range (+ the counts on either side), and the
+// bracket of each quantile is the span of bins between its lower and upper sample ranks.
+constexpr int kBracketThreads = 1024;
+__global__ void __launch_bounds__(kBracketThreads)
 stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
-  __shared__ SelShared sh;
-  __shared__ uint32_t s_flo[kTargets], s_fhi[kTargets], s_out[kTargets];
+  __shared__ uint32_t s_sort[1024];
+  __shared__ uint32_t s_hist[kBrBins];
+  __shared__ int scan_smem[33];
+  __shared__ uint32_t s_under, s_bin[kTargets];
   __shared__ long long s_rank[kTargets];
-  const int v = blockIdx.x;
+  const int v = blockIdx.x, tid = threadIdx.x;
   StatsHdr* h = ws.hdr + v;
   if (status && (status[v] & MDI_STATUS_LOW_CONFIDENCE)) return;
   const uint32_t ns = h->n_sample;
-  if (ns < 1024) {  // too small to bracket: everything is a candidate (tiny images fit the list)
-    if (threadIdx.x == 0) {
+  if (ns < 4096) {  // too small to bracket: everything is a candidate (small images fit the list)
+    if (tid == 0)
       for (int g = 0; g < 2; ++g) { h->br_lo[g] = 0; h->br_hi[g] = 0xFFFFFFFFu; h->br_shift[g] = 21; }
-    }
     return;
   }
+  const uint32_t* keys = ws.sample + (int64_t)v * ws.s_cap;
+  // bitonic sort of an evenly spaced 1024-key sub-sample
+  s_sort[tid] = keys[(uint64_t)tid * ns / 1024];
+  for (int i = tid; i < kBrBins; i += kBracketThreads) s_hist[i] = 0;
+  if (tid == 0) s_under = 0;
+  __syncthreads();
+  for (int k = 2; k <= 1024; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const int ixj = tid ^ j;
+      if (ixj > tid) {
+        const uint32_t x = s_sort[tid], y = s_sort[ixj];
+        const bool up = (tid & k) == 0;
+        if ((x > y) == up) { s_sort[tid] = y; s_sort[ixj] = x; }
+      }
+      __syncthreads();
+    }
+  }
+  const uint32_t Rlo = s_sort[102], Rhi = s_sort[921];
+  uint32_t sft = 0;
+  while (((Rhi - Rlo) >> sft) >= (uint32_t)kBrBins) ++sft;
+  // linear histogram of [Rlo, Rhi]; keys below counted, keys above implied
+  uint32_t under = 0;
+  for (uint32_t base = 0; base < ns; base += 4 * kBracketThreads) {
+    uint32_t kk[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t i = base + u * kBracketThreads + tid;
+      kk[u] = i < ns ? keys[i] : 0xFFFFFFFFu;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool in = base + u * kBracketThreads + tid < ns;
+      if (!in) continue;
+      if (kk[u] < Rlo) ++under;
+      else if (kk[u] <= Rhi) atomicAdd(&s_hist[(kk[u] - Rlo) >> sft], 1u);
+    }
+  }
+  under = __reduce_add_sync(0xffffffffu, under);
+  if ((tid & 31) == 0 && under) atomicAdd(&s_under, under);
   // half-width of the rank bracket: the sample is ns / 8 sectors of 8 adjacent (correlated) pixels,
   // so 4.5 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
   const double delta = 0.005 + 4.5 * sqrt(0.1875 * 8.0 / (double)ns);
-  bool open_lo[2], open_hi[2];
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     for (int g = 0; g < 2; ++g) {
       const double q = g == 0 ? 0.25 : 0.75;
       long long rl = (long long)floor((q - delta) * (double)ns);
@@ -271,34 +336,47 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
       s_rank[2 * g] = rl < 0 ? 0 : rl;
       s_rank[2 * g + 1] = rh > (long long)ns - 1 ? (long long)ns - 1 : rh;
     }
-    for (int j = 0; j < kTargets; ++j) { s_flo[j] = 0; s_fhi[j] = 0xFFFFFFFFu; }
   }
   __syncthreads();
-  for (int g = 0; g < 2; ++g) {
-    const double q = g == 0 ? 0.25 : 0.75;
-    open_lo[g] = (q - delta) * (double)ns < 1.0;
-    open_hi[g] = (q + delta) * (double)ns > (double)ns - 2.0;
+  // bin of each bracket rank: 2 bins per thread; -1 = below the range, kBrBins = above it
+  const uint32_t c0 = s_hist[2 * tid], c1 = s_hist[2 * tid + 1];
+  int tot;
+  const long long cum = (long long)s_under + block_excl_scan((int)(c0 + c1), scan_smem, &tot);
+  if (tid < kTargets) s_bin[tid] = s_rank[tid] < (long long)s_under ? 0xFFFFFFFFu : (uint32_t)kBrBins;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < kTargets; ++j) {
+    const long long r = s_rank[j];
+    if (r >= cum && r < cum + c0) s_bin[j] = 2 * tid;
+    else if (r >= cum + c0 && r < cum + c0 + c1) s_bin[j] = 2 * tid + 1;
   }
-  block_select(ws.sample + (int64_t)v * ws.s_cap, ns, s_flo, s_fhi, s_rank, s_out, sh);
-  if (threadIdx.x == 0) {
+  __syncthreads();
+  if (tid == 0) {
     for (int g = 0; g < 2; ++g) {
-      const uint32_t L = open_lo[g] ? 0u : s_out[2 * g];
-      const uint32_t U = open_hi[g] ? 0xFFFFFFFFu : s_out[2 * g + 1];
-      uint32_t sft = 0;
-      while (((U - L) >> sft) >= (uint32_t)kBrBins) ++sft;
-      h->br_lo[g] = L; h->br_hi[g] = U; h->br_shift[g] = sft;
+      const uint32_t bl = s_bin[2 * g], bh = s_bin[2 * g + 1];
+      // lower bound: start of the lower rank's bin (open when it lies outside the range)
+      uint32_t L = 0u, U = 0xFFFFFFFFu;
+      if (bl == (uint32_t)kBrBins) L = Rhi;
+      else if (bl != 0xFFFFFFFFu) L = Rlo + (bl << sft);
+      if (bh == 0xFFFFFFFFu) U = Rlo;
+      else if (bh != (uint32_t)kBrBins) {
+        const unsigned long long e = (unsigned long long)Rlo + (((unsigned long long)bh + 1ull) << sft) - 1ull;
+        U = e > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)e;
+      }
+      uint32_t bs = 0;
+      while (((U - L) >> bs) >= (uint32_t)kBrBins) ++bs;
+      h->br_lo[g] = L; h->br_hi[g] = U; h->br_shift[g] = bs;
     }
   }
 }
 
-constexpr int kStageCap = MDI_TILE_PX;
+constexpr int kWarpStage = 768;  // keys staged per warp; flushed once fewer than 512 slots remain
 
 __global__ void __launch_bounds__(kStatsThreads)
 stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
                   const int32_t* __restrict__ status, int flags, StatsWs ws) {
-  __shared__ uint32_t s_stage[kStageCap];
+  __shared__ uint32_t s_stage[kStatsThreads / 32][kWarpStage];
   __shared__ uint32_t s_brhist[2][kBrBins];
-  __shared__ uint32_t s_n, s_base;
   __shared__ uint32_t s_min, s_max, s_cnt, s_below[2];
   const int v = blockIdx.y;
   const MdiView* vp = views + v;
@@ -310,7 +388,7 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   const uint32_t W0 = h->br_hi[0] - L0, W1 = h->br_hi[1] - L1;  // bracket widths (unsigned)
   const uint32_t sh0 = h->br_shift[0], sh1 = h->br_shift[1];
   for (int i = threadIdx.x; i < 2 * kBrBins; i += kStatsThreads) (&s_brhist[0][0])[i] = 0;
-  if (threadIdx.x == 0) { s_n = 0; s_min = 0xFFFFFFFFu; s_max = 0u; s_cnt = 0u; s_below[0] = 0; s_below[1] = 0; }
+  if (threadIdx.x == 0) { s_min = 0xFFFFFFFFu; s_max = 0u; s_cnt = 0u; s_below[0] = 0; s_below[1] = 0; }
   __syncthreads();
   const float* __restrict__ depth = vp->depth;
   const uint8_t* __restrict__ pmask = vp->mask;
@@ -321,22 +399,40 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
                       (!pmask || (reinterpret_cast<uintptr_t>(pmask) & 3) == 0);
   uint32_t kmin = 0xFFFFFFFFu, kmax = 0u, cnt = 0, below0 = 0, below1 = 0;
   uint32_t* cand = ws.cand + (int64_t)v * ws.c_cap;
+  const int lane = lane_id();
+  uint32_t* stage = s_stage[warp_id()];
+  uint32_t wcount = 0;  // keys in this warp's stage (warp-uniform)
+  const uint32_t lt = (1u << lane) - 1u;
 
-  auto feed = [&](float dv, uint32_t mbyte) {
+  // called by all 32 lanes together (pixels outside the image / population pass valid = false)
+  auto feed = [&](float dv, uint32_t mbyte, bool valid) {
     const float a = align_depth(dv, s, t);
-    if (!in_population(mbyte, a, flags)) return;
+    const bool pop = valid && in_population(mbyte, a, flags);
     const uint32_t key = float_to_key(a);
-    kmin = min(kmin, key); kmax = max(kmax, key); ++cnt;
-    below0 += key < L0 ? 1u : 0u;
-    below1 += key < L1 ? 1u : 0u;
-    const uint32_t o0 = key - L0, o1 = key - L1;
-    const bool in0 = o0 <= W0, in1 = o1 <= W1;
-    if (in0 || in1) {
+    bool c = false;
+    if (pop) {
+      kmin = min(kmin, key); kmax = max(kmax, key); ++cnt;
+      below0 += key < L0 ? 1u : 0u;
+      below1 += key < L1 ? 1u : 0u;
+      const uint32_t o0 = key - L0, o1 = key - L1;
+      const bool in0 = o0 <= W0, in1 = o1 <= W1;
       if (in0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
       if (in1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
-      const uint32_t slot = atomicAdd(&s_n, 1u);
-      s_stage[slot] = key;  // <= 4096 candidates per tile by construction
+      c = in0 || in1;
     }
+    const uint32_t m = __ballot_sync(0xffffffffu, c);
+    if (c) stage[wcount + __popc(m & lt)] = key;
+    wcount += __popc(m);
+  };
+  auto flush = [&]() {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(&h->n_cand, wcount);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    __syncwarp();
+    for (uint32_t i = lane; i < wcount; i += 32)
+      if ((int64_t)base + i < ws.c_cap) cand[base + i] = stage[i];
+    __syncwarp();
+    wcount = 0;
   };
 
   const int last_tile = min(first_tile + kStatsTilesPerCta, (int)vp->n_tiles);
@@ -355,35 +451,25 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
       }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        feed(d4[k].x, mk[k] & 0xffu); feed(d4[k].y, (mk[k] >> 8) & 0xffu);
-        feed(d4[k].z, (mk[k] >> 16) & 0xffu); feed(d4[k].w, mk[k] >> 24);
+        feed(d4[k].x, mk[k] & 0xffu, true); feed(d4[k].y, (mk[k] >> 8) & 0xffu, true);
+        feed(d4[k].z, (mk[k] >> 16) & 0xffu, true); feed(d4[k].w, mk[k] >> 24, true);
       }
     } else {
-      for (int k = threadIdx.x; k < MDI_TILE_PX; k += kStatsThreads) {
+      for (int k = threadIdx.x; k < MDI_TILE_PX; k += kStatsThreads) {  // uniform trip count
         const int64_t p = px0 + k;
-        if (p < HW) feed(__ldg(&depth[p]), pmask ? (uint32_t)__ldg(&pmask[p]) : 1u);
+        const bool in = p < HW;
+        feed(in ? __ldg(&depth[p]) : 0.f, in ? (pmask ? (uint32_t)__ldg(&pmask[p]) : 1u) : 0u, in);
       }
     }
-    __syncthreads();
-    // flush the stage: one reservation per tile, coalesced copy
-    const uint32_t n = s_n;
-    if (n) {
-      if (threadIdx.x == 0) s_base = atomicAdd(&h->n_cand, n);
-      __syncthreads();
-      const uint32_t base = s_base;
-      for (uint32_t i = threadIdx.x; i < n; i += kStatsThreads)
-        if ((int64_t)base + i < ws.c_cap) cand[base + i] = s_stage[i];
-      __syncthreads();
-      if (threadIdx.x == 0) s_n = 0;
-      __syncthreads();
-    }
+    if (wcount > (uint32_t)(kWarpStage - 512)) flush();  // a tile adds at most 512 keys per warp
   }
+  if (wcount) flush();
   kmin = __reduce_min_sync(0xffffffffu, kmin);
   kmax = __reduce_max_sync(0xffffffffu, kmax);
   cnt = __reduce_add_sync(0xffffffffu, cnt);
   below0 = __reduce_add_sync(0xffffffffu, below0);
   below1 = __reduce_add_sync(0xffffffffu, below1);
-  if (lane_id() == 0 && cnt) {
+  if (lane == 0 && cnt) {
     atomicMin(&s_min, kmin); atomicMax(&s_max, kmax); atomicAdd(&s_cnt, cnt);
     atomicAdd(&s_below[0], below0); atomicAdd(&s_below[1], below1);
   }
@@ -471,15 +557,24 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
         if (slot[j] == j && (i >> 1) == (j >> 1) && bin[i] == bin[j]) slot[j] = i;
     }
     const uint32_t* cand = ws.cand + (int64_t)v * ws.c_cap;
-    for (uint32_t i = tid; i < n_cand; i += kSelThreads) {
-      const uint32_t key = cand[i];
+    for (uint32_t base = 0; base < n_cand; base += 4 * kSelThreads) {
+      uint32_t kk[4];
 #pragma unroll
-      for (int j = 0; j < kTargets; ++j) {
-        if (slot[j] != j) continue;
-        const uint32_t o = key - L[j >> 1];
-        if (o <= Wd[j >> 1] && (o >> sft[j >> 1]) == bin[j]) {
-          const uint32_t at = atomicAdd(&s_len[j], 1u);
-          if (at < (uint32_t)kListCap) s_list[j][at] = key;
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t i = base + u * kSelThreads + tid;
+        kk[u] = i < n_cand ? cand[i] : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (base + u * kSelThreads + tid >= n_cand) continue;
+#pragma unroll
+        for (int j = 0; j < kTargets; ++j) {
+          if (slot[j] != j) continue;
+          const uint32_t o = kk[u] - L[j >> 1];
+          if (o <= Wd[j >> 1] && (o >> sft[j >> 1]) == bin[j]) {
+            const uint32_t at = atomicAdd(&s_len[j], 1u);
+            if (at < (uint32_t)kListCap) s_list[j][at] = kk[u];
+          }
         }
       }
     }
@@ -769,7 +864,7 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     const int64_t groups = max_tiles_per_view * (MDI_TILE_PX / kSampleGroup);
     stats_sample_kernel<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n_views), 256, 0, st>>>(
         views, scale_shift, status, pop, ws);
-    stats_bracket_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws);
+    stats_bracket_kernel<<<n_views, kBracketThreads, 0, st>>>(status, ws);
     stats_main_kernel<<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, pop, ws);
     stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
   } else {

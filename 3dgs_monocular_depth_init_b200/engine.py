@@ -416,7 +416,8 @@ class Engine:
             tail = meta[2 * V:].cpu()
             return int(tail[0]), bool(tail[1])
 
-        res.total, retry = mask_stage(L.STATS_EXACT if opt.stats_exact else 0)
+        # views under 64K pixels give the one-pass path too small a sample to bracket: exact select
+        res.total, retry = mask_stage(L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0)
         if retry:
             # a view's one-pass quantile brackets could not be certified (e.g. a constant depth
             # map): exact three-pass select for the flagged views, then mask + scan again
