@@ -78,9 +78,9 @@ _SIGNATURES = {
     "mdi_depth_range": (_INT, [_P, _INT, _I64, _P, _P, _INT, _P, _P, _P, _P, _P]),
     "mdi_grad_range": (_INT, [_P, _INT, _I64, _P, _P, _P, _P]),
     "mdi_factor_table": (_INT, [_INT, _P, _INT, _INT, _P, _P]),
-    "mdi_keep_mask": (_INT, [_P, _INT, _I64, _I64, _INT, _P, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),
+    "mdi_keep_mask": (_INT, [_P, _INT, _I64, _I64, _INT, _INT, _P, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),
     "mdi_scan_tiles": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P]),
-    "mdi_emit_points": (_INT, [_P, _INT, _I64, _P, _P, _P, _INT, _P, _P, _P]),
+    "mdi_emit_points": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _P]),
     "mdi_min_extents": (_INT, [_P, _I64, _P, _P, _P, _INT, _P, _P]),
 }
 

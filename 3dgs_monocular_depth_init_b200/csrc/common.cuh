@@ -50,6 +50,16 @@ __device__ __forceinline__ int find_view(const MdiView* __restrict__ views, int 
   return lo;
 }
 
+// tiles of equal-sized views: v = tile * n_views / total_tiles is right on the first probe;
+// anything else falls back to the binary search
+__device__ __forceinline__ int find_view_fast(const MdiView* __restrict__ views, int n_views,
+                                              int64_t tile, int64_t total_tiles) {
+  const int v = (int)((tile * n_views) / total_tiles);
+  const int64_t tb = __ldg(&views[v].tile_begin);
+  if (tile >= tb && tile < tb + __ldg(&views[v].n_tiles)) return v;
+  return find_view(views, n_views, tile);
+}
+
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 __device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
 

@@ -119,9 +119,15 @@ __device__ __forceinline__ void mark_kept(const MdiView* vp, int64_t q, uint8_t*
 }
 
 constexpr int kLatticeWarps = 8;
+constexpr int kBatch = 8;                              // lattice points per lane, loads in flight together
+constexpr int kChunk = 32 * kBatch;                    // lattice points per warp
+constexpr int kCtaPoints = kChunk * kLatticeWarps;     // lattice points per CTA
 
-// One warp per (view, stride f, lattice row i): pixels (f i, f j), j = lane, lane + 32, ...
-// grid = (ceil(max_rows / kLatticeWarps), n_strides, n_views)
+// The lattice of stride f of a view, (f i, f j) with i < ceil(H/f), j < ceil(W/f), is flattened
+// row-major and cut into chunks of 256 points, one warp each; lane l owns points chunk*256 + 32 u
+// + l (u < 8): the 8 depth loads are issued together, then the stride test, then the predicted-
+// mask loads of the survivors together, then their patch lookups together.
+// grid = (ceil(max lattice points / kCtaPoints), n_strides, n_views)
 __global__ void __launch_bounds__(kLatticeWarps * 32)
 keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
                     const int32_t* __restrict__ status, const float* __restrict__ lo_hi,
@@ -133,42 +139,96 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
   if (status && status[v] != MDI_STATUS_OK) return;
   const bool adaptive = prm.mode == MDI_SUBSAMPLE_ADAPTIVE;
   const int f = adaptive ? prm.fmin + (int)blockIdx.y : prm.static_factor;
-  const int i = blockIdx.x * kLatticeWarps + warp_id();
   const MdiView* vp = views + v;
   const int H = vp->H, W = vp->W;
-  const int64_t r64 = (int64_t)i * f;
-  if (r64 >= H) return;
-  const int r = (int)r64;
+  const uint32_t n_rows = (uint32_t)((H + f - 1) / f), n_cols = (uint32_t)((W + f - 1) / f);
+  const uint64_t n_pts = (uint64_t)n_rows * n_cols;
+  const uint64_t first = ((uint64_t)blockIdx.x * kLatticeWarps + warp_id()) * kChunk + lane_id();
+  if (first - lane_id() >= n_pts) return;
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
   const float* __restrict__ depth = vp->depth;
   // stride test: f(a) == f  <=>  a >= b_lo && !(a >= b_hi) when the view has a breakpoint table
   bool table = false;
-  float b_lo = 0.f, b_hi = 0.f, lo = 0.f, hi = 0.f;
+  float b_lo = 0.f, b_hi = 0.f;
   if (adaptive) {
     const float* row = factor_table ? factor_table + (int64_t)v * MDI_FACTOR_TABLE_STRIDE : nullptr;
     table = row && row[0] != 0.f;
     if (table) { b_lo = row[1 + (f - prm.fmin + 1)]; b_hi = row[1 + (f - prm.fmin)]; }
-    else { lo = lo_hi[2 * v]; hi = lo_hi[2 * v + 1]; }
   }
   const RestCtx ctx = make_ctx(vp, v, prm, patch_blocked, grad_range, s, t);
-  const int64_t row0 = (int64_t)r * W;
-  for (int64_t c64 = (int64_t)lane_id() * f; c64 < W; c64 += 32LL * f) {
-    const int c = (int)c64;
-    const int64_t q = row0 + c;
-    const float a = align_depth(__ldg(&depth[q]), s, t);
-    bool hit = true;
-    if (adaptive) {
+
+  int64_t q[kBatch];   // pixel index, -1 = outside
+  float av[kBatch];
+  bool ok[kBatch];
+#pragma unroll
+  for (int u = 0; u < kBatch; ++u) {
+    const uint64_t idx = first + 32u * u;
+    if (idx < n_pts) {
+      const uint32_t i = (uint32_t)(idx / n_cols), j = (uint32_t)(idx - (uint64_t)i * n_cols);
+      q[u] = (int64_t)i * f * W + (int64_t)j * f;
+    } else {
+      q[u] = -1;
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < kBatch; ++u) av[u] = q[u] >= 0 ? __ldg(&depth[q[u]]) : 0.f;
+  bool any = false;
+#pragma unroll
+  for (int u = 0; u < kBatch; ++u) {
+    const float a = align_depth(av[u], s, t);
+    av[u] = a;
+    bool hit = q[u] >= 0;
+    if (hit && adaptive) {
       if (table && a == a) {
         hit = (a >= b_lo) && !(a >= b_hi);
       } else {
         // exact arithmetic; a NaN stride (INT32_MIN) keeps index 0 only: visit it once, at fmin
-        const int fa = adaptive_factor(a, table ? lo_hi[2 * v] : lo, table ? lo_hi[2 * v + 1] : hi,
-                                       prm.fmin, prm.fmax);
-        hit = (fa == INT32_MIN) ? (r == 0 && c == 0 && f == prm.fmin) : (fa == f);
+        const int fa = adaptive_factor(a, lo_hi[2 * v], lo_hi[2 * v + 1], prm.fmin, prm.fmax);
+        hit = (fa == INT32_MIN) ? (q[u] == 0 && f == prm.fmin) : (fa == f);
       }
     }
-    if (hit && rest_ok(ctx, q, r, c, a)) mark_kept(vp, q, keep, bits, tile_counts);
+    if (prm.flags & MDI_KEEP_SENTINEL) hit = hit && (a != -42.0f);
+    if (prm.flags & MDI_KEEP_NONNEG) hit = hit && (a >= 0.f);
+    ok[u] = hit;
+    any = any || hit;
+  }
+  if (!any) return;
+  // predicted mask of the survivors
+  if ((prm.flags & MDI_KEEP_PRED_MASK) && ctx.pmask) {
+    uint8_t mb[kBatch];
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) mb[u] = ok[u] ? __ldg(&ctx.pmask[q[u]]) : 0;
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) ok[u] = ok[u] && mb[u] != 0;
+  }
+  // SfM-density patch lookup of the survivors
+  if (ctx.pb) {
+    uint8_t pv[kBatch];
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      pv[u] = 0;
+      if (ok[u]) {
+        const int r = (int)(q[u] / W), c = (int)(q[u] - (int64_t)r * W);
+        const int pr = r / ctx.patch_h, pc = c / ctx.patch_w;
+        if (pr < ctx.grid_h && pc < ctx.grid_w) pv[u] = __ldg(&ctx.pb[pr * ctx.grid_w + pc]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) ok[u] = ok[u] && pv[u] == 0;
+  }
+#pragma unroll
+  for (int u = 0; u < kBatch; ++u) {
+    if (!ok[u]) continue;
+    if (prm.flags & MDI_KEEP_GRAD) {
+      const int r = (int)(q[u] / W), c = (int)(q[u] - (int64_t)r * W);
+      const float gmin = grad_range[2 * v];
+      // (g - min) / ((max - min) + 1e-8)   (points_from_depth.py:210-211)
+      const float gden = fadd(fsub(grad_range[2 * v + 1], gmin), 1e-8f);
+      const float g = grad_at(depth, W, q[u], r, c, av[u], s, t);
+      if (!(fdiv(fsub(g, gmin), gden) <= prm.grad_thresh)) continue;
+    }
+    mark_kept(vp, q[u], keep, bits, tile_counts);
   }
 }
 
@@ -223,7 +283,8 @@ extern "C" int mdi_factor_table(int n_views, const float* lo_hi, int factor_min,
 }
 
 extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_tiles,
-                             int64_t total_px, int max_height, const float* scale_shift,
+                             int64_t total_px, int max_height, int max_width,
+                             const float* scale_shift,
                              const int32_t* status, const float* lo_hi, const float* grad_range,
                              const uint8_t* patch_blocked, const float* factor_table,
                              const MdiSubsampleConfig* cfg, uint8_t* keep, uint32_t* bits,
@@ -258,9 +319,11 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
   if (keep) MDI_CUDA(cudaMemsetAsync(keep, 0, (size_t)total_px, st), "mdi_keep_mask memset");
   MDI_CUDA(cudaMemsetAsync(bits, 0, (size_t)total_tiles * MDI_TILE_WORDS * 4, st), "mdi_keep_mask memset");
   MDI_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)total_tiles * 4, st), "mdi_keep_mask memset");
-  if (lattice && max_height > 0) {
-    const int max_rows = (max_height + min_stride - 1) / min_stride;
-    dim3 grid((max_rows + kLatticeWarps - 1) / kLatticeWarps, n_strides, n_views);
+  if (lattice && max_height > 0 && max_width > 0) {
+    const int64_t max_pts = (int64_t)((max_height + min_stride - 1) / min_stride) *
+                            ((max_width + min_stride - 1) / min_stride);
+    MDI_REQUIRE((max_pts + kCtaPoints - 1) / kCtaPoints < (1LL << 31), "mdi_keep_mask: lattice too large");
+    dim3 grid((unsigned)((max_pts + kCtaPoints - 1) / kCtaPoints), n_strides, n_views);
     keep_lattice_kernel<<<grid, kLatticeWarps * 32, 0, st>>>(
         views, scale_shift, status, lo_hi, grad_range, patch_blocked, factor_table, prm, keep, bits,
         tile_counts);

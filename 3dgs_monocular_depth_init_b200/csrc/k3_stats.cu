@@ -95,6 +95,14 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
   return x;
 }
 
+// order-preserving key without the NaN special case: NaNs land above key(+inf) / below key(-inf),
+// which is all the one-pass path needs (their presence makes the result NaN; stats_finish_kernel)
+__device__ __forceinline__ uint32_t fast_key(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);
+}
+constexpr uint32_t kKeyPosInf = 0xFF800000u, kKeyNegInf = 0x007FFFFFu;
+
 // ---- generic block-wide radix select over a key list -------------------------------------------
 // Among keys[0..n) with flo[j] <= key <= fhi[j], finds the key of (0-based, ascending) rank
 // rank[j], for j < kTargets.  11/11/10-bit passes, histogram updates aggregated per warp with
@@ -235,7 +243,7 @@ stats_sample_kernel(const MdiView* __restrict__ views, const float* __restrict__
     for (int k = 0; k < 8; ++k) {
       const float a = align_depth(dv[k], s, t);
       const uint32_t mb = ((k < 4 ? mlo : mhi) >> (8 * (k & 3))) & 0xffu;
-      keys[k] = float_to_key(a);
+      keys[k] = fast_key(a);
       if (((inside >> k) & 1u) && in_population(mb, a, flags)) valid |= 1u << k;
     }
   }
@@ -372,9 +380,10 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
 
 constexpr int kWarpStage = 768;  // keys staged per warp; flushed once fewer than 512 slots remain
 
+template <bool kUseMask, bool kSentinel>
 __global__ void __launch_bounds__(kStatsThreads)
 stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
-                  const int32_t* __restrict__ status, int flags, StatsWs ws) {
+                  const int32_t* __restrict__ status, StatsWs ws) {
   __shared__ uint32_t s_stage[kStatsThreads / 32][kWarpStage];
   __shared__ uint32_t s_brhist[2][kBrBins];
   __shared__ uint32_t s_min, s_max, s_cnt, s_below[2];
@@ -391,7 +400,7 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   if (threadIdx.x == 0) { s_min = 0xFFFFFFFFu; s_max = 0u; s_cnt = 0u; s_below[0] = 0; s_below[1] = 0; }
   __syncthreads();
   const float* __restrict__ depth = vp->depth;
-  const uint8_t* __restrict__ pmask = vp->mask;
+  const uint8_t* __restrict__ pmask = kUseMask ? vp->mask : nullptr;
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
   const int64_t HW = (int64_t)vp->H * vp->W;
@@ -404,22 +413,21 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   uint32_t wcount = 0;  // keys in this warp's stage (warp-uniform)
   const uint32_t lt = (1u << lane) - 1u;
 
-  // called by all 32 lanes together (pixels outside the image / population pass valid = false)
-  auto feed = [&](float dv, uint32_t mbyte, bool valid) {
+  // straight-line per-pixel work, called by all 32 lanes together
+  auto feed = [&](float dv, bool pop) {
     const float a = align_depth(dv, s, t);
-    const bool pop = valid && in_population(mbyte, a, flags);
-    const uint32_t key = float_to_key(a);
-    bool c = false;
-    if (pop) {
-      kmin = min(kmin, key); kmax = max(kmax, key); ++cnt;
-      below0 += key < L0 ? 1u : 0u;
-      below1 += key < L1 ? 1u : 0u;
-      const uint32_t o0 = key - L0, o1 = key - L1;
-      const bool in0 = o0 <= W0, in1 = o1 <= W1;
-      if (in0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
-      if (in1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
-      c = in0 || in1;
-    }
+    if (kSentinel) pop = pop && (a != -42.0f);
+    const uint32_t key = fast_key(a);
+    kmin = min(kmin, pop ? key : 0xFFFFFFFFu);
+    kmax = max(kmax, pop ? key : 0u);
+    cnt += pop ? 1u : 0u;
+    below0 += (pop && key < L0) ? 1u : 0u;
+    below1 += (pop && key < L1) ? 1u : 0u;
+    const uint32_t o0 = key - L0, o1 = key - L1;
+    const bool in0 = pop && o0 <= W0, in1 = pop && o1 <= W1;
+    if (in0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
+    if (in1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
+    const bool c = in0 || in1;
     const uint32_t m = __ballot_sync(0xffffffffu, c);
     if (c) stage[wcount + __popc(m & lt)] = key;
     wcount += __popc(m);
@@ -451,14 +459,14 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
       }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        feed(d4[k].x, mk[k] & 0xffu, true); feed(d4[k].y, (mk[k] >> 8) & 0xffu, true);
-        feed(d4[k].z, (mk[k] >> 16) & 0xffu, true); feed(d4[k].w, mk[k] >> 24, true);
+        feed(d4[k].x, (mk[k] & 0xffu) != 0); feed(d4[k].y, (mk[k] & 0xff00u) != 0);
+        feed(d4[k].z, (mk[k] & 0xff0000u) != 0); feed(d4[k].w, (mk[k] & 0xff000000u) != 0);
       }
     } else {
       for (int k = threadIdx.x; k < MDI_TILE_PX; k += kStatsThreads) {  // uniform trip count
         const int64_t p = px0 + k;
         const bool in = p < HW;
-        feed(in ? __ldg(&depth[p]) : 0.f, in ? (pmask ? (uint32_t)__ldg(&pmask[p]) : 1u) : 0u, in);
+        feed(in ? __ldg(&depth[p]) : 0.f, in && (pmask ? __ldg(&pmask[p]) != 0 : true));
       }
     }
     if (wcount > (uint32_t)(kWarpStage - 512)) flush();  // a tile adds at most 512 keys per warp
@@ -522,7 +530,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
   const QuantileRank r1 = quantile_rank(0.25f, (int64_t)n);
   const QuantileRank r3 = quantile_rank(0.75f, (int64_t)n);
   const uint32_t n_cand = h->n_cand;
-  const bool has_nan = h->max_key == 0xFFFFFFFFu;
+  const bool has_nan = h->max_key > kKeyPosInf || h->min_key < kKeyNegInf;
   const uint32_t L[2] = {h->br_lo[0], h->br_lo[1]};
   const uint32_t Wd[2] = {h->br_hi[0] - L[0], h->br_hi[1] - L[1]};
   const uint32_t sft[2] = {h->br_shift[0], h->br_shift[1]};
@@ -605,7 +613,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
     } else {
       float val[kTargets];
       for (int j = 0; j < kTargets; ++j) val[j] = key_to_float(s_out[j]);
-      write_range(v, val, r1.w, r3.w, h->min_key, h->max_key, lo_hi, quantiles);
+      write_range(v, val, r1.w, r3.w, h->min_key, has_nan ? 0xFFFFFFFFu : h->max_key, lo_hi, quantiles);
     }
   }
 }
@@ -865,7 +873,11 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     stats_sample_kernel<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n_views), 256, 0, st>>>(
         views, scale_shift, status, pop, ws);
     stats_bracket_kernel<<<n_views, kBracketThreads, 0, st>>>(status, ws);
-    stats_main_kernel<<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, pop, ws);
+    const bool um = pop & MDI_KEEP_PRED_MASK, se = pop & MDI_KEEP_SENTINEL;
+    if (um && se) stats_main_kernel<true, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
+    else if (um) stats_main_kernel<true, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
+    else if (se) stats_main_kernel<false, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
+    else stats_main_kernel<false, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
   } else {
     static bool attr_done = false;

@@ -4,49 +4,78 @@
 
 namespace mdi {
 
-constexpr int kScanThreads = 1024;
+constexpr int kScanThreads = 256;
 
-// Single-CTA exclusive scan over all tiles in global (view-major, row-major) order.  The tile
-// count is tiny next to the pixel traffic (<= ~1M ints for 500 4K views).
+// Level 1: one CTA per view, exclusive scan of the view's tile counts -> offsets WITHIN the view
+// and the view's point count.
 __global__ void __launch_bounds__(kScanThreads)
-scan_tiles_kernel(const MdiView* __restrict__ views, int n_views, int64_t total_tiles,
-                  const int32_t* __restrict__ tile_counts, int64_t* __restrict__ tile_offsets,
-                  int64_t* __restrict__ view_counts, int64_t* __restrict__ view_offsets,
-                  int64_t* __restrict__ total) {
+scan_view_tiles_kernel(const MdiView* __restrict__ views, const int32_t* __restrict__ tile_counts,
+                       int64_t* __restrict__ tile_offsets, int64_t* __restrict__ view_counts) {
   __shared__ int scan_smem[33];
   __shared__ long long s_base;
+  const int v = blockIdx.x;
+  const int64_t tb = views[v].tile_begin;
+  const int n = views[v].n_tiles;
   if (threadIdx.x == 0) s_base = 0;
   __syncthreads();
-  // each thread owns 4 consecutive tiles per step so the loads are 128-bit
-  for (int64_t start = 0; start < total_tiles; start += (int64_t)kScanThreads * 4) {
-    const int64_t i0 = start + (int64_t)threadIdx.x * 4;
+  for (int start = 0; start < n; start += kScanThreads * 4) {
+    const int i0 = start + threadIdx.x * 4;
     int c[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) c[k] = (i0 + k < total_tiles) ? tile_counts[i0 + k] : 0;
-    const int mine = c[0] + c[1] + c[2] + c[3];
+    for (int k = 0; k < 4; ++k) c[k] = (i0 + k < n) ? tile_counts[tb + i0 + k] : 0;
     int tot;
-    const int excl = block_excl_scan(mine, scan_smem, &tot);
+    const int excl = block_excl_scan(c[0] + c[1] + c[2] + c[3], scan_smem, &tot);
     long long o = s_base + excl;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      if (i0 + k < total_tiles) tile_offsets[i0 + k] = o;
+      if (i0 + k < n) tile_offsets[tb + i0 + k] = o;
       o += c[k];
     }
     __syncthreads();
     if (threadIdx.x == 0) s_base += tot;
     __syncthreads();
   }
-  if (threadIdx.x == 0 && total) *total = s_base;
+  if (threadIdx.x == 0) view_counts[v] = s_base;
+}
+
+// Level 2: one CTA, exclusive scan of the per-view counts in view order -> view offsets, total.
+__global__ void __launch_bounds__(1024)
+scan_views_kernel(int n_views, const int64_t* __restrict__ view_counts,
+                  int64_t* __restrict__ view_offsets, int64_t* __restrict__ total) {
+  __shared__ long long s_warp[32];
+  __shared__ long long s_base;
+  if (threadIdx.x == 0) s_base = 0;
   __syncthreads();
-  const long long grand = s_base;
-  for (int v = threadIdx.x; v < n_views; v += blockDim.x) {
-    const int64_t tb = views[v].tile_begin;
-    const int64_t te = tb + views[v].n_tiles;
-    const long long b = (tb < total_tiles) ? tile_offsets[tb] : grand;
-    const long long e = (te < total_tiles) ? tile_offsets[te] : grand;
-    if (view_offsets) view_offsets[v] = b;
-    if (view_counts) view_counts[v] = e - b;
+  const int lane = lane_id(), warp = warp_id();
+  for (int start = 0; start < n_views; start += 1024) {
+    const int i = start + threadIdx.x;
+    const long long c = i < n_views ? view_counts[i] : 0;
+    long long incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const long long y = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += y;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      const long long w = s_warp[lane];
+      long long wi = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const long long y = __shfl_up_sync(0xffffffffu, wi, d);
+        if (lane >= d) wi += y;
+      }
+      s_warp[lane] = wi - w;
+    }
+    __syncthreads();
+    const long long excl = s_base + s_warp[warp] + incl - c;
+    if (i < n_views && view_offsets) view_offsets[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_base = excl + c;
+    __syncthreads();
   }
+  if (threadIdx.x == 0 && total) *total = s_base;
 }
 
 constexpr int kEmitThreads = MDI_TILE_WORDS;  // one thread per bit word
@@ -58,15 +87,15 @@ template <int IMAGE_KIND>
 __global__ void __launch_bounds__(kEmitThreads)
 emit_points_kernel(const MdiView* __restrict__ views, int n_views,
                    const float* __restrict__ scale_shift, const uint32_t* __restrict__ bits,
-                   const int64_t* __restrict__ tile_offsets, float* __restrict__ xyz,
-                   float* __restrict__ rgb) {
+                   const int64_t* __restrict__ tile_offsets, const int64_t* __restrict__ view_offsets,
+                   int64_t total_tiles, float* __restrict__ xyz, float* __restrict__ rgb) {
   __shared__ int scan_smem[33];
   const int64_t tile = blockIdx.x;
   uint32_t word = bits[tile * MDI_TILE_WORDS + threadIdx.x];
   int tot;
   const int excl = block_excl_scan(__popc(word), scan_smem, &tot);
   if (tot == 0) return;
-  const int v = find_view(views, n_views, tile);
+  const int v = find_view_fast(views, n_views, tile, total_tiles);
   const MdiView& vw = views[v];
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
@@ -74,7 +103,7 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
   const float* depth = vw.depth;
   const float* Ki = vw.Kinv;
   const float* M = vw.c2w;
-  int64_t out = tile_offsets[tile] + excl;
+  int64_t out = view_offsets[v] + tile_offsets[tile] + excl;
   const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX + (int64_t)threadIdx.x * 32;
   while (word) {
     const int b = __ffs(word) - 1;
@@ -119,35 +148,38 @@ extern "C" int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_t
                               int64_t* view_counts, int64_t* view_offsets, int64_t* total,
                               void* stream) {
   MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_scan_tiles: negative size");
-  MDI_REQUIRE(views && tile_counts && tile_offsets, "mdi_scan_tiles: null pointer");
-  mdi::scan_tiles_kernel<<<1, mdi::kScanThreads, 0, (cudaStream_t)stream>>>(
-      views, n_views, total_tiles, tile_counts, tile_offsets, view_counts, view_offsets, total);
+  MDI_REQUIRE(views && tile_counts && tile_offsets && view_counts && view_offsets,
+              "mdi_scan_tiles: null pointer");
+  if (n_views > 0)
+    mdi::scan_view_tiles_kernel<<<n_views, mdi::kScanThreads, 0, (cudaStream_t)stream>>>(
+        views, tile_counts, tile_offsets, view_counts);
+  mdi::scan_views_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_views, view_counts, view_offsets, total);
   MDI_CHECK_LAUNCH("mdi_scan_tiles");
   return MDI_OK;
 }
 
 extern "C" int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
                                const float* scale_shift, const uint32_t* bits,
-                               const int64_t* tile_offsets, int image_kind, float* xyz, float* rgb,
-                               void* stream) {
+                               const int64_t* tile_offsets, const int64_t* view_offsets,
+                               int image_kind, float* xyz, float* rgb, void* stream) {
   MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_emit_points: negative size");
   if (n_views == 0 || total_tiles == 0) return MDI_OK;
-  MDI_REQUIRE(views && bits && tile_offsets, "mdi_emit_points: null pointer");
+  MDI_REQUIRE(views && bits && tile_offsets && view_offsets, "mdi_emit_points: null pointer");
   MDI_REQUIRE(total_tiles < (1LL << 31), "mdi_emit_points: too many tiles");
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)total_tiles;
   switch (image_kind) {
     case MDI_IMAGE_F32_UNIT:
       mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitThreads, 0, st>>>(
-          views, n_views, scale_shift, bits, tile_offsets, xyz, rgb);
+          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     case MDI_IMAGE_F32_255:
       mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitThreads, 0, st>>>(
-          views, n_views, scale_shift, bits, tile_offsets, xyz, rgb);
+          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     case MDI_IMAGE_U8:
       mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitThreads, 0, st>>>(
-          views, n_views, scale_shift, bits, tile_offsets, xyz, rgb);
+          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     default:
       mdi::set_error("mdi_emit_points: unknown image kind %d", image_kind);

@@ -141,7 +141,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
-    "mdi_scan_tiles": 1, "mdi_emit_points": 1, "mdi_min_extents": 1,
+    "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_min_extents": 1,
 }
 
 
@@ -405,7 +405,7 @@ class Engine:
                                             meta[2 * V + 1:].data_ptr(), st), "mdi_depth_range")
                 L.check(lib.mdi_factor_table(V, res.lo_hi.data_ptr(), int(opt.factor_min), int(opt.factor_max),
                                              ftab.data_ptr(), st), "mdi_factor_table")
-            L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), ssp,
+            L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), int(desc["W"].max()), ssp,
                                       res.status.data_ptr(), L.ptr(res.lo_hi), L.ptr(res.grad_range),
                                       L.ptr(res.patch_blocked), L.ptr(ftab), C.byref(scfg), L.ptr(res.keep),
                                       bits.data_ptr(), tile_counts.data_ptr(), st), "mdi_keep_mask")
@@ -435,7 +435,7 @@ class Engine:
             res.rgb = torch.empty((N, 3), dtype=f32, device=self.device)
         if N:
             L.check(lib.mdi_emit_points(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
-                                        int(vin.image_kind), L.ptr(res.xyz), L.ptr(res.rgb), st),
+                                        res.view_offsets.data_ptr(), int(vin.image_kind), L.ptr(res.xyz), L.ptr(res.rgb), st),
                     "mdi_emit_points")
         return res
 

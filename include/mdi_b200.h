@@ -225,21 +225,23 @@ int mdi_factor_table(int n_views, const float* lo_hi, int factor_min, int factor
 /*
  * a5-a10 (predicate): composes the keep mask of every pixel.
  *   factor_table: output of mdi_factor_table for the same lo_hi / factor range, or NULL.
- *   total_px = sum H*W (size of keep), max_height = max H: the outputs are zero-filled and the
- *   stride lattices (f i, f j) of the configured strides are walked, one warp per lattice row.
+ *   total_px = sum H*W (size of keep), max_height / max_width = max H / W: the outputs are zero-filled and the
+ *   stride lattices (f i, f j) of the configured strides are walked, 256 points per warp.
  *   keep      uint8 [sum H*W] at px_begin (may be NULL), bits uint32 [total_tiles*128] (bit i of
  *   word w of tile t = pixel t*4096 + 32*w + i), tile_counts int32 [total_tiles].
  */
 int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_tiles, int64_t total_px,
-                  int max_height, const float* scale_shift, const int32_t* status, const float* lo_hi,
+                  int max_height, int max_width, const float* scale_shift, const int32_t* status, const float* lo_hi,
                   const float* grad_range, const uint8_t* patch_blocked,
                   const float* factor_table, const MdiSubsampleConfig* cfg, uint8_t* keep,
                   uint32_t* bits,
                   int32_t* tile_counts, void* stream);
 
 /*
- * exclusive scan of tile_counts in global (view-major) order -> tile_offsets int64
- * [total_tiles]; per-view counts / offsets int64 [V]; total int64 [1].
+ * compaction offsets in (view-major, row-major) order: tile_offsets int64 [total_tiles] = exclusive
+ * scan of tile_counts WITHIN each view; view_counts / view_offsets int64 [V] = points per view and
+ * their exclusive scan over views; total int64 [1].  A kept pixel's output slot is
+ * view_offsets[v] + tile_offsets[tile] + its rank inside the tile.
  */
 int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_tiles,
                    const int32_t* tile_counts, int64_t* tile_offsets, int64_t* view_counts,
@@ -247,11 +249,12 @@ int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_tiles,
 
 /*
  * a10 + a11: for every kept pixel in row-major order: unproject to world space and gather RGB.
- *   xyz float32 [N,3], rgb float32 [N,3] (either may be NULL), written at tile_offsets.
+ *   xyz float32 [N,3], rgb float32 [N,3] (either may be NULL), written at the slots above.
  */
 int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
                     const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
-                    int image_kind, float* xyz, float* rgb, void* stream);
+                    const int64_t* view_offsets, int image_kind, float* xyz, float* rgb,
+                    void* stream);
 
 /*
  * a13: minimal Gaussian extent per point over all cameras that see it (else -1).
