@@ -16,6 +16,8 @@ namespace mdi {
 
 constexpr int kRansacWarps = 16;
 constexpr int kRansacThreads = kRansacWarps * 32;
+constexpr int kHyp = 4;                               // hypotheses scored together by one warp
+constexpr int kRound = kRansacWarps * kHyp;           // hypotheses per round
 constexpr int kMaxSample = 8;
 
 __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
@@ -45,9 +47,9 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
               int32_t* __restrict__ n_inliers) {
   extern __shared__ __align__(16) float s_pts[];  // d[smem_points] then g[smem_points]
   __shared__ __align__(8) unsigned long long s_bar;
-  __shared__ double s_loss_sample[kRansacWarps], s_loss_lo[kRansacWarps];
-  __shared__ float s_hlo[kRansacWarps][2];
-  __shared__ int s_ninl_lo[kRansacWarps];
+  __shared__ double s_loss_sample[kRound], s_loss_lo[kRound];
+  __shared__ float s_hlo[kRound][2];
+  __shared__ int s_ninl_lo[kRound];
   __shared__ double s_best_sample, s_best_lo;
   __shared__ float s_hbest[2];
   __shared__ int s_have, s_done, s_last_it, s_ninl;
@@ -59,6 +61,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
   const bool skip = status && status[v] != MDI_STATUS_OK;
   const float thr = cfg.inlier_threshold;
   const int ss = cfg.sample_size;
+  const bool msac_loss = cfg.loss_kind == MDI_LOSS_MSAC;
   const float* dg = d_all + base;
   const float* gg = g_all + base;
 
@@ -116,14 +119,13 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
   __syncthreads();
 
   const int n_samp = ss < n ? ss : n;
-  for (int round0 = 0; round0 < cfg.max_iters; round0 += kRansacWarps) {
-    const int it = round0 + warp;
-    const bool active = it < cfg.max_iters;
+  for (int round0 = 0; round0 < cfg.max_iters; round0 += kRound) {
+    const int it0 = round0 + warp * kHyp;   // this warp's hypotheses: it0 .. it0 + kHyp - 1
     const double cutoff = s_best_sample;
-    float hs0 = 0.f, hs1 = 0.f, hl0 = 0.f, hl1 = 0.f;
-    double loss_s = INFINITY;
-    // ---- phase A: sample fit, sample loss, inlier normal equations ------------------------
-    if (active) {
+    // ---- sample fits: lane k < kHyp fits hypothesis it0 + k, then broadcasts it --------------
+    float hs0 = 0.f, hs1 = 0.f;
+    if (lane < kHyp && it0 + lane < cfg.max_iters) {
+      const int it = it0 + lane;
       Sums sm = {0, 0, 0, 0, 0};
       int chosen[kMaxSample];
       for (int k = 0; k < n_samp; ++k) {
@@ -149,46 +151,95 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
         }
       }
       solve(sm, &hs0, &hs1);
-      Sums in = {0, 0, 0, 0, 0};
-      int n_out = 0;
-      double msac = 0.0;
+    }
+    float h0[kHyp], h1[kHyp];
+    bool act[kHyp];
+#pragma unroll
+    for (int k = 0; k < kHyp; ++k) {
+      h0[k] = __shfl_sync(0xffffffffu, hs0, k);
+      h1[k] = __shfl_sync(0xffffffffu, hs1, k);
+      act[k] = it0 + k < cfg.max_iters;
+    }
+    // ---- phase A: sample loss and inlier normal equations of the kHyp hypotheses ---------------
+    Sums in[kHyp];
+    int n_out[kHyp];
+    double msac[kHyp];
+#pragma unroll
+    for (int k = 0; k < kHyp; ++k) { in[k] = {0, 0, 0, 0, 0}; n_out[k] = 0; msac[k] = 0.0; }
+    if (act[0]) {
       for (int i = lane; i < n; i += 32) {
         const float dv = dp[i], gv = gp[i];
-        const float r = residual_sq(hs0, hs1, dv, gv);
-        if (r < thr) {
-          const double dd = (double)dv, gd = (double)gv;
-          in.dd += dd * dd; in.d += dd; in.n += 1.0; in.dg += dd * gd; in.g += gd;
+        const double dd = (double)dv, gd = (double)gv;
+        const double ddd = dd * dd, ddg = dd * gd;
+#pragma unroll
+        for (int k = 0; k < kHyp; ++k) {
+          const float r = residual_sq(h0[k], h1[k], dv, gv);
+          if (r < thr) { in[k].dd += ddd; in[k].d += dd; in[k].n += 1.0; in[k].dg += ddg; in[k].g += gd; }
+          if (r >= thr) ++n_out[k];
+          if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
         }
-        if (r >= thr) ++n_out;
-        if (cfg.loss_kind == MDI_LOSS_MSAC) msac += (r != r) ? (double)NAN : (double)fminf(r, thr);
       }
-      in.dd = warp_sum_f64(in.dd); in.d = warp_sum_f64(in.d); in.n = warp_sum_f64(in.n);
-      in.dg = warp_sum_f64(in.dg); in.g = warp_sum_f64(in.g);
-      if (cfg.loss_kind == MDI_LOSS_MSAC) loss_s = (double)(float)warp_sum_f64(msac);
-      else loss_s = (double)warp_sum_i32(n_out);
-      solve(in, &hl0, &hl1);
-      if (lane == 0) { s_loss_sample[warp] = loss_s; s_hlo[warp][0] = hl0; s_hlo[warp][1] = hl1; }
     }
-    // ---- phase B: local-optimisation loss for candidates -------------------------------------
-    if (active && loss_s < cutoff) {
-      int n_out = 0, n_in = 0;
-      double msac = 0.0;
-      for (int i = lane; i < n; i += 32) {
-        const float r = residual_sq(hl0, hl1, dp[i], gp[i]);
-        if (r < thr) ++n_in;
-        if (r >= thr) ++n_out;
-        if (cfg.loss_kind == MDI_LOSS_MSAC) msac += (r != r) ? (double)NAN : (double)fminf(r, thr);
+    float hl0 = 0.f, hl1 = 0.f;   // lane k keeps the local-optimisation fit of hypothesis k
+    double loss_s_mine = INFINITY;
+#pragma unroll
+    for (int k = 0; k < kHyp; ++k) {
+      Sums t;
+      t.dd = warp_sum_f64(in[k].dd); t.d = warp_sum_f64(in[k].d); t.n = warp_sum_f64(in[k].n);
+      t.dg = warp_sum_f64(in[k].dg); t.g = warp_sum_f64(in[k].g);
+      double ls;
+      if (msac_loss) ls = (double)(float)warp_sum_f64(msac[k]);
+      else ls = (double)warp_sum_i32(n_out[k]);
+      if (lane == k) {
+        loss_s_mine = act[k] ? ls : INFINITY;
+        if (act[k]) solve(t, &hl0, &hl1);
       }
-      n_in = warp_sum_i32(n_in);
-      double loss_lo;
-      if (cfg.loss_kind == MDI_LOSS_MSAC) loss_lo = (double)(float)warp_sum_f64(msac);
-      else loss_lo = (double)warp_sum_i32(n_out);
-      if (lane == 0) { s_loss_lo[warp] = loss_lo; s_ninl_lo[warp] = n_in; }
+    }
+    if (lane < kHyp && it0 + lane < cfg.max_iters) {
+      s_loss_sample[warp * kHyp + lane] = loss_s_mine;
+      s_hlo[warp * kHyp + lane][0] = hl0; s_hlo[warp * kHyp + lane][1] = hl1;
+    }
+    // ---- phase B: local-optimisation loss of the candidates --------------------------------------
+    bool candk[kHyp];
+    bool any_cand = false;
+#pragma unroll
+    for (int k = 0; k < kHyp; ++k) {
+      h0[k] = __shfl_sync(0xffffffffu, hl0, k);
+      h1[k] = __shfl_sync(0xffffffffu, hl1, k);
+      const double ls = __shfl_sync(0xffffffffu, loss_s_mine, k);
+      candk[k] = act[k] && ls < cutoff;
+      any_cand = any_cand || candk[k];
+      n_out[k] = 0; msac[k] = 0.0;
+    }
+    int n_in[kHyp] = {0, 0, 0, 0};
+    if (any_cand) {
+      for (int i = lane; i < n; i += 32) {
+        const float dv = dp[i], gv = gp[i];
+#pragma unroll
+        for (int k = 0; k < kHyp; ++k) {
+          if (!candk[k]) continue;  // warp-uniform
+          const float r = residual_sq(h0[k], h1[k], dv, gv);
+          if (r < thr) ++n_in[k];
+          if (r >= thr) ++n_out[k];
+          if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kHyp; ++k) {
+        if (!candk[k]) continue;
+        const int ni = warp_sum_i32(n_in[k]);
+        double loss_lo;
+        if (msac_loss) loss_lo = (double)(float)warp_sum_f64(msac[k]);
+        else loss_lo = (double)warp_sum_i32(n_out[k]);
+        if (lane == 0) { s_loss_lo[warp * kHyp + k] = loss_lo; s_ninl_lo[warp * kHyp + k] = ni; }
+      }
     }
     __syncthreads();
     // ---- replay of the sequential state machine (ransacs.py:141-162) --------------------------
     if (threadIdx.x == 0) {
-      for (int w = 0; w < kRansacWarps; ++w) {
+      // the stopping bound only changes when the best model does
+      double req = s_have ? required_samples((int64_t)s_ninl, (int64_t)n, ss, cfg.confidence) : 0.0;
+      for (int w = 0; w < kRound; ++w) {
         const int itw = round0 + w;
         if (itw >= cfg.max_iters) break;
         if (s_loss_sample[w] < s_best_sample) {
@@ -198,10 +249,10 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
             s_best_sample = s_loss_sample[w];
             s_ninl = s_ninl_lo[w];
             s_have = 1;
+            req = required_samples((int64_t)s_ninl, (int64_t)n, ss, cfg.confidence);
           }
         }
-        if (s_have && itw >= cfg.min_iters &&
-            required_samples((int64_t)s_ninl, (int64_t)n, ss, cfg.confidence) <= (double)itw) {
+        if (s_have && itw >= cfg.min_iters && req <= (double)itw) {
           s_done = 1; s_last_it = itw;
           break;
         }
@@ -242,7 +293,7 @@ extern "C" int mdi_ransac(const MdiView* views, int n_views, const float* d, con
   const size_t smem = (size_t)pts * 8;
   if (smem <= 200 * 1024) {
     static size_t attr_set = 0;
-    if (smem > 48 * 1024 && smem > attr_set) {
+    if (smem > 32 * 1024 && smem > attr_set) {  // static + dynamic may not exceed 48 KB by default
       MDI_CUDA(cudaFuncSetAttribute(ransac_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     200 * 1024), "mdi_ransac attr");
       attr_set = 200 * 1024;

@@ -187,6 +187,7 @@ class Engine:
         self.device = torch.device("cuda", idx)
         L.check(self.lib.mdi_check_device(idx), "mdi_check_device")
         self._ws: dict[str, torch.Tensor] = {}
+        self._pin: dict[str, torch.Tensor] = {}
         self.launches = 0   # kernels launched through this engine (bench `gpu_launches`)
         self.profile = False
         self.events: list = []  # (entry point, start event, end event) when profile is on
@@ -240,7 +241,12 @@ class Engine:
         tile_begin = np.zeros(V + 1, dtype=np.int64)
         np.cumsum(n_tiles, out=tile_begin[1:])
         desc["px_begin"], desc["tile_begin"], desc["n_tiles"] = px_begin[:-1], tile_begin[:-1], n_tiles
-        if opt.use_patch_mask and V:
+        if opt.use_patch_mask and V and (Hs == Hs[0]).all() and (Ws == Ws[0]).all():
+            g = patch_geometry(int(Hs[0]), int(Ws[0]), opt.num_patches_small_axis)
+            if g[2] * g[3] > L.PATCH_STRIDE:
+                raise L.MdiError(f"patch grid {g[2]}x{g[3]} exceeds {L.PATCH_STRIDE} patches")
+            desc["patch_h"], desc["patch_w"], desc["grid_h"], desc["grid_w"] = g
+        elif opt.use_patch_mask and V:
             geo = {}
             pg = np.empty((V, 4), dtype=np.int32)
             for i, key in enumerate(zip(Hs.tolist(), Ws.tolist())):
@@ -255,9 +261,22 @@ class Engine:
             desc["patch_h"] = desc["patch_w"] = 1
         return desc, px_begin, tile_begin, sfm_begin
 
-    def _upload(self, name: str, host: torch.Tensor) -> torch.Tensor:
-        dev = self._buf(name, host.numel(), host.dtype)
-        dev.copy_(host.reshape(-1), non_blocking=True)
+    def _upload(self, name: str, parts) -> torch.Tensor:
+        """One H2D copy of the concatenated byte images of `parts` (numpy arrays) through a
+        persistent pinned staging buffer.  Safe to reuse across calls: every run() ends with a
+        stream synchronisation (the read-back of the point count)."""
+        sizes = [int(a.nbytes) for a in parts]
+        n = sum(sizes)
+        pin = self._pin.get(name)
+        if pin is None or pin.numel() < n:
+            pin = self._pin[name] = torch.empty(max(int(n * 1.25), 256), dtype=torch.uint8, pin_memory=True)
+        host = pin.numpy()
+        o = 0
+        for a, sz in zip(parts, sizes):
+            host[o:o + sz] = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
+            o += sz
+        dev = self._buf(name, n, torch.uint8)
+        dev.copy_(pin[:n], non_blocking=True)
         return dev
 
     # ---- the pipeline -------------------------------------------------------------------------
@@ -271,29 +290,24 @@ class Engine:
         res = RunResult(n_views=V, px_begin=px_begin, sfm_begin=sfm_begin)
         if V == 0:
             return res
-        views = self._upload("views", torch.from_numpy(desc.view(np.uint8).reshape(-1)))
-        vp = views.data_ptr()
-
-        # a1: cameras
-        Kf = vin.K.detach().cpu().float().contiguous()
-        c2wf = vin.c2w.detach().cpu().float().contiguous()
-        kn = Kf.numpy()
+        # a1: cameras.  One upload: [descriptors][K][cam2world][inv(K) unless pinhole]
+        kn = np.ascontiguousarray(vin.K.detach().cpu().numpy(), dtype=np.float32).reshape(V, 3, 3)
+        c2wn = np.ascontiguousarray(vin.c2w.detach().cpu().numpy(), dtype=np.float32).reshape(V, 4, 4)
         pinhole = bool(((kn[:, 0, 1] == 0) & (kn[:, 1, 0] == 0) & (kn[:, 2, 0] == 0) & (kn[:, 2, 1] == 0)
                         & (kn[:, 2, 2] == 1)).all())
         # zero-skew pinhole intrinsics: inv(K) in closed form on the device (bit-identical to
         # torch.linalg.inv); anything else: batched LU inverse on the host like the reference
-        parts = [Kf.reshape(-1), c2wf.reshape(-1)]
+        if vin.P_override is not None:  # stage-wise parity / project_and_filter_sfm_pts: P as given
+            desc["P"] = vin.P_override.reshape(V, 12).numpy()
+        parts = [desc.view(np.uint8).reshape(-1), kn, c2wn]
         if not pinhole:
-            parts.append(torch.linalg.inv(Kf).reshape(-1))
-        cam = self._upload("cams", torch.cat(parts))
-        kp = cam.data_ptr()
+            parts.append(torch.linalg.inv(torch.from_numpy(kn)).numpy())
+        blob = self._upload("views", parts)
+        vp = blob.data_ptr()
+        kp = vp + desc.nbytes
         c2wp = kp + 4 * 9 * V
         kinvp = None if pinhole else c2wp + 4 * 16 * V
         res.P = torch.empty((V, 3, 4), dtype=torch.float32, device=self.device)
-        if vin.P_override is not None:  # stage-wise parity / project_and_filter_sfm_pts: P as given
-            desc["P"] = vin.P_override.reshape(V, 12).numpy()
-            views = self._upload("views", torch.from_numpy(desc.view(np.uint8).reshape(-1)))
-            vp = views.data_ptr()
         L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(),
                                       0 if vin.P_override is None else 1, st), "mdi_setup_cameras")
 
