@@ -69,6 +69,8 @@ _SIGNATURES = {
     "mdi_abi_version": (_INT, []),
     "mdi_check_device": (_INT, [_INT]),
     "mdi_sizeof_view": (_INT, []),
+    "mdi_profile_enable": (None, [_INT]),
+    "mdi_profile_collect": (_INT, [_P, _INT, _P, _P, _INT]),
     "mdi_setup_cameras": (_INT, [_P, _INT, _P, _P, _P, _P, _INT, _P]),
     "mdi_project_filter": (_INT, [_P, _INT, _P, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "mdi_gather_fit": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P, _INT, _INT, _P, _P]),
@@ -125,3 +127,15 @@ def ptr(t) -> int | None:
     if t is None:
         return None
     return t.data_ptr()
+
+
+def profile_collect() -> dict:
+    """{kernel name: {"ms": total device ms, "calls": n}} since the last collect (profiling on)."""
+    lib = load()
+    cap = 64
+    names = C.create_string_buffer(4096)
+    ms = (C.c_float * cap)()
+    calls = (C.c_int32 * cap)()
+    n = lib.mdi_profile_collect(C.cast(names, C.c_void_p), 4096, C.cast(ms, C.c_void_p), C.cast(calls, C.c_void_p), cap)
+    keys = names.value.decode().split("\n") if n else []
+    return {k: {"ms": float(ms[i]), "calls": int(calls[i])} for i, k in enumerate(keys[:n])}

@@ -10,6 +10,9 @@
 namespace mdi {
 
 void set_error(const char* fmt, ...);
+// per-kernel timing hook: closes the open range (if any) and opens `name` (nullptr: just close)
+extern bool g_prof;
+void prof_mark(const char* name, cudaStream_t st);
 
 #define MDI_REQUIRE(cond, ...)      \
   do {                              \
@@ -21,6 +24,7 @@ void set_error(const char* fmt, ...);
 
 #define MDI_CHECK_LAUNCH(name)                                                       \
   do {                                                                               \
+    if (mdi::g_prof) mdi::prof_mark(nullptr, 0);                                     \
     cudaError_t e__ = cudaGetLastError();                                            \
     if (e__ != cudaSuccess) {                                                        \
       mdi::set_error("%s: CUDA error: %s", name, cudaGetErrorString(e__));           \

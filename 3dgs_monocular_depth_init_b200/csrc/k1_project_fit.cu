@@ -182,6 +182,7 @@ extern "C" int mdi_setup_cameras(MdiView* views, int n_views, const float* K, co
   MDI_REQUIRE(n_views >= 0, "mdi_setup_cameras: negative size");
   if (n_views == 0) return MDI_OK;
   MDI_REQUIRE(views && K && c2w, "mdi_setup_cameras: null pointer");
+  mdi::prof_mark("setup_cameras_kernel", (cudaStream_t)stream);
   mdi::setup_cameras_kernel<<<(n_views + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
       views, n_views, K, c2w, Kinv, P_out, keep_P);
   MDI_CHECK_LAUNCH("mdi_setup_cameras");
@@ -196,6 +197,7 @@ extern "C" int mdi_project_filter(const MdiView* views, int n_views, const float
   if (n_views == 0) return MDI_OK;
   MDI_REQUIRE(views && sfm_xyz && uv && z && n_inbounds && n_valid && status,
               "mdi_project_filter: null pointer");
+  mdi::prof_mark("project_filter_kernel", (cudaStream_t)stream);
   mdi::project_filter_kernel<<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
       views, sfm_xyz, sfm_index, slots, uv, z, n_inbounds, n_valid, status);
   MDI_CHECK_LAUNCH("mdi_project_filter");
@@ -210,6 +212,7 @@ extern "C" int mdi_gather_fit(const MdiView* views, int n_views, int64_t slots, 
   if (n_views == 0) return MDI_OK;
   MDI_REQUIRE(views && uv && z && n_valid && d && sums, "mdi_gather_fit: null pointer");
   MDI_REQUIRE(!write_fit || scale_shift, "mdi_gather_fit: write_fit without scale_shift");
+  mdi::prof_mark("gather_fit_kernel", (cudaStream_t)stream);
   mdi::gather_fit_kernel<<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
       views, slots, uv, z, n_valid, d, sums, scale_shift, write_fit, patch_threshold,
       patch_blocked);
@@ -224,6 +227,7 @@ extern "C" int mdi_apply_scale_shift(const float* depth, int64_t n, const float*
   MDI_REQUIRE(depth && scale_shift && out, "mdi_apply_scale_shift: null pointer");
   int blocks = (int)((n + 1023) / 1024);
   if (blocks > mdi::kSMs * 16) blocks = mdi::kSMs * 16;
+  mdi::prof_mark("apply_scale_shift_kernel", (cudaStream_t)stream);
   mdi::apply_scale_shift_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(depth, n, scale_shift,
                                                                           out);
   MDI_CHECK_LAUNCH("mdi_apply_scale_shift");

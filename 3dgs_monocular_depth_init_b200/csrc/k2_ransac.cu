@@ -298,9 +298,11 @@ extern "C" int mdi_ransac(const MdiView* views, int n_views, const float* d, con
                                     200 * 1024), "mdi_ransac attr");
       attr_set = 200 * 1024;
     }
+    mdi::prof_mark("ransac_kernel", st);
     ransac_kernel<true><<<n_views, kRansacThreads, smem, st>>>(
         views, d, z, n_valid, status, sample_idx, *cfg, pts, scale_shift, inliers, n_iter, n_inliers);
   } else {
+    mdi::prof_mark("ransac_kernel", st);
     ransac_kernel<false><<<n_views, kRansacThreads, 0, st>>>(
         views, d, z, n_valid, status, sample_idx, *cfg, pts, scale_shift, inliers, n_iter, n_inliers);
   }

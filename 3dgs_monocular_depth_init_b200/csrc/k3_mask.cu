@@ -276,6 +276,7 @@ extern "C" int mdi_factor_table(int n_views, const float* lo_hi, int factor_min,
   MDI_REQUIRE(n_views >= 0, "mdi_factor_table: negative size");
   if (n_views == 0) return MDI_OK;
   MDI_REQUIRE(lo_hi && table, "mdi_factor_table: null pointer");
+  mdi::prof_mark("factor_table_kernel", (cudaStream_t)stream);
   mdi::factor_table_kernel<<<(n_views + 3) / 4, 128, 0, (cudaStream_t)stream>>>(
       n_views, lo_hi, factor_min, factor_max, table);
   MDI_CHECK_LAUNCH("mdi_factor_table");
@@ -316,6 +317,7 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
   }
   MDI_REQUIRE(!(prm.flags & MDI_KEEP_GRAD) || grad_range, "mdi_keep_mask: grad flag needs grad_range");
   cudaStream_t st = (cudaStream_t)stream;
+  mdi::prof_mark("keep_zero_fill", st);
   if (keep) MDI_CUDA(cudaMemsetAsync(keep, 0, (size_t)total_px, st), "mdi_keep_mask memset");
   MDI_CUDA(cudaMemsetAsync(bits, 0, (size_t)total_tiles * MDI_TILE_WORDS * 4, st), "mdi_keep_mask memset");
   MDI_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)total_tiles * 4, st), "mdi_keep_mask memset");
@@ -324,10 +326,12 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
                             ((max_width + min_stride - 1) / min_stride);
     MDI_REQUIRE((max_pts + kCtaPoints - 1) / kCtaPoints < (1LL << 31), "mdi_keep_mask: lattice too large");
     dim3 grid((unsigned)((max_pts + kCtaPoints - 1) / kCtaPoints), n_strides, n_views);
+    mdi::prof_mark("keep_lattice_kernel", st);
     keep_lattice_kernel<<<grid, kLatticeWarps * 32, 0, st>>>(
         views, scale_shift, status, lo_hi, grad_range, patch_blocked, factor_table, prm, keep, bits,
         tile_counts);
   } else {
+    mdi::prof_mark("keep_pixel_kernel", st);
     keep_pixel_kernel<<<(unsigned)total_tiles, kMaskThreads, 0, st>>>(
         views, n_views, scale_shift, status, lo_hi, grad_range, patch_blocked, prm, keep, bits,
         tile_counts);

@@ -864,20 +864,25 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
   const int mode = (flags & MDI_STATS_EXACT) ? 1 : ((flags & MDI_STATS_RETRY_FLAGGED) ? 2 : 0);
   const int pop = flags & (MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL);
   MDI_CUDA(cudaMemsetAsync(ws.hdr, 0, sizeof(StatsHdr) * (size_t)n_views, st), "mdi_depth_range");
+  mdi::prof_mark("stats_init_kernel", st);
   stats_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(ws.hdr, n_views, status, mode);
   dim3 grid(max_chunks(max_tiles_per_view), (unsigned)n_views);
   MDI_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(uint32_t) * kTargets * kBins * (size_t)n_views, st),
            "mdi_depth_range");
   if (mode == 0) {
     const int64_t groups = max_tiles_per_view * (MDI_TILE_PX / kSampleGroup);
+    mdi::prof_mark("stats_sample_kernel", st);
     stats_sample_kernel<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n_views), 256, 0, st>>>(
         views, scale_shift, status, pop, ws);
+    mdi::prof_mark("stats_bracket_kernel", st);
     stats_bracket_kernel<<<n_views, kBracketThreads, 0, st>>>(status, ws);
     const bool um = pop & MDI_KEEP_PRED_MASK, se = pop & MDI_KEEP_SENTINEL;
+    mdi::prof_mark("stats_main_kernel", st);
     if (um && se) stats_main_kernel<true, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     else if (um) stats_main_kernel<true, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     else if (se) stats_main_kernel<false, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     else stats_main_kernel<false, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
+    mdi::prof_mark("stats_finish_kernel", st);
     stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
   } else {
     static bool attr_done = false;
@@ -886,11 +891,17 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
                                     kTargets * kBins * 4), "mdi_depth_range attr");
       attr_done = true;
     }
+    mdi::prof_mark("stats_pass_kernel", st);
     stats_pass_kernel<0><<<grid, kStatsThreads, kBins * 4, st>>>(views, scale_shift, status, pop, ws);
+    mdi::prof_mark("stats_select_kernel", st);
     stats_select_kernel<0><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
+    mdi::prof_mark("stats_pass_kernel", st);
     stats_pass_kernel<1><<<grid, kStatsThreads, kTargets * kBins * 4, st>>>(views, scale_shift, status, pop, ws);
+    mdi::prof_mark("stats_select_kernel", st);
     stats_select_kernel<1><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
+    mdi::prof_mark("stats_pass_kernel", st);
     stats_pass_kernel<2><<<grid, kStatsThreads, kTargets * 256 * 4, st>>>(views, scale_shift, status, pop, ws);
+    mdi::prof_mark("stats_select_kernel", st);
     stats_select_kernel<2><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
   }
   MDI_CHECK_LAUNCH("mdi_depth_range");
@@ -907,9 +918,12 @@ extern "C" int mdi_grad_range(const MdiView* views, int n_views, int64_t max_til
   MDI_REQUIRE(n_views <= 65535, "mdi_grad_range: more than 65535 views per call");
   cudaStream_t st = (cudaStream_t)stream;
   uint32_t* keys = reinterpret_cast<uint32_t*>(grad_range);
+  mdi::prof_mark("grad_range_init_kernel", st);
   grad_range_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(keys, n_views);
   dim3 grid(max_chunks(max_tiles_per_view), (unsigned)n_views);
+  mdi::prof_mark("grad_range_kernel", st);
   grad_range_kernel<<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, keys);
+  mdi::prof_mark("grad_range_finish_kernel", st);
   grad_range_finish_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(grad_range, n_views);
   MDI_CHECK_LAUNCH("mdi_grad_range");
   return MDI_OK;

@@ -150,9 +150,12 @@ extern "C" int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_t
   MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_scan_tiles: negative size");
   MDI_REQUIRE(views && tile_counts && tile_offsets && view_counts && view_offsets,
               "mdi_scan_tiles: null pointer");
-  if (n_views > 0)
+  if (n_views > 0) {
+    mdi::prof_mark("scan_view_tiles_kernel", (cudaStream_t)stream);
     mdi::scan_view_tiles_kernel<<<n_views, mdi::kScanThreads, 0, (cudaStream_t)stream>>>(
         views, tile_counts, tile_offsets, view_counts);
+  }
+  mdi::prof_mark("scan_views_kernel", (cudaStream_t)stream);
   mdi::scan_views_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_views, view_counts, view_offsets, total);
   MDI_CHECK_LAUNCH("mdi_scan_tiles");
   return MDI_OK;
@@ -170,14 +173,17 @@ extern "C" int mdi_emit_points(const MdiView* views, int n_views, int64_t total_
   const unsigned grid = (unsigned)total_tiles;
   switch (image_kind) {
     case MDI_IMAGE_F32_UNIT:
+      mdi::prof_mark("emit_points_kernel", st);
       mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitThreads, 0, st>>>(
           views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     case MDI_IMAGE_F32_255:
+      mdi::prof_mark("emit_points_kernel", st);
       mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitThreads, 0, st>>>(
           views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     case MDI_IMAGE_U8:
+      mdi::prof_mark("emit_points_kernel", st);
       mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitThreads, 0, st>>>(
           views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;

@@ -64,6 +64,7 @@ extern "C" int mdi_min_extents(const float* pts, int64_t n, const float* K, cons
   MDI_REQUIRE(pts && extents && (n_cams == 0 || (K && P && sizes)), "mdi_min_extents: null pointer");
   const int64_t blocks = (n + mdi::kExtThreads - 1) / mdi::kExtThreads;
   MDI_REQUIRE(blocks < (1LL << 31), "mdi_min_extents: too many points");
+  mdi::prof_mark("min_extents_kernel", (cudaStream_t)stream);
   mdi::min_extents_kernel<<<(unsigned)blocks, mdi::kExtThreads, 0, (cudaStream_t)stream>>>(
       pts, n, K, P, sizes, n_cams, extents);
   MDI_CHECK_LAUNCH("mdi_min_extents");

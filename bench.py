@@ -90,15 +90,17 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def algorithmic_bytes(call: str, HW: int, V: int, n_kept: int, n_sfm_slots: int, adaptive: bool) -> float:
-    """Algorithmic bytes of one launch group, per SURVEY.md 8(d): per view
-    B = P*HW*5 + HW + 36*Nk + 16*M, split over the entry points that move them."""
+def algorithmic_bytes(kernel: str, HW: int, V: int, n_kept: int, n_sfm_slots: int, adaptive: bool) -> float:
+    """Algorithmic bytes of one launch of a kernel, per SURVEY.md 8(d): per view
+    B = P*HW*5 + HW + 36*Nk + 16*M, split over the kernels that move them."""
     return {
-        "mdi_depth_range": V * HW * 5.0,              # the one statistics read of depth + mask
-        "mdi_keep_mask": V * HW * 6.0,                # depth + mask read, keep mask written
-        "mdi_emit_points": 36.0 * n_kept,             # rgb read, xyz + rgb written
-        "mdi_project_filter": 16.0 * n_sfm_slots,     # sfm xyz + index
-    }.get(call, 0.0)
+        "stats_main_kernel": V * HW * 5.0,            # the one statistics read of depth + mask
+        "keep_lattice_kernel": V * HW * 5.0,          # the mask pass's read of depth + mask (rows without
+                                                      # a lattice point are skipped: real traffic is lower)
+        "keep_zero_fill": V * HW * 1.0,               # keep mask written
+        "emit_points_kernel": 36.0 * n_kept,          # rgb read, xyz + rgb written
+        "project_filter_kernel": 16.0 * n_sfm_slots,  # sfm xyz + index
+    }.get(kernel, 0.0)
 
 
 def cpu_reference_run(workload: str, n_views_sample: int, seed: int = 20261104):
@@ -194,9 +196,9 @@ def run_ours(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    eng.profile = True
-    eng.events = []
-    launches0 = eng.launches
+    lib = L.load()
+    lib.mdi_profile_enable(1)   # CUDA events around every kernel launch of the library
+    L.profile_collect()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -208,9 +210,9 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms)
-    eng.profile = False
-    ktimes = eng.kernel_times_ms()
-    launches = eng.launches - launches0
+    ktimes = L.profile_collect()
+    lib.mdi_profile_enable(0)
+    launches = sum(v["calls"] for k, v in ktimes.items() if k != "keep_zero_fill")
     n_kept = int(res.total)
     n_ok = int((res.status == 0).sum())
 
@@ -262,6 +264,10 @@ def run_ours(args):
     n_slots = sum(len(sc.point_indices[n]) for n in sc.names)
     hbm_calls = {k: v for k, v in ktimes.items() if algorithmic_bytes(k, HW, V, n_kept, n_slots, subsample == "adaptive") > 0}
     dom = max(hbm_calls, key=lambda k: hbm_calls[k]["ms"]) if hbm_calls else None
+    traffic = None   # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu capture
+    tpath = ROOT / "profiles" / "ncu_traffic.json"
+    if tpath.exists() and dom:
+        traffic = json.loads(tpath.read_text()).get(args.workload, {}).get(dom)
     roof = None
     breakdown = {}
     for k, v in ktimes.items():
@@ -273,7 +279,8 @@ def run_ours(args):
         per = ktimes[dom]["ms"] / ktimes[dom]["calls"]
         ach = algorithmic_bytes(dom, HW, V, n_kept, n_slots, subsample == "adaptive") / (per * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src}
+                "traffic": traffic, "peak_source": peak_src,
+                "note": "achieved = algorithmic bytes of one launch / its mean CUDA-event duration inside the timed region"}
     # whole-step algorithmic bytes: P*HW*5 + HW + 36*Nk + 16*M per view
     P = 2 if subsample == "adaptive" else 1
     step_bytes = V * (P * HW * 5 + HW) + 36 * n_kept + 16 * n_slots

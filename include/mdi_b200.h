@@ -138,6 +138,14 @@ int mdi_check_device(int device);
 int mdi_sizeof_view(void);
 
 /*
+ * Optional tracing: with profiling enabled every kernel launch of the library is bracketed by CUDA
+ * events on its stream; mdi_profile_collect synchronises, sums the device time by kernel name
+ * ('\n'-separated into names_buf), clears the record and returns the number of names.
+ */
+void mdi_profile_enable(int on);
+int mdi_profile_collect(char* names_buf, int buf_len, float* ms, int32_t* calls, int cap);
+
+/*
  * a1: fills P, Kinv and c2w of every descriptor on the device.  K float32 [V,9], c2w float32
  * [V,16] (row-major 4x4), Kinv float32 [V,9] (inv(K) computed by the caller) or NULL when every K
  * is a zero-skew pinhole matrix (then the closed form is used); P_out float32 [V,12] or NULL.

@@ -1,0 +1,61 @@
+"""Multi-rank plumbing on the CPU (gloo, world_size 2): the view partition and the order-preserving
+variable-length all-gather of the per-rank clouds (output must equal the 1-rank order)."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from helpers import mod
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, counts, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        d = mod("distributed")
+        g = torch.Generator().manual_seed(100 + rank)
+        n = counts[rank]
+        xyz = torch.rand(n, 3, generator=g)
+        rgb = torch.rand(n, 3, generator=g)
+        gx, gr, c = d.allgather_points(xyz, rgb)
+        out[rank] = (gx.numpy().copy(), gr.numpy().copy(), c.numpy().copy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_view_partition_covers_views_in_order():
+    d = mod("distributed")
+    for n_views, world in [(200, 8), (7, 2), (3, 4), (0, 2), (300, 4)]:
+        got = [i for r in range(world) for i in d.view_partition(n_views, world, r)]
+        assert got == list(range(n_views))
+
+
+def test_allgather_points_gloo_world2_is_rank_ordered_concat():
+    world, counts = 2, [5, 9]
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), counts, out), nprocs=world, join=True)
+    exp_x, exp_r = [], []
+    for r in range(world):
+        g = torch.Generator().manual_seed(100 + r)
+        exp_x.append(torch.rand(counts[r], 3, generator=g)); exp_r.append(torch.rand(counts[r], 3, generator=g))
+    exp_x, exp_r = torch.cat(exp_x).numpy(), torch.cat(exp_r).numpy()
+    for r in range(world):
+        gx, gr, c = out[r]
+        assert np.array_equal(gx, exp_x) and np.array_equal(gr, exp_r) and c.tolist() == counts
+
+
+def test_allgather_points_handles_an_empty_rank():
+    world, counts = 2, [0, 4]
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), counts, out), nprocs=world, join=True)
+    for r in range(world):
+        assert out[r][0].shape == (4, 3) and out[r][2].tolist() == counts
