@@ -45,7 +45,7 @@ struct StatsHdr {
   uint32_t slot_prefix[kTargets];  // prefix each histogram slot selects on
   uint32_t tgt_prefix[kTargets];
   uint32_t tgt_slot[kTargets];
-  uint32_t smp_min, smp_max, _pad;
+  uint32_t smp_min, smp_max, fail_code;  // fail_code: why the one-pass path asked for a retry
   long long tgt_rank[kTargets];
   float w[2];
   uint32_t gmin_key, gmax_key;
@@ -334,8 +334,8 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
   under = __reduce_add_sync(0xffffffffu, under);
   if ((tid & 31) == 0 && under) atomicAdd(&s_under, under);
   // half-width of the rank bracket: the sample is ns / 8 sectors of 8 adjacent (correlated) pixels,
-  // so 4.5 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
-  const double delta = 0.005 + 4.5 * sqrt(0.1875 * 8.0 / (double)ns);
+  // so 6 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
+  const double delta = 0.005 + 6.0 * sqrt(0.1875 * 8.0 / (double)ns);
   if (tid == 0) {
     for (int g = 0; g < 2; ++g) {
       const double q = g == 0 ? 0.25 : 0.75;
@@ -423,22 +423,24 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
     cnt += pop ? 1u : 0u;
     below0 += (pop && key < L0) ? 1u : 0u;
     below1 += (pop && key < L1) ? 1u : 0u;
-    const uint32_t o0 = key - L0, o1 = key - L1;
-    const bool in0 = pop && o0 <= W0, in1 = pop && o1 <= W1;
-    if (in0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
-    if (in1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
-    const bool c = in0 || in1;
+    const bool c = pop && ((key - L0) <= W0 || (key - L1) <= W1);
     const uint32_t m = __ballot_sync(0xffffffffu, c);
     if (c) stage[wcount + __popc(m & lt)] = key;
     wcount += __popc(m);
   };
+  // staged keys -> bracket histograms (all lanes busy: only candidates get here) + candidate list
   auto flush = [&]() {
     uint32_t base = 0;
     if (lane == 0) base = atomicAdd(&h->n_cand, wcount);
     base = __shfl_sync(0xffffffffu, base, 0);
     __syncwarp();
-    for (uint32_t i = lane; i < wcount; i += 32)
-      if ((int64_t)base + i < ws.c_cap) cand[base + i] = stage[i];
+    for (uint32_t i = lane; i < wcount; i += 32) {
+      const uint32_t key = stage[i];
+      const uint32_t o0 = key - L0, o1 = key - L1;
+      if (o0 <= W0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
+      if (o1 <= W1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
+      if ((int64_t)base + i < ws.c_cap) cand[base + i] = key;
+    }
     __syncwarp();
     wcount = 0;
   };
@@ -535,7 +537,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
   const uint32_t Wd[2] = {h->br_hi[0] - L[0], h->br_hi[1] - L[1]};
   const uint32_t sft[2] = {h->br_shift[0], h->br_shift[1]};
   if (tid < kTargets) { s_len[tid] = 0; s_bin[tid] = 0xFFFFFFFFu; s_out[tid] = 0; }
-  if (tid == 0) s_fail = (int64_t)n_cand > ws.c_cap ? 1u : 0u;
+  if (tid == 0) s_fail = (int64_t)n_cand > ws.c_cap ? 1u : 0u;   // 1: candidate list overflow
   __syncthreads();
   if (!has_nan && !s_fail) {
     // 1. bin of each target rank in its bracket histogram (2 bins per thread)
@@ -549,7 +551,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
       const long long cum = block_excl_scan((int)(c0 + c1), scan_smem, &tot);
       if (r >= cum && r < cum + c0) { s_bin[j] = 2 * tid; s_rank[j] = r - cum; }
       else if (r >= cum + c0 && r < cum + c0 + c1) { s_bin[j] = 2 * tid + 1; s_rank[j] = r - cum - c0; }
-      if (tid == 0 && (r < 0 || r >= tot)) s_fail = 1u;
+      if (tid == 0 && (r < 0 || r >= tot)) s_fail = r < 0 ? 2u : 3u;  // 2 / 3: rank below / above the bracket
       __syncthreads();
     }
   }
@@ -591,7 +593,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
 #pragma unroll 1
     for (int j = 0; j < kTargets; ++j) {
       const uint32_t m = s_len[slot[j]];
-      if (m > (uint32_t)kListCap || (long long)m <= s_rank[j]) { if (tid == 0) s_fail = 1u; continue; }
+      if (m > (uint32_t)kListCap || (long long)m <= s_rank[j]) { if (tid == 0) s_fail = 4u; continue; }  // 4: bin too full
       const uint32_t* lst = s_list[slot[j]];
       for (uint32_t a = tid; a < m; a += kSelThreads) {
         const uint32_t key = lst[a];
@@ -606,6 +608,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
     __syncthreads();
   }
   if (tid == 0) {
+    h->fail_code = s_fail;
     if (s_fail) {
       if (lo_hi) { lo_hi[2 * v] = NAN; lo_hi[2 * v + 1] = NAN; }
       if (status) status[v] |= MDI_STATUS_STATS_RETRY;

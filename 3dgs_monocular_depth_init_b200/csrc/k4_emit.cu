@@ -78,66 +78,73 @@ scan_views_kernel(int n_views, const int64_t* __restrict__ view_counts,
   if (threadIdx.x == 0 && total) *total = s_base;
 }
 
-constexpr int kEmitThreads = MDI_TILE_WORDS;  // one thread per bit word
+constexpr int kEmitWarps = 8;  // one warp per 4096-pixel tile, 4 bit words per lane
 
 // Reference: points_from_depth.py:292-312.  pc = ((x+.5) z, (y+.5) z, z); world =
 // c2w[:3,:3] (Kinv pc) + c2w[:3,3]; dot products as FMA chains (mdi_math.cuh dot3/dot4_fma).
 // RGB: image.view(-1,3)[mask] (monocular_depth_init.py:128,168), image/255.0 as a division.
 template <int IMAGE_KIND>
-__global__ void __launch_bounds__(kEmitThreads)
+__global__ void __launch_bounds__(kEmitWarps * 32)
 emit_points_kernel(const MdiView* __restrict__ views, int n_views,
                    const float* __restrict__ scale_shift, const uint32_t* __restrict__ bits,
                    const int64_t* __restrict__ tile_offsets, const int64_t* __restrict__ view_offsets,
                    int64_t total_tiles, float* __restrict__ xyz, float* __restrict__ rgb) {
-  __shared__ int scan_smem[33];
-  const int64_t tile = blockIdx.x;
-  uint32_t word = bits[tile * MDI_TILE_WORDS + threadIdx.x];
-  int tot;
-  const int excl = block_excl_scan(__popc(word), scan_smem, &tot);
-  if (tot == 0) return;
+  const int64_t tile = (int64_t)blockIdx.x * kEmitWarps + warp_id();
+  if (tile >= total_tiles) return;
+  const int lane = lane_id();
+  const uint4 w4 = __ldg(reinterpret_cast<const uint4*>(bits + tile * MDI_TILE_WORDS) + lane);
+  const int cnt = __popc(w4.x) + __popc(w4.y) + __popc(w4.z) + __popc(w4.w);
+  const int incl = warp_incl_scan(cnt);
+  if (__shfl_sync(0xffffffffu, incl, 31) == 0) return;
   const int v = find_view_fast(views, n_views, tile, total_tiles);
   const MdiView& vw = views[v];
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
   const int W = vw.W;
-  const float* depth = vw.depth;
+  const bool small = (int64_t)vw.H * W <= 0x7FFFFFFFLL;
+  const float* __restrict__ depth = vw.depth;
   const float* Ki = vw.Kinv;
   const float* M = vw.c2w;
-  int64_t out = view_offsets[v] + tile_offsets[tile] + excl;
-  const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX + (int64_t)threadIdx.x * 32;
-  while (word) {
-    const int b = __ffs(word) - 1;
-    word &= word - 1;
-    const int64_t p = px0 + b;
-    const int row = (int)(p / W);
-    const int col = (int)(p - (int64_t)row * W);
-    const float z = align_depth(__ldg(&depth[p]), s, t);
-    if (xyz) {
-      const float px = fmul(fadd((float)col, 0.5f), z);
-      const float py = fmul(fadd((float)row, 0.5f), z);
-      // inv(K) @ pc (dot-product kernel) and cam2world @ [cam;1] (FMA chain), see mdi_math.cuh
-      const float cx = dot3_kinv(Ki[0], Ki[1], Ki[2], px, py, z);
-      const float cy = dot3_kinv(Ki[3], Ki[4], Ki[5], px, py, z);
-      const float cz = dot3_kinv(Ki[6], Ki[7], Ki[8], px, py, z);
-      xyz[3 * out + 0] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
-      xyz[3 * out + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
-      xyz[3 * out + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
-    }
-    if (rgb) {
-      float r, g, bl;
-      if (IMAGE_KIND == MDI_IMAGE_U8) {
-        const uint8_t* im = reinterpret_cast<const uint8_t*>(vw.image) + 3 * p;
-        r = fdiv((float)im[0], 255.0f); g = fdiv((float)im[1], 255.0f); bl = fdiv((float)im[2], 255.0f);
-      } else {
-        const float* im = reinterpret_cast<const float*>(vw.image) + 3 * p;
-        r = im[0]; g = im[1]; bl = im[2];
-        if (IMAGE_KIND == MDI_IMAGE_F32_255) {
-          r = fdiv(r, 255.0f); g = fdiv(g, 255.0f); bl = fdiv(bl, 255.0f);
+  int64_t out = view_offsets[v] + tile_offsets[tile] + (incl - cnt);
+  const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX + (int64_t)lane * 128;
+#pragma unroll 1
+  for (int k = 0; k < 4; ++k) {
+    uint32_t word = k == 0 ? w4.x : k == 1 ? w4.y : k == 2 ? w4.z : w4.w;
+    while (word) {
+      const int b = __ffs(word) - 1;
+      word &= word - 1;
+      const int64_t p = px0 + 32 * k + b;
+      const int row = small ? (int)((uint32_t)p / (uint32_t)W) : (int)(p / W);
+      const int col = (int)(p - (int64_t)row * W);
+      const float z = align_depth(__ldg(&depth[p]), s, t);
+      float r = 0.f, g = 0.f, bl = 0.f;
+      if (rgb) {
+        if (IMAGE_KIND == MDI_IMAGE_U8) {
+          const uint8_t* im = reinterpret_cast<const uint8_t*>(vw.image) + 3 * p;
+          const uint8_t a0 = im[0], a1 = im[1], a2 = im[2];
+          r = fdiv((float)a0, 255.0f); g = fdiv((float)a1, 255.0f); bl = fdiv((float)a2, 255.0f);
+        } else {
+          const float* im = reinterpret_cast<const float*>(vw.image) + 3 * p;
+          r = im[0]; g = im[1]; bl = im[2];
+          if (IMAGE_KIND == MDI_IMAGE_F32_255) {
+            r = fdiv(r, 255.0f); g = fdiv(g, 255.0f); bl = fdiv(bl, 255.0f);
+          }
         }
       }
-      rgb[3 * out + 0] = r; rgb[3 * out + 1] = g; rgb[3 * out + 2] = bl;
+      if (xyz) {
+        const float px = fmul(fadd((float)col, 0.5f), z);
+        const float py = fmul(fadd((float)row, 0.5f), z);
+        // inv(K) @ pc (dot-product kernel) and cam2world @ [cam;1] (FMA chain), see mdi_math.cuh
+        const float cx = dot3_kinv(Ki[0], Ki[1], Ki[2], px, py, z);
+        const float cy = dot3_kinv(Ki[3], Ki[4], Ki[5], px, py, z);
+        const float cz = dot3_kinv(Ki[6], Ki[7], Ki[8], px, py, z);
+        xyz[3 * out + 0] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
+        xyz[3 * out + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
+        xyz[3 * out + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
+      }
+      if (rgb) { rgb[3 * out + 0] = r; rgb[3 * out + 1] = g; rgb[3 * out + 2] = bl; }
+      ++out;
     }
-    ++out;
   }
 }
 
@@ -170,21 +177,21 @@ extern "C" int mdi_emit_points(const MdiView* views, int n_views, int64_t total_
   MDI_REQUIRE(views && bits && tile_offsets && view_offsets, "mdi_emit_points: null pointer");
   MDI_REQUIRE(total_tiles < (1LL << 31), "mdi_emit_points: too many tiles");
   cudaStream_t st = (cudaStream_t)stream;
-  const unsigned grid = (unsigned)total_tiles;
+  const unsigned grid = (unsigned)((total_tiles + mdi::kEmitWarps - 1) / mdi::kEmitWarps);
   switch (image_kind) {
     case MDI_IMAGE_F32_UNIT:
       mdi::prof_mark("emit_points_kernel", st);
-      mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitThreads, 0, st>>>(
+      mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
           views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     case MDI_IMAGE_F32_255:
       mdi::prof_mark("emit_points_kernel", st);
-      mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitThreads, 0, st>>>(
+      mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
           views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     case MDI_IMAGE_U8:
       mdi::prof_mark("emit_points_kernel", st);
-      mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitThreads, 0, st>>>(
+      mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
           views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
       break;
     default:

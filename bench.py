@@ -176,8 +176,9 @@ def run_ours(args):
     HW = H * W
     input_bytes = depth.numel() * 4 + mask.numel() + image.numel()
 
+    torch.manual_seed(1234)   # RANSAC device-sampler seeds are drawn from torch's CPU generator
+
     def step():
-        torch.manual_seed(1234)
         res = mdi.points_from_views(cfg, depth, mask, image, sc.K, sc.c2w, sc.names, sc.points,
                                     sc.point_indices, dev, L.IMAGE_U8, sfm=sfm)
         if world > 1:
@@ -236,7 +237,6 @@ def run_ours(args):
     f0.record()
     e2e_steps = max(1, min(args.steps, 5))
     for _ in range(e2e_steps):
-        torch.manual_seed(1234)
         r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names,
                                                          sc.points, sc.point_indices, dev, L.IMAGE_U8)
         if world > 1:
