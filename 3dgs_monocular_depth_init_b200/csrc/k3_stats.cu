@@ -283,7 +283,7 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
   __shared__ uint32_t s_sort[1024];
   __shared__ uint32_t s_hist[kBrBins];
   __shared__ int scan_smem[33];
-  __shared__ uint32_t s_under, s_bin[kTargets];
+  __shared__ uint32_t s_bin[kTargets];
   __shared__ long long s_rank[kTargets];
   const int v = blockIdx.x, tid = threadIdx.x;
   StatsHdr* h = ws.hdr + v;
@@ -298,7 +298,6 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
   // bitonic sort of an evenly spaced 1024-key sub-sample
   s_sort[tid] = keys[(uint64_t)tid * ns / 1024];
   for (int i = tid; i < kBrBins; i += kBracketThreads) s_hist[i] = 0;
-  if (tid == 0) s_under = 0;
   __syncthreads();
   for (int k = 2; k <= 1024; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
@@ -311,11 +310,8 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
       __syncthreads();
     }
   }
-  const uint32_t Rlo = s_sort[102], Rhi = s_sort[921];
-  uint32_t sft = 0;
-  while (((Rhi - Rlo) >> sft) >= (uint32_t)kBrBins) ++sft;
-  // linear histogram of [Rlo, Rhi]; keys below counted, keys above implied
-  uint32_t under = 0;
+  // equal-mass bins: bin(key) = number of sorted sub-sample keys < key, 0 .. 1024.  (A histogram
+  // that is linear in the key is useless when the values straddle zero, where keys are log-spaced.)
   for (uint32_t base = 0; base < ns; base += 4 * kBracketThreads) {
     uint32_t kk[4];
 #pragma unroll
@@ -323,19 +319,25 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
       const uint32_t i = base + u * kBracketThreads + tid;
       kk[u] = i < ns ? keys[i] : 0xFFFFFFFFu;
     }
+    // four lower-bound searches in lock step (independent shared-memory loads in flight)
+    int lo[4] = {0, 0, 0, 0}, hi[4] = {1024, 1024, 1024, 1024};
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const bool in = base + u * kBracketThreads + tid < ns;
-      if (!in) continue;
-      if (kk[u] < Rlo) ++under;
-      else if (kk[u] <= Rhi) atomicAdd(&s_hist[(kk[u] - Rlo) >> sft], 1u);
+    for (int it = 0; it < 11; ++it) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (lo[u] < hi[u]) {
+          const int mid = (lo[u] + hi[u]) >> 1;
+          if (s_sort[mid] < kk[u]) lo[u] = mid + 1; else hi[u] = mid;
+        }
+      }
     }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (base + u * kBracketThreads + tid < ns) atomicAdd(&s_hist[lo[u]], 1u);
   }
-  under = __reduce_add_sync(0xffffffffu, under);
-  if ((tid & 31) == 0 && under) atomicAdd(&s_under, under);
   // half-width of the rank bracket: the sample is ns / 8 sectors of 8 adjacent (correlated) pixels,
-  // so 6 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
-  const double delta = 0.005 + 6.0 * sqrt(0.1875 * 8.0 / (double)ns);
+  // so 4.5 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
+  const double delta = 0.005 + 4.5 * sqrt(0.1875 * 8.0 / (double)ns);
   if (tid == 0) {
     for (int g = 0; g < 2; ++g) {
       const double q = g == 0 ? 0.25 : 0.75;
@@ -346,34 +348,27 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
     }
   }
   __syncthreads();
-  // bin of each bracket rank: 2 bins per thread; -1 = below the range, kBrBins = above it
-  const uint32_t c0 = s_hist[2 * tid], c1 = s_hist[2 * tid + 1];
+  // bin of each bracket rank (one bin per thread; bin 1024 = whatever lies above the last key)
+  const uint32_t c0 = s_hist[tid];
   int tot;
-  const long long cum = (long long)s_under + block_excl_scan((int)(c0 + c1), scan_smem, &tot);
-  if (tid < kTargets) s_bin[tid] = s_rank[tid] < (long long)s_under ? 0xFFFFFFFFu : (uint32_t)kBrBins;
+  const long long cum = block_excl_scan((int)c0, scan_smem, &tot);
+  if (tid < kTargets) s_bin[tid] = 1024u;
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < kTargets; ++j) {
     const long long r = s_rank[j];
-    if (r >= cum && r < cum + c0) s_bin[j] = 2 * tid;
-    else if (r >= cum + c0 && r < cum + c0 + c1) s_bin[j] = 2 * tid + 1;
+    if (r >= cum && r < cum + c0) s_bin[j] = tid;
   }
   __syncthreads();
   if (tid == 0) {
     for (int g = 0; g < 2; ++g) {
       const uint32_t bl = s_bin[2 * g], bh = s_bin[2 * g + 1];
-      // lower bound: start of the lower rank's bin (open when it lies outside the range)
-      uint32_t L = 0u, U = 0xFFFFFFFFu;
-      if (bl == (uint32_t)kBrBins) L = Rhi;
-      else if (bl != 0xFFFFFFFFu) L = Rlo + (bl << sft);
-      if (bh == 0xFFFFFFFFu) U = Rlo;
-      else if (bh != (uint32_t)kBrBins) {
-        const unsigned long long e = (unsigned long long)Rlo + (((unsigned long long)bh + 1ull) << sft) - 1ull;
-        U = e > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)e;
-      }
+      // keys of bin b satisfy sort[b-1] < key <= sort[b]
+      const uint32_t L = bl == 0 ? 0u : s_sort[bl - 1] + (s_sort[bl - 1] == 0xFFFFFFFFu ? 0u : 1u);
+      const uint32_t U = bh >= 1024u ? 0xFFFFFFFFu : s_sort[bh];
       uint32_t bs = 0;
       while (((U - L) >> bs) >= (uint32_t)kBrBins) ++bs;
-      h->br_lo[g] = L; h->br_hi[g] = U; h->br_shift[g] = bs;
+      h->br_lo[g] = L; h->br_hi[g] = U >= L ? U : L; h->br_shift[g] = bs;
     }
   }
 }
@@ -513,10 +508,14 @@ __device__ __forceinline__ void write_range(int v, const float val[kTargets], fl
 __global__ void __launch_bounds__(kSelThreads)
 stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict__ lo_hi,
                     float* __restrict__ quantiles, int64_t* __restrict__ retry_flag) {
-  __shared__ uint32_t s_list[kTargets][kListCap];
+  // the in-bin lists and the radix-select fallback share one buffer
+  __shared__ __align__(16) unsigned char s_raw[sizeof(SelShared) > sizeof(uint32_t) * kTargets * kListCap
+                                                   ? sizeof(SelShared) : sizeof(uint32_t) * kTargets * kListCap];
+  uint32_t (*s_list)[kListCap] = reinterpret_cast<uint32_t (*)[kListCap]>(s_raw);
   __shared__ int scan_smem[33];
   __shared__ uint32_t s_len[kTargets], s_bin[kTargets], s_out[kTargets], s_fail;
-  __shared__ long long s_rank[kTargets];
+  __shared__ uint32_t s_flo[kTargets], s_fhi[kTargets];
+  __shared__ long long s_rank[kTargets], s_rank0[kTargets];
   const int v = blockIdx.x, tid = threadIdx.x;
   StatsHdr* h = ws.hdr + v;
   const bool low_conf = status && (status[v] & MDI_STATUS_LOW_CONFIDENCE);
@@ -551,7 +550,10 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
       const long long cum = block_excl_scan((int)(c0 + c1), scan_smem, &tot);
       if (r >= cum && r < cum + c0) { s_bin[j] = 2 * tid; s_rank[j] = r - cum; }
       else if (r >= cum + c0 && r < cum + c0 + c1) { s_bin[j] = 2 * tid + 1; s_rank[j] = r - cum - c0; }
-      if (tid == 0 && (r < 0 || r >= tot)) s_fail = r < 0 ? 2u : 3u;  // 2 / 3: rank below / above the bracket
+      if (tid == 0) {
+        s_rank0[j] = r; s_flo[j] = L[g]; s_fhi[j] = L[g] + Wd[g];
+        if (r < 0 || r >= tot) s_fail = r < 0 ? 2u : 3u;  // 2 / 3: rank below / above the bracket
+      }
       __syncthreads();
     }
   }
@@ -606,6 +608,15 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
       }
     }
     __syncthreads();
+    if (s_fail == 4u) {
+      // a bracket bin holds more keys than the list (heavy ties, values straddling zero): exact
+      // radix select among the candidates instead
+      __syncthreads();
+      SelShared& sel = *reinterpret_cast<SelShared*>(s_raw);
+      const uint32_t f = block_select(cand, n_cand, s_flo, s_fhi, s_rank0, s_out, sel);
+      if (tid == 0) s_fail = f ? 5u : 0u;
+      __syncthreads();
+    }
   }
   if (tid == 0) {
     h->fail_code = s_fail;

@@ -78,24 +78,30 @@ scan_views_kernel(int n_views, const int64_t* __restrict__ view_counts,
   if (threadIdx.x == 0 && total) *total = s_base;
 }
 
-constexpr int kEmitWarps = 8;  // one warp per 4096-pixel tile, 4 bit words per lane
+constexpr int kEmitWarps = 8;     // one warp per 4096-pixel tile, 4 bit words per lane
+constexpr int kEmitList = 1024;   // kept pixels of a tile listed in shared memory per pass
 
 // Reference: points_from_depth.py:292-312.  pc = ((x+.5) z, (y+.5) z, z); world =
 // c2w[:3,:3] (Kinv pc) + c2w[:3,3]; dot products as FMA chains (mdi_math.cuh dot3/dot4_fma).
 // RGB: image.view(-1,3)[mask] (monocular_depth_init.py:128,168), image/255.0 as a division.
+// The warp first lists the tile's kept pixels in row-major order in shared memory (scan of the
+// bit words), then lane j takes points j, j + 32, ...: one point per lane with all its loads
+// independent, consecutive lanes writing consecutive output records.
 template <int IMAGE_KIND>
 __global__ void __launch_bounds__(kEmitWarps * 32)
 emit_points_kernel(const MdiView* __restrict__ views, int n_views,
                    const float* __restrict__ scale_shift, const uint32_t* __restrict__ bits,
                    const int64_t* __restrict__ tile_offsets, const int64_t* __restrict__ view_offsets,
                    int64_t total_tiles, float* __restrict__ xyz, float* __restrict__ rgb) {
+  __shared__ uint16_t s_px[kEmitWarps][kEmitList];
   const int64_t tile = (int64_t)blockIdx.x * kEmitWarps + warp_id();
   if (tile >= total_tiles) return;
   const int lane = lane_id();
   const uint4 w4 = __ldg(reinterpret_cast<const uint4*>(bits + tile * MDI_TILE_WORDS) + lane);
   const int cnt = __popc(w4.x) + __popc(w4.y) + __popc(w4.z) + __popc(w4.w);
   const int incl = warp_incl_scan(cnt);
-  if (__shfl_sync(0xffffffffu, incl, 31) == 0) return;
+  const int tot = __shfl_sync(0xffffffffu, incl, 31);
+  if (tot == 0) return;
   const int v = find_view_fast(views, n_views, tile, total_tiles);
   const MdiView& vw = views[v];
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
@@ -105,15 +111,28 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
   const float* __restrict__ depth = vw.depth;
   const float* Ki = vw.Kinv;
   const float* M = vw.c2w;
-  int64_t out = view_offsets[v] + tile_offsets[tile] + (incl - cnt);
-  const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX + (int64_t)lane * 128;
+  const int64_t out0 = view_offsets[v] + tile_offsets[tile];
+  const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX;
+  uint16_t* list = s_px[warp_id()];
 #pragma unroll 1
-  for (int k = 0; k < 4; ++k) {
-    uint32_t word = k == 0 ? w4.x : k == 1 ? w4.y : k == 2 ? w4.z : w4.w;
-    while (word) {
-      const int b = __ffs(word) - 1;
-      word &= word - 1;
-      const int64_t p = px0 + 32 * k + b;
+  for (int base = 0; base < tot; base += kEmitList) {
+    // list points base .. base + kEmitList - 1 of the tile
+    int idx = incl - cnt;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      uint32_t word = k == 0 ? w4.x : k == 1 ? w4.y : k == 2 ? w4.z : w4.w;
+      while (word) {
+        const int b = __ffs(word) - 1;
+        word &= word - 1;
+        if (idx >= base && idx < base + kEmitList) list[idx - base] = (uint16_t)(lane * 128 + 32 * k + b);
+        ++idx;
+      }
+    }
+    __syncwarp();
+    const int n_here = min(kEmitList, tot - base);
+    for (int j = lane; j < n_here; j += 32) {
+      const int64_t p = px0 + list[j];
+      const int64_t out = out0 + base + j;
       const int row = small ? (int)((uint32_t)p / (uint32_t)W) : (int)(p / W);
       const int col = (int)(p - (int64_t)row * W);
       const float z = align_depth(__ldg(&depth[p]), s, t);
@@ -143,8 +162,8 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
         xyz[3 * out + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
       }
       if (rgb) { rgb[3 * out + 0] = r; rgb[3 * out + 1] = g; rgb[3 * out + 2] = bl; }
-      ++out;
     }
+    __syncwarp();
   }
 }
 

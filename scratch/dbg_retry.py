@@ -18,17 +18,18 @@ class P:
         if n != "mdi_depth_range": return f
         def g(*a):
             rc = f(*a); torch.cuda.synchronize()
-            snaps.append(eng._ws["stats_ws"][:200 * 160].cpu().numpy().view(np.uint32).reshape(200, 40).copy()); return rc
+            snaps.append(eng._ws["stats_ws"][:200 * 184].cpu().numpy().view(np.uint32).reshape(200, 46).copy()); return rc
         return g
 eng.lib = P(eng.lib)
 torch.manual_seed(1234)
 names = ["n_sample", "n_cand", "min", "max", "count", "below0", "below1", "brlo0", "brlo1", "brhi0", "brhi1", "sh0", "sh1", "run_exact"]
-for step in range(12):
+for step in range(40):
     snaps.clear()
     res = mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points, sc.point_indices, dev, L.IMAGE_U8, sfm=sfm)
     h = snaps[0]
-    fc = h[:, 33]
+    fc = h[:, 32]
     bad = np.nonzero(fc)[0]
+    if len(bad) == 0: continue
     print(step, "retry", res.extras.get("stats_retry"), "bad views", bad.tolist(), [int(fc[i]) for i in bad])
     for i in bad[:3]:
         d = dict(zip(names, h[i, :14].tolist()))

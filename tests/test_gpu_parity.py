@@ -182,6 +182,10 @@ def test_subsampler_and_mask_apis_vs_oracle():
     ad_cfg = mod("depth_subsampling.config").AdaptiveSubsamplingConfig(4, 11)
     ad = mod("depth_subsampling.adaptive_subsampling").AdaptiveDepthSubsampler(ad_cfg)
     assert torch.equal(ad.get_mask(rgb, a_dev, m_dev).cpu(), O.adaptive_mask(aligned, c.mask, 4, 11))
+    # more than 32 strides: the flat lattice walk with the exact per-point stride arithmetic
+    ad_wide = mod("depth_subsampling.adaptive_subsampling").AdaptiveDepthSubsampler(
+        mod("depth_subsampling.config").AdaptiveSubsamplingConfig(2, 40))
+    assert torch.equal(ad_wide.get_mask(rgb, a_dev, m_dev).cpu(), O.adaptive_mask(aligned, c.mask, 2, 40))
     nm = mod("depth_subsampling.num_sfm_points_mask")
     uv = torch.from_numpy(c.ref_uv)
     for n_small, thr in [(10, 8), (20, 2), (5, 30)]:
