@@ -282,6 +282,7 @@ __global__ void __launch_bounds__(kBracketThreads)
 stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
   __shared__ uint32_t s_sort[1024];
   __shared__ uint32_t s_hist[kBrBins];
+  __shared__ uint16_t s_guide[kBrBins + 2];
   __shared__ int scan_smem[33];
   __shared__ uint32_t s_bin[kTargets];
   __shared__ long long s_rank[kTargets];
@@ -312,6 +313,23 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
   }
   // equal-mass bins: bin(key) = number of sorted sub-sample keys < key, 0 .. 1024.  (A histogram
   // that is linear in the key is useless when the values straddle zero, where keys are log-spaced.)
+  // A 2048-entry guide over the robust range [sort[102], sort[921]] narrows each lower-bound
+  // search to a step or two in the common case.
+  const uint32_t Rlo = s_sort[102], Rhi = s_sort[921];
+  uint32_t gs = 0;
+  while (((Rhi - Rlo) >> gs) >= (uint32_t)kBrBins) ++gs;
+  auto lower_bound = [&](uint32_t key, int lo, int hi) {
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (s_sort[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+  };
+  for (int g = tid; g <= kBrBins; g += kBracketThreads) {
+    const unsigned long long e = (unsigned long long)Rlo + ((unsigned long long)g << gs);
+    s_guide[g] = (uint16_t)(e > (unsigned long long)Rhi ? lower_bound(Rhi, 0, 1024) + 0 : lower_bound((uint32_t)e, 0, 1024));
+  }
+  __syncthreads();
   for (uint32_t base = 0; base < ns; base += 4 * kBracketThreads) {
     uint32_t kk[4];
 #pragma unroll
@@ -319,21 +337,16 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
       const uint32_t i = base + u * kBracketThreads + tid;
       kk[u] = i < ns ? keys[i] : 0xFFFFFFFFu;
     }
-    // four lower-bound searches in lock step (independent shared-memory loads in flight)
-    int lo[4] = {0, 0, 0, 0}, hi[4] = {1024, 1024, 1024, 1024};
 #pragma unroll
-    for (int it = 0; it < 11; ++it) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (lo[u] < hi[u]) {
-          const int mid = (lo[u] + hi[u]) >> 1;
-          if (s_sort[mid] < kk[u]) lo[u] = mid + 1; else hi[u] = mid;
-        }
-      }
+    for (int u = 0; u < 4; ++u) {
+      if (base + u * kBracketThreads + tid >= ns) continue;
+      const uint32_t key = kk[u];
+      int lo, hi;
+      if (key < Rlo) { lo = 0; hi = 102; }
+      else if (key > Rhi) { lo = 921; hi = 1024; }
+      else { const uint32_t g = (key - Rlo) >> gs; lo = s_guide[g]; hi = s_guide[g + 1]; }
+      atomicAdd(&s_hist[lower_bound(key, lo, hi)], 1u);
     }
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (base + u * kBracketThreads + tid < ns) atomicAdd(&s_hist[lo[u]], 1u);
   }
   // half-width of the rank bracket: the sample is ns / 8 sectors of 8 adjacent (correlated) pixels,
   // so 4.5 sigma of a quantile estimated from ns / 8 draws, + 0.5 %
