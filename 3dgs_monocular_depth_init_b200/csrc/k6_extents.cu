@@ -3,7 +3,8 @@
 // cameras of 2 * depth / min(fx, fy); -1 when no camera sees the point).
 // One thread per point, cameras streamed through shared memory in chunks.  FP32-ALU bound
 // (N * C projections); min is order independent, the per-pair arithmetic keeps the reference
-// op order (no contraction), so the result is bit-exact.
+// op order (no contraction): Eigen evaluates P * p.homogeneous() as leftCols(3) * p + col(3) with
+// the 3-term dot product reduced as a0 + (a1 + a2) (oracle/native_oracle.c states the rules).
 #include <float.h>
 
 #include "common.cuh"
@@ -41,10 +42,10 @@ min_extents_kernel(const float* __restrict__ pts, int64_t n, const float* __rest
     if (i < n) {
       for (int c = 0; c < nc; ++c) {
         const CamRec& r = s_cam[c];
-        const float qz = fadd(fadd(fadd(fmul(r.P[8], x), fmul(r.P[9], y)), fmul(r.P[10], z)), r.P[11]);
+        const float qz = fadd(fadd(fmul(r.P[8], x), fadd(fmul(r.P[9], y), fmul(r.P[10], z))), r.P[11]);
         if (!(qz > 0.f)) continue;  // depth <= 0 (NaN falls through in the reference)
-        const float qx = fadd(fadd(fadd(fmul(r.P[0], x), fmul(r.P[1], y)), fmul(r.P[2], z)), r.P[3]);
-        const float qy = fadd(fadd(fadd(fmul(r.P[4], x), fmul(r.P[5], y)), fmul(r.P[6], z)), r.P[7]);
+        const float qx = fadd(fadd(fmul(r.P[0], x), fadd(fmul(r.P[1], y), fmul(r.P[2], z))), r.P[3]);
+        const float qy = fadd(fadd(fmul(r.P[4], x), fadd(fmul(r.P[5], y), fmul(r.P[6], z))), r.P[7]);
         const float u = fdiv(qx, qz), vv = fdiv(qy, qz);
         if (u < 0.f || u >= r.w || vv < 0.f || vv >= r.h) continue;
         const float e = fmul(2.0f, fdiv(qz, r.f));

@@ -26,8 +26,6 @@
  *   mdi_emit_points         points_from_depth.py:292-312, monocular_depth_init.py:168
  *   mdi_min_extents         native_modules/subsampling/src/impl.cpp:17-35,70-126
  *   mdi_merge_subsample     native_modules/subsampling/src/impl.cpp:198-274,313-426
- *   mdi_knn / mdi_lof       point_cloud_postprocess/postprocess.py:16-22 (sklearn LOF),
- *                           utils/runner_utils.py:143-147 (knn)
  */
 #ifndef MDI_B200_H_
 #define MDI_B200_H_
@@ -270,6 +268,23 @@ int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
  */
 int mdi_min_extents(const float* pts, int64_t n, const float* K, const float* P,
                     const int32_t* sizes, int n_cams, float* extents, void* stream);
+
+/*
+ * a14: merge subsampling of the final cloud (impl.cpp:313-426 with spatial_median :261-274).
+ *   pts, rgb float32 [n,3]; extents float32 [n] (mdi_min_extents).  out_pts / out_rgb float32 [n,3]
+ *   (worst case: nothing merges) receive *n_out rows in the reference's emission order (DFS, right
+ *   child first; merged rows are sequential fp32 means in original index order).
+ *   The tree is built level by level; the call synchronises `stream` once per level and on return,
+ *   so n_out / n_levels are HOST pointers.  max_levels <= 0 selects 1024; when frames are still
+ *   open after max_levels the call fails with MDI_EINVAL (>= 3 coincident points whose merge test
+ *   fails -- the reference loops forever on that input).  The debug cloud of the reference
+ *   (impl.cpp:322-323,378-388) is not produced.
+ */
+int64_t mdi_merge_workspace_bytes(int64_t n);
+int mdi_merge_subsample(const float* pts, const float* rgb, const float* extents, int64_t n,
+                        float max_bbox_aspect_ratio, float min_extent_mult, int max_levels,
+                        void* workspace, float* out_pts, float* out_rgb, int64_t* n_out,
+                        int32_t* n_levels, void* stream);
 
 #ifdef __cplusplus
 }
