@@ -84,6 +84,9 @@ _SIGNATURES = {
     "mdi_scan_tiles": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P]),
     "mdi_emit_points": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _P]),
     "mdi_min_extents": (_INT, [_P, _I64, _P, _P, _P, _INT, _P, _P]),
+    "mdi_knn_workspace_bytes": (_I64, [_I64]),
+    "mdi_knn": (_INT, [_P, _I64, _INT, _INT, _P, _P, _P, _P, _P]),
+    "mdi_lof": (_INT, [_I64, _INT, _P, _P, _P, _P, _P, _P, _P]),
     "mdi_merge_workspace_bytes": (_I64, [_I64]),
     "mdi_merge_subsample": (_INT, [_P, _P, _P, _I64, C.c_float, C.c_float, _INT, _P, _P, _P,
                                    C.POINTER(C.c_int64), C.POINTER(C.c_int32), _P]),

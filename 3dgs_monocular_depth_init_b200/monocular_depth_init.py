@@ -15,6 +15,7 @@ import torch
 from . import _lib as L
 from ._single import options_from_config, ransac_seed
 from .engine import ViewInputs, get_engine
+from .knn import knn
 from .point_cloud_postprocess.postprocess import postprocess_point_cloud
 from .types import InputImage
 
@@ -130,8 +131,12 @@ def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth
                                         config.mdi.postprocess, dev)
     _LOGGER.info("Num points after postprocess: %d", pts.shape[0])
     scales = None
-    if config.mdi.limit_init_scale:
-        raise NotImplementedError("limit_init_scale (kNN scales) is the next row of SURVEY.md 8f")
+    if config.mdi.limit_init_scale:  # monocular_depth_init.py:215-223
+        dist2_avg = (knn(pts, 4)[:, 1:] ** 2).mean(dim=-1)
+        dist_avg = torch.sqrt(dist2_avg)
+        quantile = torch.quantile(dist_avg, config.mdi.init_scale_clamp_quantile)
+        dist_avg = torch.clamp(dist_avg, max=quantile)
+        scales = torch.log(dist_avg * config.init_scale).unsqueeze(-1).repeat(1, 3)
     return pts, rgbs, scales
 
 

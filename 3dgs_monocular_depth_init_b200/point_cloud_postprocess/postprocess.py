@@ -6,15 +6,26 @@ import torch
 
 from .config import OutlierRemovalMethod, PointCloudPostprocessConfig
 from .subsampling import subsample_pointcloud_device
+from ..knn import local_outlier_factor
+
+
+def lof_outlier_removal(pts: torch.Tensor, config: PointCloudPostprocessConfig) -> torch.Tensor:
+    """postprocess.py:16-22: bool [N], True where LocalOutlierFactor(n_neighbors).fit_predict == -1."""
+    outliers, _ = local_outlier_factor(pts, config.lof_num_neighbors)
+    return outliers
 
 
 def postprocess_point_cloud(pts, rgbs, intrinsic_matrices, proj_matrices, image_sizes,
                             config: PointCloudPostprocessConfig, device):
     method = getattr(config.outlier_removal, "value", config.outlier_removal)
     if method == OutlierRemovalMethod.lof.value:
-        raise NotImplementedError("LOF outlier removal (SURVEY.md a12) is not built yet")
+        # postprocess.py:16-22,41-58 (the filtered_* / outliers_* PLY exports are not written)
+        outliers = lof_outlier_removal(pts, config)
+        keep = ~outliers
+        pts = pts[keep]
+        rgbs = rgbs[keep.to(rgbs.device)]
     elif method != OutlierRemovalMethod.off.value:
-        raise ValueError(f"Unsupported outlier removal method: {config.outlier_removal}")
+        raise ValueError(f"Unknown outlier removal method: {config.outlier_removal}")
     if config.subsample:
         # postprocess.py:60-75; the cloud stays on the device instead of a numpy round trip
         dev = torch.device(device)

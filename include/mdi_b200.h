@@ -26,6 +26,8 @@
  *   mdi_emit_points         points_from_depth.py:292-312, monocular_depth_init.py:168
  *   mdi_min_extents         native_modules/subsampling/src/impl.cpp:17-35,70-126
  *   mdi_merge_subsample     native_modules/subsampling/src/impl.cpp:198-274,313-426
+ *   mdi_knn / mdi_lof       point_cloud_postprocess/postprocess.py:16-22 (sklearn LOF),
+ *                           utils/runner_utils.py:143-147 (knn)
  */
 #ifndef MDI_B200_H_
 #define MDI_B200_H_
@@ -285,6 +287,30 @@ int mdi_merge_subsample(const float* pts, const float* rgb, const float* extents
                         float max_bbox_aspect_ratio, float min_extent_mult, int max_levels,
                         void* workspace, float* out_pts, float* out_rgb, int64_t* n_out,
                         int32_t* n_levels, void* stream);
+
+/*
+ * a12 / 8f-1: exact k nearest neighbours of every point of the cloud among the cloud
+ * (sklearn NearestNeighbors(k).kneighbors, utils/runner_utils.py:143-147; LocalOutlierFactor's
+ * neighbour search, point_cloud_postprocess/postprocess.py:16-22).
+ *   pts float32 [n,3]; idx int32 [n,k] original indices in ascending (distance, index) order;
+ *   dist float32 [n,k] or NULL; kdist float32 [n] (distance to the k-th neighbour) or NULL.
+ *   exclude_self != 0 leaves the query point itself out (LOF); 0 keeps it (kneighbors(x) of the
+ *   fitted x: first column is the point itself at distance 0).  1 <= k <= 64.
+ *   Distances: differences, squares, sum and square root in fp64 (sklearn's KDTree), cast to fp32.
+ */
+int64_t mdi_knn_workspace_bytes(int64_t n);
+int mdi_knn(const float* pts, int64_t n, int k, int exclude_self, void* workspace, int32_t* idx,
+            float* dist, float* kdist, void* stream);
+
+/*
+ * a12: Local Outlier Factor from the neighbours of mdi_knn(exclude_self=1) (sklearn _lof.py):
+ *   idx / dist / kdist as written by mdi_knn; lrd float32 [n] (scratch / result), lof float32 [n] or
+ *   NULL (= -negative_outlier_factor_), outlier uint8 [n] = (-lof < -1.5), the contamination="auto"
+ *   rule of fit_predict.  All arithmetic in fp32 with numpy's summation order, as sklearn does for
+ *   fp32 input.
+ */
+int mdi_lof(int64_t n, int k, const int32_t* idx, const float* dist, const float* kdist, float* lrd,
+            float* lof, uint8_t* outlier, void* stream);
 
 #ifdef __cplusplus
 }
