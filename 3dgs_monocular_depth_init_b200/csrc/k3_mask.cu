@@ -141,9 +141,10 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
   const int f = adaptive ? prm.fmin + (int)blockIdx.y : prm.static_factor;
   const MdiView* vp = views + v;
   const int H = vp->H, W = vp->W;
+  // all index arithmetic in 32 bits: the host entry point requires H * W < 2^31 for this kernel
   const uint32_t n_rows = (uint32_t)((H + f - 1) / f), n_cols = (uint32_t)((W + f - 1) / f);
-  const uint64_t n_pts = (uint64_t)n_rows * n_cols;
-  const uint64_t first = ((uint64_t)blockIdx.x * kLatticeWarps + warp_id()) * kChunk + lane_id();
+  const uint32_t n_pts = n_rows * n_cols;
+  const uint32_t first = ((uint32_t)blockIdx.x * kLatticeWarps + warp_id()) * kChunk + lane_id();
   if (first - lane_id() >= n_pts) return;
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
@@ -158,27 +159,29 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
   }
   const RestCtx ctx = make_ctx(vp, v, prm, patch_blocked, grad_range, s, t);
 
-  int64_t q[kBatch];   // pixel index, -1 = outside
+  // lattice coordinates of the lane's points: one division, then steps of 32 columns
+  uint32_t q[kBatch];           // pixel index, 0xFFFFFFFF = outside
+  uint16_t li[kBatch], lj[kBatch];
+  {
+    uint32_t i = first / n_cols, j = first - i * n_cols;
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      q[u] = (first + 32u * u < n_pts) ? (i * (uint32_t)f) * (uint32_t)W + j * (uint32_t)f : 0xFFFFFFFFu;
+      li[u] = (uint16_t)i; lj[u] = (uint16_t)j;
+      j += 32u;
+      while (j >= n_cols) { j -= n_cols; ++i; }
+    }
+  }
   float av[kBatch];
   bool ok[kBatch];
 #pragma unroll
-  for (int u = 0; u < kBatch; ++u) {
-    const uint64_t idx = first + 32u * u;
-    if (idx < n_pts) {
-      const uint32_t i = (uint32_t)(idx / n_cols), j = (uint32_t)(idx - (uint64_t)i * n_cols);
-      q[u] = (int64_t)i * f * W + (int64_t)j * f;
-    } else {
-      q[u] = -1;
-    }
-  }
-#pragma unroll
-  for (int u = 0; u < kBatch; ++u) av[u] = q[u] >= 0 ? __ldg(&depth[q[u]]) : 0.f;
+  for (int u = 0; u < kBatch; ++u) av[u] = q[u] != 0xFFFFFFFFu ? __ldg(&depth[q[u]]) : 0.f;
   bool any = false;
 #pragma unroll
   for (int u = 0; u < kBatch; ++u) {
     const float a = align_depth(av[u], s, t);
     av[u] = a;
-    bool hit = q[u] >= 0;
+    bool hit = q[u] != 0xFFFFFFFFu;
     if (hit && adaptive) {
       if (table && a == a) {
         hit = (a >= b_lo) && !(a >= b_hi);
@@ -202,15 +205,18 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
 #pragma unroll
     for (int u = 0; u < kBatch; ++u) ok[u] = ok[u] && mb[u] != 0;
   }
-  // SfM-density patch lookup of the survivors
+  // SfM-density patch lookup of the survivors.  r / patch_h as a multiply-high: exact because
+  // r, patch_h < 2^16 (x * d < 2^32 with M = floor(2^32 / d) + 1)
   if (ctx.pb) {
+    const uint32_t mh = 0xFFFFFFFFu / (uint32_t)max(ctx.patch_h, 1) + 1u, mw = 0xFFFFFFFFu / (uint32_t)max(ctx.patch_w, 1) + 1u;
     uint8_t pv[kBatch];
 #pragma unroll
     for (int u = 0; u < kBatch; ++u) {
       pv[u] = 0;
       if (ok[u]) {
-        const int r = (int)(q[u] / W), c = (int)(q[u] - (int64_t)r * W);
-        const int pr = r / ctx.patch_h, pc = c / ctx.patch_w;
+        const uint32_t r = (uint32_t)li[u] * (uint32_t)f, c = (uint32_t)lj[u] * (uint32_t)f;
+        const int pr = ctx.patch_h <= 1 ? (int)r : (int)__umulhi(r, mh);
+        const int pc = ctx.patch_w <= 1 ? (int)c : (int)__umulhi(c, mw);
         if (pr < ctx.grid_h && pc < ctx.grid_w) pv[u] = __ldg(&ctx.pb[pr * ctx.grid_w + pc]);
       }
     }
@@ -221,14 +227,14 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
   for (int u = 0; u < kBatch; ++u) {
     if (!ok[u]) continue;
     if (prm.flags & MDI_KEEP_GRAD) {
-      const int r = (int)(q[u] / W), c = (int)(q[u] - (int64_t)r * W);
+      const int r = (int)li[u] * f, c = (int)lj[u] * f;
       const float gmin = grad_range[2 * v];
       // (g - min) / ((max - min) + 1e-8)   (points_from_depth.py:210-211)
       const float gden = fadd(fsub(grad_range[2 * v + 1], gmin), 1e-8f);
-      const float g = grad_at(depth, W, q[u], r, c, av[u], s, t);
+      const float g = grad_at(depth, W, (int64_t)q[u], r, c, av[u], s, t);
       if (!(fdiv(fsub(g, gmin), gden) <= prm.grad_thresh)) continue;
     }
-    mark_kept(vp, q[u], keep, bits, tile_counts);
+    mark_kept(vp, (int64_t)q[u], keep, bits, tile_counts);
   }
 }
 
@@ -321,7 +327,8 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
   if (keep) MDI_CUDA(cudaMemsetAsync(keep, 0, (size_t)total_px, st), "mdi_keep_mask memset");
   MDI_CUDA(cudaMemsetAsync(bits, 0, (size_t)total_tiles * MDI_TILE_WORDS * 4, st), "mdi_keep_mask memset");
   MDI_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)total_tiles * 4, st), "mdi_keep_mask memset");
-  if (lattice && max_height > 0 && max_width > 0) {
+  // the lattice kernel indexes pixels and coordinates in 32 / 16 bits
+  if (lattice && max_height > 0 && max_width > 0 && max_height < 65536 && max_width < 65536) {
     const int64_t max_pts = (int64_t)((max_height + min_stride - 1) / min_stride) *
                             ((max_width + min_stride - 1) / min_stride);
     MDI_REQUIRE((max_pts + kCtaPoints - 1) / kCtaPoints < (1LL << 31), "mdi_keep_mask: lattice too large");

@@ -11,7 +11,6 @@ cfg.mdi.subsample_factor = "adaptive"
 sc = syn.make_scene(n_views=200, H=840, W=1297, n_sfm=5000, seed=1, device=str(dev), low_conf_every=50)
 sfm = mdi.SfmTable(sc.points, sc.point_indices, sc.names, dev)
 def step():
-    torch.manual_seed(1234)
     return mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points, sc.point_indices, dev, L.IMAGE_U8, sfm=sfm)
 for _ in range(3): step()
 torch.cuda.synchronize()
