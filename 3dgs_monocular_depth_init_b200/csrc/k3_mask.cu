@@ -66,9 +66,14 @@ __device__ __forceinline__ float grad_at(const float* __restrict__ depth, int W,
   return g;
 }
 
+constexpr int kFlatStrides = 32;
 struct MaskParams {
   int mode, static_factor, fmin, fmax, flags;
   float grad_thresh;
+  // flat grid of the lattice walk: CTAs of stride fmin + k are blockIdx.x in [cta_begin[k], cta_begin[k+1])
+  // (sized for the largest view); n_flat == 0 selects the (chunk, stride) 2-D grid instead
+  int n_flat;
+  int cta_begin[kFlatStrides + 1];
 };
 
 // every test but the stride test, for one pixel q = (r, c) with aligned depth a
@@ -138,13 +143,20 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
   const int v = blockIdx.z;
   if (status && status[v] != MDI_STATUS_OK) return;
   const bool adaptive = prm.mode == MDI_SUBSAMPLE_ADAPTIVE;
-  const int f = adaptive ? prm.fmin + (int)blockIdx.y : prm.static_factor;
+  int si = (int)blockIdx.y;
+  uint32_t bx = blockIdx.x;
+  if (prm.n_flat) {  // flat grid: no CTA is launched for chunks a coarse stride does not have
+    si = 0;
+    while (si + 1 < prm.n_flat && (int)blockIdx.x >= prm.cta_begin[si + 1]) ++si;
+    bx -= (uint32_t)prm.cta_begin[si];
+  }
+  const int f = adaptive ? prm.fmin + si : prm.static_factor;
   const MdiView* vp = views + v;
   const int H = vp->H, W = vp->W;
   // all index arithmetic in 32 bits: the host entry point requires H * W < 2^31 for this kernel
   const uint32_t n_rows = (uint32_t)((H + f - 1) / f), n_cols = (uint32_t)((W + f - 1) / f);
   const uint32_t n_pts = n_rows * n_cols;
-  const uint32_t first = ((uint32_t)blockIdx.x * kLatticeWarps + warp_id()) * kChunk + lane_id();
+  const uint32_t first = (bx * kLatticeWarps + warp_id()) * kChunk + lane_id();
   if (first - lane_id() >= n_pts) return;
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
@@ -302,8 +314,9 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
   MDI_REQUIRE(views && cfg && bits && tile_counts, "mdi_keep_mask: null pointer");
   MDI_REQUIRE(total_tiles < (1LL << 31), "mdi_keep_mask: too many tiles");
   MDI_REQUIRE(n_views <= 65535, "mdi_keep_mask: more than 65535 views per call");
-  MaskParams prm{cfg->mode, cfg->static_factor, cfg->factor_min, cfg->factor_max, cfg->flags,
-                 cfg->grad_thresh};
+  MaskParams prm{};
+  prm.mode = cfg->mode; prm.static_factor = cfg->static_factor; prm.fmin = cfg->factor_min;
+  prm.fmax = cfg->factor_max; prm.flags = cfg->flags; prm.grad_thresh = cfg->grad_thresh;
   bool lattice = false;
   int n_strides = 1, min_stride = 1;
   if (prm.flags & MDI_KEEP_SUBSAMPLE) {
@@ -333,6 +346,17 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
                             ((max_width + min_stride - 1) / min_stride);
     MDI_REQUIRE((max_pts + kCtaPoints - 1) / kCtaPoints < (1LL << 31), "mdi_keep_mask: lattice too large");
     dim3 grid((unsigned)((max_pts + kCtaPoints - 1) / kCtaPoints), n_strides, n_views);
+    if (n_strides > 1 && n_strides <= kFlatStrides) {
+      int64_t total = 0;
+      for (int k = 0; k < n_strides; ++k) {
+        const int fk = min_stride + k;
+        prm.cta_begin[k] = (int)total;
+        total += ((int64_t)((max_height + fk - 1) / fk) * ((max_width + fk - 1) / fk) + kCtaPoints - 1) / kCtaPoints;
+      }
+      prm.cta_begin[n_strides] = (int)total;
+      prm.n_flat = n_strides;
+      grid = dim3((unsigned)total, 1, n_views);
+    }
     mdi::prof_mark("keep_lattice_kernel", st);
     keep_lattice_kernel<<<grid, kLatticeWarps * 32, 0, st>>>(
         views, scale_shift, status, lo_hi, grad_range, patch_blocked, factor_table, prm, keep, bits,

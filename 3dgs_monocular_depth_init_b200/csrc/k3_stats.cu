@@ -518,7 +518,7 @@ __device__ __forceinline__ void write_range(int v, const float val[kTargets], fl
   if (quantiles) { quantiles[4 * v] = q1; quantiles[4 * v + 1] = q3; quantiles[4 * v + 2] = mn; quantiles[4 * v + 3] = mx; }
 }
 
-__global__ void __launch_bounds__(kSelThreads)
+__global__ void __launch_bounds__(kSelThreads, 2)
 stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict__ lo_hi,
                     float* __restrict__ quantiles, int64_t* __restrict__ retry_flag) {
   // the in-bin lists and the radix-select fallback share one buffer
