@@ -10,6 +10,8 @@
 // The local-optimisation pass is only run for hypotheses whose sample loss beats the best
 // sample loss at the start of the round (a superset of those the sequential loop refits,
 // because that bound only decreases).  Issue-bound, not HBM-bound.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace mdi {
@@ -53,6 +55,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
   __shared__ double s_best_sample, s_best_lo;
   __shared__ float s_hbest[2];
   __shared__ int s_have, s_done, s_last_it, s_ninl;
+  __shared__ double s_req;  // iteration at which the stopping rule fires if the best model stays
 
   const int v = blockIdx.x;
   const int n = n_valid[v];
@@ -68,7 +71,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
   if (threadIdx.x == 0) {
     s_best_sample = INFINITY; s_best_lo = INFINITY;
     s_hbest[0] = NAN; s_hbest[1] = NAN;
-    s_have = 0; s_done = 0; s_last_it = cfg.max_iters - 1; s_ninl = 0;
+    s_have = 0; s_done = 0; s_last_it = cfg.max_iters - 1; s_ninl = 0; s_req = INFINITY;
   }
   if (skip) {
     if (threadIdx.x == 0) {
@@ -119,12 +122,18 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
   __syncthreads();
 
   const int n_samp = ss < n ? ss : n;
-  for (int round0 = 0; round0 < cfg.max_iters; round0 += kRound) {
-    const int it0 = round0 + warp * kHyp;   // this warp's hypotheses: it0 .. it0 + kHyp - 1
+  // One round = KH hypotheses per warp.  The first round takes one per warp (16 hypotheses): with a
+  // healthy inlier ratio the stopping rule fires after a handful of iterations, and a 64-wide
+  // round would score 50+ hypotheses nobody asks for; later rounds take 1, 2 or kHyp per warp,
+  // whatever covers the iterations the stopping rule still requires.
+  auto round = [&](auto kh_c, const int round0) {
+    constexpr int KH = decltype(kh_c)::value;
+    constexpr int HR = kRansacWarps * KH;
+    const int it0 = round0 + warp * KH;   // this warp's hypotheses: it0 .. it0 + KH - 1
     const double cutoff = s_best_sample;
-    // ---- sample fits: lane k < kHyp fits hypothesis it0 + k, then broadcasts it --------------
+    // ---- sample fits: lane k < KH fits hypothesis it0 + k, then broadcasts it --------------
     float hs0 = 0.f, hs1 = 0.f;
-    if (lane < kHyp && it0 + lane < cfg.max_iters) {
+    if (lane < KH && it0 + lane < cfg.max_iters) {
       const int it = it0 + lane;
       Sums sm = {0, 0, 0, 0, 0};
       int chosen[kMaxSample];
@@ -152,27 +161,27 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
       }
       solve(sm, &hs0, &hs1);
     }
-    float h0[kHyp], h1[kHyp];
-    bool act[kHyp];
+    float h0[KH], h1[KH];
+    bool act[KH];
 #pragma unroll
-    for (int k = 0; k < kHyp; ++k) {
+    for (int k = 0; k < KH; ++k) {
       h0[k] = __shfl_sync(0xffffffffu, hs0, k);
       h1[k] = __shfl_sync(0xffffffffu, hs1, k);
       act[k] = it0 + k < cfg.max_iters;
     }
-    // ---- phase A: sample loss and inlier normal equations of the kHyp hypotheses ---------------
-    Sums in[kHyp];
-    int n_out[kHyp];
-    double msac[kHyp];
+    // ---- phase A: sample loss and inlier normal equations of the KH hypotheses ---------------
+    Sums in[KH];
+    int n_out[KH];
+    double msac[KH];
 #pragma unroll
-    for (int k = 0; k < kHyp; ++k) { in[k] = {0, 0, 0, 0, 0}; n_out[k] = 0; msac[k] = 0.0; }
+    for (int k = 0; k < KH; ++k) { in[k] = {0, 0, 0, 0, 0}; n_out[k] = 0; msac[k] = 0.0; }
     if (act[0]) {
       for (int i = lane; i < n; i += 32) {
         const float dv = dp[i], gv = gp[i];
         const double dd = (double)dv, gd = (double)gv;
         const double ddd = dd * dd, ddg = dd * gd;
 #pragma unroll
-        for (int k = 0; k < kHyp; ++k) {
+        for (int k = 0; k < KH; ++k) {
           const float r = residual_sq(h0[k], h1[k], dv, gv);
           if (r < thr) { in[k].dd += ddd; in[k].d += dd; in[k].n += 1.0; in[k].dg += ddg; in[k].g += gd; }
           if (r >= thr) ++n_out[k];
@@ -183,7 +192,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
     float hl0 = 0.f, hl1 = 0.f;   // lane k keeps the local-optimisation fit of hypothesis k
     double loss_s_mine = INFINITY;
 #pragma unroll
-    for (int k = 0; k < kHyp; ++k) {
+    for (int k = 0; k < KH; ++k) {
       Sums t;
       t.dd = warp_sum_f64(in[k].dd); t.d = warp_sum_f64(in[k].d); t.n = warp_sum_f64(in[k].n);
       t.dg = warp_sum_f64(in[k].dg); t.g = warp_sum_f64(in[k].g);
@@ -195,15 +204,15 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
         if (act[k]) solve(t, &hl0, &hl1);
       }
     }
-    if (lane < kHyp && it0 + lane < cfg.max_iters) {
-      s_loss_sample[warp * kHyp + lane] = loss_s_mine;
-      s_hlo[warp * kHyp + lane][0] = hl0; s_hlo[warp * kHyp + lane][1] = hl1;
+    if (lane < KH && it0 + lane < cfg.max_iters) {
+      s_loss_sample[warp * KH + lane] = loss_s_mine;
+      s_hlo[warp * KH + lane][0] = hl0; s_hlo[warp * KH + lane][1] = hl1;
     }
     // ---- phase B: local-optimisation loss of the candidates --------------------------------------
-    bool candk[kHyp];
+    bool candk[KH];
     bool any_cand = false;
 #pragma unroll
-    for (int k = 0; k < kHyp; ++k) {
+    for (int k = 0; k < KH; ++k) {
       h0[k] = __shfl_sync(0xffffffffu, hl0, k);
       h1[k] = __shfl_sync(0xffffffffu, hl1, k);
       const double ls = __shfl_sync(0xffffffffu, loss_s_mine, k);
@@ -211,12 +220,14 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
       any_cand = any_cand || candk[k];
       n_out[k] = 0; msac[k] = 0.0;
     }
-    int n_in[kHyp] = {0, 0, 0, 0};
+    int n_in[KH];
+#pragma unroll
+    for (int k = 0; k < KH; ++k) n_in[k] = 0;
     if (any_cand) {
       for (int i = lane; i < n; i += 32) {
         const float dv = dp[i], gv = gp[i];
 #pragma unroll
-        for (int k = 0; k < kHyp; ++k) {
+        for (int k = 0; k < KH; ++k) {
           if (!candk[k]) continue;  // warp-uniform
           const float r = residual_sq(h0[k], h1[k], dv, gv);
           if (r < thr) ++n_in[k];
@@ -225,13 +236,13 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
         }
       }
 #pragma unroll
-      for (int k = 0; k < kHyp; ++k) {
+      for (int k = 0; k < KH; ++k) {
         if (!candk[k]) continue;
         const int ni = warp_sum_i32(n_in[k]);
         double loss_lo;
         if (msac_loss) loss_lo = (double)(float)warp_sum_f64(msac[k]);
         else loss_lo = (double)warp_sum_i32(n_out[k]);
-        if (lane == 0) { s_loss_lo[warp * kHyp + k] = loss_lo; s_ninl_lo[warp * kHyp + k] = ni; }
+        if (lane == 0) { s_loss_lo[warp * KH + k] = loss_lo; s_ninl_lo[warp * KH + k] = ni; }
       }
     }
     __syncthreads();
@@ -239,7 +250,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
     if (threadIdx.x == 0) {
       // the stopping bound only changes when the best model does
       double req = s_have ? required_samples((int64_t)s_ninl, (int64_t)n, ss, cfg.confidence) : 0.0;
-      for (int w = 0; w < kRound; ++w) {
+      for (int w = 0; w < HR; ++w) {
         const int itw = round0 + w;
         if (itw >= cfg.max_iters) break;
         if (s_loss_sample[w] < s_best_sample) {
@@ -257,9 +268,22 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
           break;
         }
       }
+      s_req = s_have ? fmax(req, (double)cfg.min_iters) : INFINITY;
     }
     __syncthreads();
-    if (s_done) break;
+  };
+  int round0 = 0;
+  if (cfg.max_iters > 0) { round(std::integral_constant<int, 1>{}, 0); round0 = kRansacWarps; }
+  while (!s_done && round0 < cfg.max_iters) {
+    // size the round to what the stopping rule still asks for with the current best model
+    const double need = s_req - (double)round0 + 1.0;
+    if (need <= (double)kRansacWarps) {
+      round(std::integral_constant<int, 1>{}, round0); round0 += kRansacWarps;
+    } else if (need <= (double)(2 * kRansacWarps)) {
+      round(std::integral_constant<int, 2>{}, round0); round0 += 2 * kRansacWarps;
+    } else {
+      round(std::integral_constant<int, kHyp>{}, round0); round0 += kRound;
+    }
   }
 
   const float h0 = s_hbest[0], h1 = s_hbest[1];
