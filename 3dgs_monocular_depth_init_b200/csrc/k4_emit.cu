@@ -87,13 +87,24 @@ constexpr int kEmitList = 1024;   // kept pixels of a tile listed in shared memo
 // The warp first lists the tile's kept pixels in row-major order in shared memory (scan of the
 // bit words), then lane j takes points j, j + 32, ...: one point per lane with all its loads
 // independent, consecutive lanes writing consecutive output records.
+// destination clouds of the emit kernel: this GPU's and (SURVEY 8e exchange step fused into the
+// kernel) the peer GPUs' copies, mapped into this address space by the caller
+struct EmitDst {
+  int n;
+  int64_t row_offset;  // first row of this GPU's points in the destination clouds
+  float* xyz[MDI_MAX_EMIT_DST];
+  float* rgb[MDI_MAX_EMIT_DST];
+};
+
 template <int IMAGE_KIND>
 __global__ void __launch_bounds__(kEmitWarps * 32)
 emit_points_kernel(const MdiView* __restrict__ views, int n_views,
                    const float* __restrict__ scale_shift, const uint32_t* __restrict__ bits,
                    const int64_t* __restrict__ tile_offsets, const int64_t* __restrict__ view_offsets,
-                   int64_t total_tiles, float* __restrict__ xyz, float* __restrict__ rgb) {
+                   int64_t total_tiles, EmitDst dst) {
   __shared__ uint16_t s_px[kEmitWarps][kEmitList];
+  __shared__ float s_rec[kEmitWarps][2][96];  // one warp-iteration of xyz / rgb records
+  const bool want_xyz = dst.xyz[0] != nullptr, want_rgb = dst.rgb[0] != nullptr;
   const int64_t tile = (int64_t)blockIdx.x * kEmitWarps + warp_id();
   if (tile >= total_tiles) return;
   const int lane = lane_id();
@@ -111,7 +122,7 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
   const float* __restrict__ depth = vw.depth;
   const float* Ki = vw.Kinv;
   const float* M = vw.c2w;
-  const int64_t out0 = view_offsets[v] + tile_offsets[tile];
+  const int64_t out0 = dst.row_offset + view_offsets[v] + tile_offsets[tile];
   const int64_t px0 = (tile - vw.tile_begin) * MDI_TILE_PX;
   uint16_t* list = s_px[warp_id()];
 #pragma unroll 1
@@ -130,38 +141,58 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
     }
     __syncwarp();
     const int n_here = min(kEmitList, tot - base);
-    for (int j = lane; j < n_here; j += 32) {
-      const int64_t p = px0 + list[j];
-      const int64_t out = out0 + base + j;
-      const int row = small ? (int)((uint32_t)p / (uint32_t)W) : (int)(p / W);
-      const int col = (int)(p - (int64_t)row * W);
-      const float z = align_depth(__ldg(&depth[p]), s, t);
-      float r = 0.f, g = 0.f, bl = 0.f;
-      if (rgb) {
-        if (IMAGE_KIND == MDI_IMAGE_U8) {
-          const uint8_t* im = reinterpret_cast<const uint8_t*>(vw.image) + 3 * p;
-          const uint8_t a0 = im[0], a1 = im[1], a2 = im[2];
-          r = fdiv((float)a0, 255.0f); g = fdiv((float)a1, 255.0f); bl = fdiv((float)a2, 255.0f);
-        } else {
-          const float* im = reinterpret_cast<const float*>(vw.image) + 3 * p;
-          r = im[0]; g = im[1]; bl = im[2];
-          if (IMAGE_KIND == MDI_IMAGE_F32_255) {
-            r = fdiv(r, 255.0f); g = fdiv(g, 255.0f); bl = fdiv(bl, 255.0f);
+    float* rec_xyz = s_rec[warp_id()][0];
+    float* rec_rgb = s_rec[warp_id()][1];
+    for (int j0 = 0; j0 < n_here; j0 += 32) {
+      const int j = j0 + lane;
+      if (j < n_here) {
+        const int64_t p = px0 + list[j];
+        const int row = small ? (int)((uint32_t)p / (uint32_t)W) : (int)(p / W);
+        const int col = (int)(p - (int64_t)row * W);
+        const float z = align_depth(__ldg(&depth[p]), s, t);
+        if (want_rgb) {
+          float r, g, bl;
+          if (IMAGE_KIND == MDI_IMAGE_U8) {
+            const uint8_t* im = reinterpret_cast<const uint8_t*>(vw.image) + 3 * p;
+            const uint8_t a0 = im[0], a1 = im[1], a2 = im[2];
+            r = fdiv((float)a0, 255.0f); g = fdiv((float)a1, 255.0f); bl = fdiv((float)a2, 255.0f);
+          } else {
+            const float* im = reinterpret_cast<const float*>(vw.image) + 3 * p;
+            r = im[0]; g = im[1]; bl = im[2];
+            if (IMAGE_KIND == MDI_IMAGE_F32_255) {
+              r = fdiv(r, 255.0f); g = fdiv(g, 255.0f); bl = fdiv(bl, 255.0f);
+            }
+          }
+          rec_rgb[3 * lane] = r; rec_rgb[3 * lane + 1] = g; rec_rgb[3 * lane + 2] = bl;
+        }
+        if (want_xyz) {
+          const float px = fmul(fadd((float)col, 0.5f), z);
+          const float py = fmul(fadd((float)row, 0.5f), z);
+          // inv(K) @ pc (dot-product kernel) and cam2world @ [cam;1] (FMA chain), see mdi_math.cuh
+          const float cx = dot3_kinv(Ki[0], Ki[1], Ki[2], px, py, z);
+          const float cy = dot3_kinv(Ki[3], Ki[4], Ki[5], px, py, z);
+          const float cz = dot3_kinv(Ki[6], Ki[7], Ki[8], px, py, z);
+          rec_xyz[3 * lane] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
+          rec_xyz[3 * lane + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
+          rec_xyz[3 * lane + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
+        }
+      }
+      __syncwarp();
+      // the records of this iteration are one contiguous run of words in every destination cloud
+      // (this GPU's and, through NVLink, its peers'): three fully coalesced stores per array
+      const int n_words = 3 * min(32, n_here - j0);
+      const int64_t w0 = 3 * (out0 + base + j0);
+      for (int d = 0; d < dst.n; ++d) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int w = 32 * k + lane;
+          if (w < n_words) {
+            if (want_xyz) dst.xyz[d][w0 + w] = rec_xyz[w];
+            if (want_rgb) dst.rgb[d][w0 + w] = rec_rgb[w];
           }
         }
       }
-      if (xyz) {
-        const float px = fmul(fadd((float)col, 0.5f), z);
-        const float py = fmul(fadd((float)row, 0.5f), z);
-        // inv(K) @ pc (dot-product kernel) and cam2world @ [cam;1] (FMA chain), see mdi_math.cuh
-        const float cx = dot3_kinv(Ki[0], Ki[1], Ki[2], px, py, z);
-        const float cy = dot3_kinv(Ki[3], Ki[4], Ki[5], px, py, z);
-        const float cz = dot3_kinv(Ki[6], Ki[7], Ki[8], px, py, z);
-        xyz[3 * out + 0] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
-        xyz[3 * out + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
-        xyz[3 * out + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
-      }
-      if (rgb) { rgb[3 * out + 0] = r; rgb[3 * out + 1] = g; rgb[3 * out + 2] = bl; }
+      __syncwarp();
     }
     __syncwarp();
   }
@@ -187,36 +218,64 @@ extern "C" int mdi_scan_tiles(const MdiView* views, int n_views, int64_t total_t
   return MDI_OK;
 }
 
+static int launch_emit(const MdiView* views, int n_views, int64_t total_tiles, const float* scale_shift,
+                       const uint32_t* bits, const int64_t* tile_offsets, const int64_t* view_offsets,
+                       int image_kind, const mdi::EmitDst& dst, void* stream, const char* who) {
+  MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "%s: negative size", who);
+  if (n_views == 0 || total_tiles == 0) return MDI_OK;
+  MDI_REQUIRE(views && bits && tile_offsets && view_offsets, "%s: null pointer", who);
+  MDI_REQUIRE(total_tiles < (1LL << 31), "%s: too many tiles", who);
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)((total_tiles + mdi::kEmitWarps - 1) / mdi::kEmitWarps);
+  mdi::prof_mark("emit_points_kernel", st);
+  switch (image_kind) {
+    case MDI_IMAGE_F32_UNIT:
+      mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
+          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, dst);
+      break;
+    case MDI_IMAGE_F32_255:
+      mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
+          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, dst);
+      break;
+    case MDI_IMAGE_U8:
+      mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
+          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, dst);
+      break;
+    default:
+      mdi::prof_mark(nullptr, 0);
+      mdi::set_error("%s: unknown image kind %d", who, image_kind);
+      return MDI_EINVAL;
+  }
+  MDI_CHECK_LAUNCH(who);
+  return MDI_OK;
+}
+
 extern "C" int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
                                const float* scale_shift, const uint32_t* bits,
                                const int64_t* tile_offsets, const int64_t* view_offsets,
                                int image_kind, float* xyz, float* rgb, void* stream) {
-  MDI_REQUIRE(n_views >= 0 && total_tiles >= 0, "mdi_emit_points: negative size");
-  if (n_views == 0 || total_tiles == 0) return MDI_OK;
-  MDI_REQUIRE(views && bits && tile_offsets && view_offsets, "mdi_emit_points: null pointer");
-  MDI_REQUIRE(total_tiles < (1LL << 31), "mdi_emit_points: too many tiles");
-  cudaStream_t st = (cudaStream_t)stream;
-  const unsigned grid = (unsigned)((total_tiles + mdi::kEmitWarps - 1) / mdi::kEmitWarps);
-  switch (image_kind) {
-    case MDI_IMAGE_F32_UNIT:
-      mdi::prof_mark("emit_points_kernel", st);
-      mdi::emit_points_kernel<MDI_IMAGE_F32_UNIT><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
-          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
-      break;
-    case MDI_IMAGE_F32_255:
-      mdi::prof_mark("emit_points_kernel", st);
-      mdi::emit_points_kernel<MDI_IMAGE_F32_255><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
-          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
-      break;
-    case MDI_IMAGE_U8:
-      mdi::prof_mark("emit_points_kernel", st);
-      mdi::emit_points_kernel<MDI_IMAGE_U8><<<grid, mdi::kEmitWarps * 32, 0, st>>>(
-          views, n_views, scale_shift, bits, tile_offsets, view_offsets, total_tiles, xyz, rgb);
-      break;
-    default:
-      mdi::set_error("mdi_emit_points: unknown image kind %d", image_kind);
-      return MDI_EINVAL;
+  mdi::EmitDst dst{};
+  dst.n = 1; dst.row_offset = 0; dst.xyz[0] = xyz; dst.rgb[0] = rgb;
+  return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
+                     dst, stream, "mdi_emit_points");
+}
+
+extern "C" int mdi_emit_points_multi(const MdiView* views, int n_views, int64_t total_tiles,
+                                     const float* scale_shift, const uint32_t* bits,
+                                     const int64_t* tile_offsets, const int64_t* view_offsets,
+                                     int image_kind, int n_dst, float* const* xyz_dst,
+                                     float* const* rgb_dst, int64_t row_offset, void* stream) {
+  MDI_REQUIRE(n_dst >= 1 && n_dst <= MDI_MAX_EMIT_DST, "mdi_emit_points_multi: n_dst %d not in 1..%d", n_dst,
+              MDI_MAX_EMIT_DST);
+  MDI_REQUIRE(row_offset >= 0, "mdi_emit_points_multi: negative row_offset");
+  MDI_REQUIRE(xyz_dst || rgb_dst, "mdi_emit_points_multi: no destination");
+  mdi::EmitDst dst{};
+  dst.n = n_dst; dst.row_offset = row_offset;
+  for (int d = 0; d < n_dst; ++d) {
+    dst.xyz[d] = xyz_dst ? xyz_dst[d] : nullptr;
+    dst.rgb[d] = rgb_dst ? rgb_dst[d] : nullptr;
+    MDI_REQUIRE((!xyz_dst || dst.xyz[d]) && (!rgb_dst || dst.rgb[d]), "mdi_emit_points_multi: null destination %d", d);
   }
-  MDI_CHECK_LAUNCH("mdi_emit_points");
-  return MDI_OK;
+  return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
+                     dst, stream, "mdi_emit_points_multi");
 }

@@ -80,6 +80,7 @@ class RunOptions:
     want_inliers: bool = False
     stop_after: Optional[str] = None             # "project" | "fit" | "mask": partial pipelines
     stats_exact: bool = False                    # force the three-pass exact quantile select
+    exchange: object = None                      # distributed.CloudExchange: emit into every rank's cloud
 
 
 @dataclass
@@ -442,6 +443,21 @@ class Engine:
         if opt.stop_after == "mask" or not (opt.want_xyz or opt.want_rgb):
             return res
         N = res.total
+        if opt.exchange is not None:
+            # multi-GPU: the emit kernel writes this rank's points into every rank's cloud
+            ex = opt.exchange
+            row_offset, total_all, counts = ex.begin(N)
+            if N:
+                n_dst = ex.world
+                xp = (C.c_void_p * n_dst)(*ex.xyz_ptrs)
+                rp = (C.c_void_p * n_dst)(*ex.rgb_ptrs) if vin.image is not None else None
+                L.check(lib.mdi_emit_points_multi(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
+                                                  res.view_offsets.data_ptr(), int(vin.image_kind), n_dst, xp, rp,
+                                                  int(row_offset), st), "mdi_emit_points_multi")
+            res.xyz, res.rgb = ex.finish()
+            res.extras["rank_counts"] = counts
+            res.extras["row_offset"] = row_offset
+            return res
         if opt.want_xyz:
             res.xyz = torch.empty((N, 3), dtype=f32, device=self.device)
         want_rgb = opt.want_rgb and vin.image is not None

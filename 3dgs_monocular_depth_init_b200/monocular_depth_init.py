@@ -54,25 +54,31 @@ class SfmTable:
         padded = (counts + 3) & ~3
         begin = np.zeros(len(lists) + 1, dtype=np.int64)
         np.cumsum(padded, out=begin[1:])
-        idx = np.zeros(int(begin[-1]) + 4, dtype=np.int32)
-        if len(lists):
-            flat = np.concatenate(lists)
-            # destination slot of every index: slot begin of its view + position within the view
-            pos = np.arange(flat.shape[0], dtype=np.int64) + np.repeat(begin[:-1] - (np.cumsum(counts) - counts), counts)
-            idx[pos] = flat
+        # staged in pinned memory (torch caches the allocation) so both uploads are asynchronous
+        use_pin = torch.device(device).type == "cuda"
+        idx_t = torch.zeros(int(begin[-1]) + 4, dtype=torch.int32, pin_memory=use_pin)
+        idx = idx_t.numpy()
+        for b, a in zip(begin[:-1].tolist(), lists):  # one slice copy per view
+            idx[b:b + len(a)] = a
+        pts_np = np.asarray(points)
+        xyz_t = torch.empty((int(pts_np.shape[0]), 3), dtype=torch.float32, pin_memory=use_pin)
+        np.copyto(xyz_t.numpy(), pts_np.reshape(-1, 3), casting="same_kind")
         self.counts = counts
-        self.host_bytes = int(points.shape[0]) * 12 + idx.nbytes
-        self.xyz = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float32)).to(device, non_blocking=True)
-        self.index = torch.from_numpy(idx).to(device, non_blocking=True)
+        self.host_bytes = int(pts_np.shape[0]) * 12 + idx.nbytes
+        self.xyz = xyz_t.to(device, non_blocking=True)
+        self.index = idx_t.to(device, non_blocking=True)
+        self._staging = (xyz_t, idx_t)  # keep the pinned buffers alive until the copies have run
 
 
 @torch.no_grad()
 def points_from_views(config, depths, masks, images, K, c2w, names, points: np.ndarray, point_indices: dict,
                       device, image_kind: int = L.IMAGE_F32_255, sample_idx: Optional[torch.Tensor] = None,
-                      sfm: Optional[SfmTable] = None):
+                      sfm: Optional[SfmTable] = None, exchange=None):
     """The batched hot path.  depths / masks / images: stacked tensors or per-view lists; images
     are [H,W,3] float32 0..255 or uint8, on the device or in pinned host memory.  `sfm` is an
     already uploaded SfmTable of (points, point_indices, names); built here when omitted.
+    `exchange` (distributed.CloudExchange, one per rank): this rank's views are emitted into every
+    rank's cloud, and xyz / rgb of the result are the whole scene (see distributed.py).
     Returns the engine RunResult (xyz / rgb on the device)."""
     eng = get_engine(device)
     dev = eng.device
@@ -84,6 +90,7 @@ def points_from_views(config, depths, masks, images, K, c2w, names, points: np.n
             opt.sample_idx = sample_idx.to(device=dev, dtype=torch.int32).contiguous()
         else:
             opt.ransac_seed = ransac_seed()
+    opt.exchange = exchange
     vin = ViewInputs(depth=depths, mask=masks, image=images, image_kind=image_kind, K=K, c2w=c2w,
                      sfm_xyz=sfm.xyz, sfm_index=sfm.index, sfm_counts=sfm.counts)
     return eng.run(vin, opt)
@@ -142,7 +149,7 @@ def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth
 
 @torch.no_grad()
 def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, points, point_indices, device,
-                           image_kind: int = L.IMAGE_U8, sample_idx: Optional[torch.Tensor] = None):
+                           image_kind: int = L.IMAGE_U8, sample_idx: Optional[torch.Tensor] = None, exchange=None):
     """End-to-end form of the hot path for HOST inputs (what a dataset loader hands over):
     depth [V,H,W] float32 and mask [V,H,W] bool in pinned host memory are copied to the device,
     the image [V,H,W,3] stays in pinned host memory and only its kept pixels are read over PCIe by
@@ -158,9 +165,14 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     mask_d.copy_(mask_h.view(torch.uint8), non_blocking=True)
     sfm = SfmTable(points, point_indices, names, dev)
     res = points_from_views(config, depth_d, mask_d, image_h, K, c2w, names, points, point_indices, dev,
-                            image_kind, sample_idx, sfm=sfm)
-    rgb_h = torch.empty(res.rgb.shape, dtype=torch.float32, pin_memory=True)
-    rgb_h.copy_(res.rgb, non_blocking=True)
+                            image_kind, sample_idx, sfm=sfm, exchange=exchange)
+    if exchange is not None:  # res.rgb is the whole scene: this rank's rows go back to its host
+        r0 = res.extras["row_offset"]
+        rgb_local = res.rgb[r0:r0 + res.total]
+    else:
+        rgb_local = res.rgb
+    rgb_h = torch.empty(rgb_local.shape, dtype=torch.float32, pin_memory=True)
+    rgb_h.copy_(rgb_local, non_blocking=True)
     counts_h = torch.empty(res.view_counts.shape, dtype=torch.int64, pin_memory=True)
     counts_h.copy_(res.view_counts, non_blocking=True)
     torch.cuda.current_stream().synchronize()

@@ -265,6 +265,21 @@ int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
                     void* stream);
 
 /*
+ * a10/a11 with the exchange step of a multi-GPU run fused in (replaces the torch.cat of
+ * monocular_depth_init.py:183-184 across ranks): every kept point of this GPU is written to n_dst
+ * clouds -- its own and its NVLink peers', mapped into this address space by the caller (CUDA IPC /
+ * symmetric memory) -- at row row_offset + its local slot, so that after all ranks have run it and
+ * met at a barrier every destination holds the whole scene in view order.  xyz_dst / rgb_dst are
+ * HOST arrays of n_dst device pointers (either may be NULL to skip that array), n_dst <= 16.
+ */
+#define MDI_MAX_EMIT_DST 16
+int mdi_emit_points_multi(const MdiView* views, int n_views, int64_t total_tiles,
+                          const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
+                          const int64_t* view_offsets, int image_kind, int n_dst,
+                          float* const* xyz_dst, float* const* rgb_dst, int64_t row_offset,
+                          void* stream);
+
+/*
  * a13: minimal Gaussian extent per point over all cameras that see it (else -1).
  *   K float32 [C,9], P float32 [C,12], sizes int32 [C,2] = (W,H).
  */

@@ -2,8 +2,10 @@
 variable-length all-gather of the per-rank clouds (output must equal the 1-rank order)."""
 import os
 import socket
+from pathlib import Path
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -59,3 +61,19 @@ def test_allgather_points_handles_an_empty_rank():
     mp.spawn(_worker, args=(world, _free_port(), counts, out), nprocs=world, join=True)
     for r in range(world):
         assert out[r][0].shape == (4, 3) and out[r][2].tolist() == counts
+
+
+@pytest.mark.gpu
+def test_fused_emit_exchange_matches_allgather_and_single_gpu():
+    """2+ GPUs only (the round-end GPU box has one: skipped there; run by hand with gpurun --gpus 2)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    n = min(torch.cuda.device_count(), 4)
+    script = str(Path(__file__).resolve().parent / "exchange_check.py")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", script],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "exchange ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
