@@ -290,6 +290,13 @@ class Engine:
         slots = int(sfm_begin[-1]) + 4
         res = RunResult(n_views=V, px_begin=px_begin, sfm_begin=sfm_begin)
         if V == 0:
+            if opt.exchange is not None and opt.stop_after is None and (opt.want_xyz or opt.want_rgb):
+                # a rank without views still takes part in the collective exchange
+                row_offset, _, counts = opt.exchange.begin(0)
+                res.total = 0
+                res.xyz, res.rgb = opt.exchange.finish()
+                res.extras["rank_counts"] = counts
+                res.extras["row_offset"] = row_offset
             return res
         # a1: cameras.  One upload: [descriptors][K][cam2world][inv(K) unless pinhole]
         kn = np.ascontiguousarray(vin.K.detach().cpu().numpy(), dtype=np.float32).reshape(V, 3, 3)

@@ -73,7 +73,8 @@ def test_fused_emit_exchange_matches_allgather_and_single_gpu():
         pytest.skip("needs at least 2 GPUs")
     n = min(torch.cuda.device_count(), 4)
     script = str(Path(__file__).resolve().parent / "exchange_check.py")
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
-                        "--master-addr", "127.0.0.1", "--master-port", "29533", script],
-                       capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and "exchange ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+    for views in ("11", "1"):  # "1": every rank but the first has no view at all
+        r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                            "--master-addr", "127.0.0.1", "--master-port", "29533", script],
+                           capture_output=True, text=True, timeout=600, env={**os.environ, "MDI_CHECK_VIEWS": views})
+        assert r.returncode == 0 and "exchange ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
