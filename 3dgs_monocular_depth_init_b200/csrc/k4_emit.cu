@@ -94,7 +94,14 @@ struct EmitDst {
   int64_t row_offset;  // first row of this GPU's points in the destination clouds
   float* xyz[MDI_MAX_EMIT_DST];
   float* rgb[MDI_MAX_EMIT_DST];
+  // NVSwitch multicast addresses of the same clouds (n == 0): one multimem store reaches every GPU
+  float* mc_xyz;
+  float* mc_rgb;
 };
+
+__device__ __forceinline__ void multicast_store(float* addr, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
 
 template <int IMAGE_KIND>
 __global__ void __launch_bounds__(kEmitWarps * 32)
@@ -104,7 +111,8 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
                    int64_t total_tiles, EmitDst dst) {
   __shared__ uint16_t s_px[kEmitWarps][kEmitList];
   __shared__ float s_rec[kEmitWarps][2][96];  // one warp-iteration of xyz / rgb records
-  const bool want_xyz = dst.xyz[0] != nullptr, want_rgb = dst.rgb[0] != nullptr;
+  const bool want_xyz = dst.xyz[0] != nullptr || dst.mc_xyz != nullptr;
+  const bool want_rgb = dst.rgb[0] != nullptr || dst.mc_rgb != nullptr;
   const int64_t tile = (int64_t)blockIdx.x * kEmitWarps + warp_id();
   if (tile >= total_tiles) return;
   const int lane = lane_id();
@@ -182,6 +190,16 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
       // (this GPU's and, through NVLink, its peers'): three fully coalesced stores per array
       const int n_words = 3 * min(32, n_here - j0);
       const int64_t w0 = 3 * (out0 + base + j0);
+      if (dst.n == 0) {  // the switch replicates the store into every GPU's cloud (this one included)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int w = 32 * k + lane;
+          if (w < n_words) {
+            if (dst.mc_xyz) multicast_store(dst.mc_xyz + w0 + w, rec_xyz[w]);
+            if (dst.mc_rgb) multicast_store(dst.mc_rgb + w0 + w, rec_rgb[w]);
+          }
+        }
+      }
       for (int d = 0; d < dst.n; ++d) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -278,4 +296,17 @@ extern "C" int mdi_emit_points_multi(const MdiView* views, int n_views, int64_t 
   }
   return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
                      dst, stream, "mdi_emit_points_multi");
+}
+
+extern "C" int mdi_emit_points_multicast(const MdiView* views, int n_views, int64_t total_tiles,
+                                         const float* scale_shift, const uint32_t* bits,
+                                         const int64_t* tile_offsets, const int64_t* view_offsets,
+                                         int image_kind, float* xyz_mc, float* rgb_mc, int64_t row_offset,
+                                         void* stream) {
+  MDI_REQUIRE(row_offset >= 0, "mdi_emit_points_multicast: negative row_offset");
+  MDI_REQUIRE(xyz_mc || rgb_mc, "mdi_emit_points_multicast: no destination");
+  mdi::EmitDst dst{};
+  dst.n = 0; dst.row_offset = row_offset; dst.mc_xyz = xyz_mc; dst.mc_rgb = rgb_mc;
+  return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
+                     dst, stream, "mdi_emit_points_multicast");
 }

@@ -454,7 +454,12 @@ class Engine:
             # multi-GPU: the emit kernel writes this rank's points into every rank's cloud
             ex = opt.exchange
             row_offset, total_all, counts = ex.begin(N)
-            if N:
+            if N and ex.use_multicast:
+                L.check(lib.mdi_emit_points_multicast(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
+                                                      res.view_offsets.data_ptr(), int(vin.image_kind), ex.xyz_mc,
+                                                      ex.rgb_mc if vin.image is not None else None, int(row_offset),
+                                                      st), "mdi_emit_points_multicast")
+            elif N:
                 n_dst = ex.world
                 xp = (C.c_void_p * n_dst)(*ex.xyz_ptrs)
                 rp = (C.c_void_p * n_dst)(*ex.rgb_ptrs) if vin.image is not None else None

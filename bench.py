@@ -185,7 +185,8 @@ def run_ours(args):
     if world > 1:
         try:
             exchange = dmod.CloudExchange(dev, capacity_rows=1 << 22)
-            gather = "emit kernel writes peer clouds over NVLink (symmetric memory)"
+            gather = ("emit kernel writes every rank's cloud through NVSwitch multicast (multimem.st)" if exchange.use_multicast
+                      else "emit kernel writes peer clouds over NVLink (symmetric memory)")
         except Exception as e:  # noqa: BLE001 - any failure to map peer memory selects the NCCL path
             gather = f"nccl all_gather ({type(e).__name__})"
 

@@ -280,6 +280,16 @@ int mdi_emit_points_multi(const MdiView* views, int n_views, int64_t total_tiles
                           void* stream);
 
 /*
+ * Same exchange through NVSwitch multicast (NVLS): xyz_mc / rgb_mc are multicast addresses bound to
+ * the clouds of every GPU of the group (this one included), so one multimem.st per word reaches
+ * all of them -- egress per GPU is its own points once instead of once per peer.
+ */
+int mdi_emit_points_multicast(const MdiView* views, int n_views, int64_t total_tiles,
+                              const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
+                              const int64_t* view_offsets, int image_kind, float* xyz_mc, float* rgb_mc,
+                              int64_t row_offset, void* stream);
+
+/*
  * a13: minimal Gaussian extent per point over all cameras that see it (else -1).
  *   K float32 [C,9], P float32 [C,12], sizes int32 [C,2] = (W,H).
  */
