@@ -113,6 +113,7 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
   __shared__ float s_rec[kEmitWarps][2][96];  // one warp-iteration of xyz / rgb records
   const bool want_xyz = dst.xyz[0] != nullptr || dst.mc_xyz != nullptr;
   const bool want_rgb = dst.rgb[0] != nullptr || dst.mc_rgb != nullptr;
+  const bool direct = dst.n == 1;
   const int64_t tile = (int64_t)blockIdx.x * kEmitWarps + warp_id();
   if (tile >= total_tiles) return;
   const int lane = lane_id();
@@ -171,7 +172,12 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
               r = fdiv(r, 255.0f); g = fdiv(g, 255.0f); bl = fdiv(bl, 255.0f);
             }
           }
-          rec_rgb[3 * lane] = r; rec_rgb[3 * lane + 1] = g; rec_rgb[3 * lane + 2] = bl;
+          if (direct) {
+            float* o = dst.rgb[0] + 3 * (out0 + base + j);
+            o[0] = r; o[1] = g; o[2] = bl;
+          } else {
+            rec_rgb[3 * lane] = r; rec_rgb[3 * lane + 1] = g; rec_rgb[3 * lane + 2] = bl;
+          }
         }
         if (want_xyz) {
           const float px = fmul(fadd((float)col, 0.5f), z);
@@ -180,11 +186,18 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
           const float cx = dot3_kinv(Ki[0], Ki[1], Ki[2], px, py, z);
           const float cy = dot3_kinv(Ki[3], Ki[4], Ki[5], px, py, z);
           const float cz = dot3_kinv(Ki[6], Ki[7], Ki[8], px, py, z);
-          rec_xyz[3 * lane] = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
-          rec_xyz[3 * lane + 1] = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
-          rec_xyz[3 * lane + 2] = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
+          const float wx = dot4_fma(M[0], M[1], M[2], M[3], cx, cy, cz);
+          const float wy = dot4_fma(M[4], M[5], M[6], M[7], cx, cy, cz);
+          const float wz = dot4_fma(M[8], M[9], M[10], M[11], cx, cy, cz);
+          if (direct) {
+            float* o = dst.xyz[0] + 3 * (out0 + base + j);
+            o[0] = wx; o[1] = wy; o[2] = wz;
+          } else {
+            rec_xyz[3 * lane] = wx; rec_xyz[3 * lane + 1] = wy; rec_xyz[3 * lane + 2] = wz;
+          }
         }
       }
+      if (direct) continue;  // one local cloud: every lane has stored its own record
       __syncwarp();
       // the records of this iteration are one contiguous run of words in every destination cloud
       // (this GPU's and, through NVLink, its peers'): three fully coalesced stores per array

@@ -14,7 +14,7 @@ import torch
 
 from . import _lib as L
 from ._single import options_from_config, ransac_seed
-from .engine import ViewInputs, get_engine
+from .engine import RunResult, ViewInputs, get_engine
 from .knn import knn
 from .point_cloud_postprocess.postprocess import postprocess_point_cloud
 from .types import InputImage
@@ -64,10 +64,22 @@ class SfmTable:
         xyz_t = torch.empty((int(pts_np.shape[0]), 3), dtype=torch.float32, pin_memory=use_pin)
         np.copyto(xyz_t.numpy(), pts_np.reshape(-1, 3), casting="same_kind")
         self.counts = counts
+        self.begin = begin
         self.host_bytes = int(pts_np.shape[0]) * 12 + idx.nbytes
         self.xyz = xyz_t.to(device, non_blocking=True)
         self.index = idx_t.to(device, non_blocking=True)
         self._staging = (xyz_t, idx_t)  # keep the pinned buffers alive until the copies have run
+
+    def slice(self, a: int, b: int) -> "SfmTable":
+        """The table of views a..b-1 (shares the uploaded arrays)."""
+        t = object.__new__(SfmTable)
+        t.counts = self.counts[a:b]
+        t.begin = self.begin[a:b + 1] - self.begin[a]
+        t.host_bytes = 0
+        t.xyz = self.xyz
+        t.index = self.index[int(self.begin[a]):]
+        t._staging = self._staging
+        return t
 
 
 @torch.no_grad()
@@ -149,23 +161,61 @@ def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth
 
 @torch.no_grad()
 def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, points, point_indices, device,
-                           image_kind: int = L.IMAGE_U8, sample_idx: Optional[torch.Tensor] = None, exchange=None):
+                           image_kind: int = L.IMAGE_U8, sample_idx: Optional[torch.Tensor] = None, exchange=None,
+                           chunks: int = 1):
     """End-to-end form of the hot path for HOST inputs (what a dataset loader hands over):
     depth [V,H,W] float32 and mask [V,H,W] bool in pinned host memory are copied to the device,
     the image [V,H,W,3] stays in pinned host memory and only its kept pixels are read over PCIe by
     the gather kernel; rgb comes back to the host (the reference returns rgbs on the CPU,
     monocular_depth_init.py:168), xyz stays on the device.
+    With chunks > 1 the views go through in blocks: all host->device copies are queued on a copy
+    stream up front and block c is processed while blocks c+1.. are still in flight.  Measured on a
+    B200 this does NOT pay (23.4 ms at 1 block, 24.8 at 4, 26.4 at 8 for the 200-view C2 scene): the
+    in-place image reads of a block's emit kernel compete with the bulk copies for the same PCIe
+    direction, so the default stays one block (always one when `exchange` is given).
     Returns (RunResult, rgb_host, h2d_bytes, d2h_bytes)."""
     eng = get_engine(device)
     dev = eng.device
     assert depth_h.is_pinned() and mask_h.is_pinned() and image_h.is_pinned()
+    V = int(depth_h.shape[0])
     depth_d = eng._buf("e2e_depth", depth_h.numel(), torch.float32).view(depth_h.shape)
     mask_d = eng._buf("e2e_mask", mask_h.numel(), torch.uint8).view(mask_h.shape)
-    depth_d.copy_(depth_h, non_blocking=True)
-    mask_d.copy_(mask_h.view(torch.uint8), non_blocking=True)
-    sfm = SfmTable(points, point_indices, names, dev)
-    res = points_from_views(config, depth_d, mask_d, image_h, K, c2w, names, points, point_indices, dev,
-                            image_kind, sample_idx, sfm=sfm, exchange=exchange)
+    mask_u8 = mask_h.view(torch.uint8)
+    n_chunks = 1 if (exchange is not None or V == 0) else max(1, min(int(chunks), V))
+    bounds = [(c * V) // n_chunks for c in range(n_chunks + 1)]
+    main = torch.cuda.current_stream(dev)
+    if not hasattr(eng, "_copy_stream"):
+        eng._copy_stream = torch.cuda.Stream(dev)
+    cs = eng._copy_stream
+    cs.wait_stream(main)  # earlier work may still be reading the staging buffers
+    arrived = []
+    with torch.cuda.stream(cs):
+        for c in range(n_chunks):
+            a, b = bounds[c], bounds[c + 1]
+            depth_d[a:b].copy_(depth_h[a:b], non_blocking=True)
+            mask_d[a:b].copy_(mask_u8[a:b], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+            arrived.append(ev)
+    sfm = SfmTable(points, point_indices, names, dev)  # host work, overlaps the copies
+    parts = []
+    for c in range(n_chunks):
+        a, b = bounds[c], bounds[c + 1]
+        main.wait_event(arrived[c])
+        parts.append(points_from_views(config, depth_d[a:b], mask_d[a:b], image_h[a:b], K[a:b], c2w[a:b], names[a:b],
+                                       points, point_indices, dev, image_kind,
+                                       sample_idx[a:b] if sample_idx is not None else None,
+                                       sfm=sfm if n_chunks == 1 else sfm.slice(a, b), exchange=exchange))
+    if n_chunks == 1:
+        res = parts[0]
+    else:
+        res = RunResult(n_views=V, px_begin=None, sfm_begin=None)
+        res.xyz = torch.cat([p.xyz for p in parts], dim=0)
+        res.rgb = torch.cat([p.rgb for p in parts], dim=0)
+        res.view_counts = torch.cat([p.view_counts for p in parts])
+        res.status = torch.cat([p.status for p in parts])
+        res.scale_shift = torch.cat([p.scale_shift for p in parts])
+        res.total = sum(p.total for p in parts)
     if exchange is not None:  # res.rgb is the whole scene: this rank's rows go back to its host
         r0 = res.extras["row_offset"]
         rgb_local = res.rgb[r0:r0 + res.total]
@@ -175,9 +225,9 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     rgb_h.copy_(rgb_local, non_blocking=True)
     counts_h = torch.empty(res.view_counts.shape, dtype=torch.int64, pin_memory=True)
     counts_h.copy_(res.view_counts, non_blocking=True)
-    torch.cuda.current_stream().synchronize()
+    main.synchronize()
     h2d = depth_h.numel() * 4 + mask_h.numel() + res.total * 3 * image_h.element_size() \
         + sfm.host_bytes + len(names) * (L.VIEW_DTYPE.itemsize + 25 * 4)
-    d2h = res.total * 12 + counts_h.numel() * 8 + 8
-    res.extras = {"counts_host": counts_h}
+    d2h = res.total * 12 + counts_h.numel() * 8 + 8 * n_chunks
+    res.extras = dict(res.extras or {}, counts_host=counts_h, chunks=n_chunks)
     return res, rgb_h, int(h2d), int(d2h)

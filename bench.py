@@ -48,7 +48,9 @@ def make_config(aligner, subsample):
 
 
 class ClockSampler:
-    """nvidia-smi clock / throttle-reason samples during the timed region."""
+    """SM clock / throttle-reason samples during the timed region: NVML from a thread (a few
+    microseconds per query; a looping nvidia-smi process was seen to disturb the PCIe-bound end-to-end
+    steps), nvidia-smi only if NVML cannot be loaded."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -56,13 +58,50 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.rows, self.proc = index, [], None
+        self.sm, self.mx, self.reasons, self._stop, self.thread, self.source = [], [], set(), False, None, None
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            bits = {"hw_slowdown": pynvml.nvmlClocksEventReasonHwSlowdown if hasattr(pynvml, "nvmlClocksEventReasonHwSlowdown")
+                    else pynvml.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown",
+                                                   getattr(pynvml, "nvmlClocksThrottleReasonHwThermalSlowdown", 0)),
+                    "sw_thermal_slowdown": getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown",
+                                                   getattr(pynvml, "nvmlClocksThrottleReasonSwThermalSlowdown", 0)),
+                    "sw_power_cap": getattr(pynvml, "nvmlClocksEventReasonSwPowerCap",
+                                            getattr(pynvml, "nvmlClocksThrottleReasonSwPowerCap", 0))}
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons",
+                                  getattr(pynvml, "nvmlDeviceGetCurrentClocksThrottleReasons", None))
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)))
+
+            def loop():
+                while not self._stop:
+                    try:
+                        self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                        if get_reasons is not None:
+                            r = int(get_reasons(h))
+                            for n, b in bits.items():
+                                if b and (r & int(b)):
+                                    self.reasons.add(n)
+                    except Exception:  # noqa: BLE001
+                        pass
+                    time.sleep(0.02)
+
+            self.thread = threading.Thread(target=loop, daemon=True)
+            self.thread.start()
+            self.source = "nvml"
+            return
+        except Exception:  # noqa: BLE001 - no NVML binding: fall back to the nvidia-smi loop
+            self.thread = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
+            self.source = "nvidia-smi"
         except OSError:
             self.proc = None
 
@@ -71,6 +110,12 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self) -> dict:
+        if self.thread is not None:
+            self._stop = True
+            self.thread.join(timeout=1.0)
+            sm = sorted(self.sm)
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                    "reasons": sorted(self.reasons), "samples": len(sm), "source": "nvml"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -87,7 +132,7 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
 def algorithmic_bytes(kernel: str, HW: int, V: int, n_kept: int, n_sfm_slots: int, adaptive: bool) -> float:

@@ -275,3 +275,29 @@ def test_quantile_one_pass_path_equals_exact_path_and_torch():
         if expect_retry is not None:
             assert bool(fast.extras.get("stats_retry", False)) == expect_retry, name
         assert not exact.extras.get("stats_retry", False)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks", [1, 3, 16])
+def test_host_views_end_to_end_path_equals_resident_path(chunks):
+    """points_from_host_views (pinned host depth / mask / image, chunked copy-compute overlap, rgb
+    back on the host) gives the cloud of the resident path, whatever the chunking."""
+    syn = mod("synthetic")
+    mdi = mod("monocular_depth_init")
+    L = mod("_lib")
+    sc = syn.make_scene(n_views=7, H=120, W=160, n_sfm=2500, seed=13, low_conf_every=3)
+    cfg = mod("config").Config()
+    cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum("lstsqrs")
+    cfg.mdi.subsample_factor = "adaptive"
+    ref = mdi.points_from_views(cfg, sc.depth.to(DEV), sc.mask.to(DEV), sc.image.to(DEV), sc.K, sc.c2w, sc.names,
+                                sc.points, sc.point_indices, DEV, L.IMAGE_U8)
+    for _ in range(2):  # twice: the staging buffers are reused
+        res, rgb_h, h2d, d2h = mdi.points_from_host_views(
+            cfg, sc.depth.pin_memory(), sc.mask.pin_memory(), sc.image.pin_memory(), sc.K, sc.c2w, sc.names,
+            sc.points, sc.point_indices, DEV, L.IMAGE_U8, chunks=chunks)
+        assert res.extras["chunks"] == min(chunks, 7)
+        assert res.total == ref.total and torch.equal(res.xyz, ref.xyz)
+        assert torch.equal(rgb_h, ref.rgb.cpu())
+        assert torch.equal(res.view_counts, ref.view_counts) and torch.equal(res.status, ref.status)
+        assert torch.equal(res.extras["counts_host"], ref.view_counts.cpu())
+        assert h2d > sc.depth.numel() * 4 and d2h >= res.total * 12
