@@ -25,6 +25,7 @@ STATS_EXACT, STATS_RETRY_FLAGGED = 64, 128
 IMAGE_F32_UNIT, IMAGE_F32_255, IMAGE_U8 = 0, 1, 2
 SUBSAMPLE_STATIC, SUBSAMPLE_ADAPTIVE = 0, 1
 KEEP_PRED_MASK, KEEP_SENTINEL, KEEP_NONNEG, KEEP_PATCH, KEEP_GRAD, KEEP_SUBSAMPLE = 1, 2, 4, 8, 16, 32
+KEEP_PREZEROED = 256
 LOSS_RANSAC, LOSS_MSAC = 0, 1
 
 # struct MdiView (align=True reproduces the C layout; checked against mdi_sizeof_view)

@@ -133,7 +133,7 @@ constexpr int kCtaPoints = kChunk * kLatticeWarps;     // lattice points per CTA
 // + l (u < 8): the 8 depth loads are issued together, then the stride test, then the predicted-
 // mask loads of the survivors together, then their patch lookups together.
 // grid = (ceil(max lattice points / kCtaPoints), n_strides, n_views)
-__global__ void __launch_bounds__(kLatticeWarps * 32)
+__global__ void __launch_bounds__(kLatticeWarps * 32, 6)
 keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
                     const int32_t* __restrict__ status, const float* __restrict__ lo_hi,
                     const float* __restrict__ grad_range, const uint8_t* __restrict__ patch_blocked,
@@ -336,10 +336,12 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
   }
   MDI_REQUIRE(!(prm.flags & MDI_KEEP_GRAD) || grad_range, "mdi_keep_mask: grad flag needs grad_range");
   cudaStream_t st = (cudaStream_t)stream;
-  mdi::prof_mark("keep_zero_fill", st);
-  if (keep) MDI_CUDA(cudaMemsetAsync(keep, 0, (size_t)total_px, st), "mdi_keep_mask memset");
-  MDI_CUDA(cudaMemsetAsync(bits, 0, (size_t)total_tiles * MDI_TILE_WORDS * 4, st), "mdi_keep_mask memset");
-  MDI_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)total_tiles * 4, st), "mdi_keep_mask memset");
+  if (!(prm.flags & MDI_KEEP_PREZEROED)) {
+    mdi::prof_mark("keep_zero_fill", st);
+    if (keep) MDI_CUDA(cudaMemsetAsync(keep, 0, (size_t)total_px, st), "mdi_keep_mask memset");
+    MDI_CUDA(cudaMemsetAsync(bits, 0, (size_t)total_tiles * MDI_TILE_WORDS * 4, st), "mdi_keep_mask memset");
+    MDI_CUDA(cudaMemsetAsync(tile_counts, 0, (size_t)total_tiles * 4, st), "mdi_keep_mask memset");
+  }
   // the lattice kernel indexes pixels and coordinates in 32 / 16 bits
   if (lattice && max_height > 0 && max_width > 0 && max_height < 65536 && max_width < 65536) {
     const int64_t max_pts = (int64_t)((max_height + min_stride - 1) / min_stride) *

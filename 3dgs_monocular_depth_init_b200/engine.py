@@ -283,6 +283,8 @@ class Engine:
     # ---- the pipeline -------------------------------------------------------------------------
     def run(self, vin: ViewInputs, opt: RunOptions) -> RunResult:
         lib, st = self.lib, _stream()
+        run_start = torch.cuda.Event()
+        run_start.record()
         V = int(vin.K.shape[0])
         desc, px_begin, tile_begin, sfm_begin = self.build_views(vin, opt)
         total_tiles = int(tile_begin[-1])
@@ -417,6 +419,22 @@ class Engine:
         bits = self._buf("bits", total_tiles * L.TILE_WORDS, i32)
         tile_counts = self._buf("tile_counts", total_tiles, i32)
         tile_offsets = self._buf("tile_offsets", total_tiles, torch.int64)
+        # zero-fill of the mask outputs on a side stream: it only has to wait for what was queued before
+        # this call, so it runs under the alignment / statistics kernels instead of after them
+        main = torch.cuda.current_stream(self.device)
+        if not hasattr(self, "_zero_stream"):
+            self._zero_stream = torch.cuda.Stream(self.device)
+        zs = self._zero_stream
+        zs.wait_event(run_start)
+        with torch.cuda.stream(zs):
+            if res.keep is not None:
+                res.keep.record_stream(zs)
+                res.keep.zero_()
+            bits.zero_()
+            tile_counts.zero_()
+            zero_done = torch.cuda.Event()
+            zero_done.record(zs)
+        prezeroed = [True]
 
         def mask_stage(stats_mode: int):
             """a7 statistics -> a5-a10 keep mask -> compaction offsets; returns (total, retry)."""
@@ -427,6 +445,12 @@ class Engine:
                                             meta[2 * V + 1:].data_ptr(), st), "mdi_depth_range")
                 L.check(lib.mdi_factor_table(V, res.lo_hi.data_ptr(), int(opt.factor_min), int(opt.factor_max),
                                              ftab.data_ptr(), st), "mdi_factor_table")
+            if prezeroed[0]:
+                main.wait_event(zero_done)
+                scfg.flags = int(flags) | L.KEEP_PREZEROED
+                prezeroed[0] = False
+            else:  # the exact-statistics retry fills again, in stream order
+                scfg.flags = int(flags)
             L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), int(desc["W"].max()), ssp,
                                       res.status.data_ptr(), L.ptr(res.lo_hi), L.ptr(res.grad_range),
                                       L.ptr(res.patch_blocked), L.ptr(ftab), C.byref(scfg), L.ptr(res.keep),

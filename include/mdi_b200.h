@@ -79,6 +79,8 @@ extern "C" {
 #define MDI_KEEP_PATCH 8      /* & SfM-density patch mask               (points_from_depth.py:276) */
 #define MDI_KEEP_GRAD 16      /* & depth-gradient mask                  (points_from_depth.py:271) */
 #define MDI_KEEP_SUBSAMPLE 32 /* & subsampler mask                      (points_from_depth.py:290) */
+#define MDI_KEEP_PREZEROED 256 /* keep / bits / tile_counts were zero-filled by the caller (e.g. on a
+                                 side stream, overlapped with the alignment stages)              */
 
 /* mdi_depth_range algorithm selection (OR-ed into its flags) */
 #define MDI_STATS_EXACT 64          /* three-pass radix select over all pixels, every view      */
