@@ -224,14 +224,28 @@ class Engine:
         else:
             for t in vin.depth:
                 assert t.dtype == torch.float32 and t.is_cuda
+        counts = (np.asarray(vin.sfm_counts, dtype=np.int64) if vin.sfm_counts is not None
+                  else np.zeros(V, dtype=np.int64))
+        # everything but the three pointer columns depends only on the shapes, the SfM counts and the
+        # patch option: kept from the previous call when those repeat (same scene again, equal chunks)
+        key = (V, tuple(dshapes) if not isinstance(vin.depth, torch.Tensor) else ("stacked",) + tuple(vin.depth.shape),
+               counts.tobytes(), bool(opt.use_patch_mask), int(opt.num_patches_small_axis))
+        cached = getattr(self, "_geom_cache", None)
+        if cached is not None and cached[0] == key:
+            desc, px_begin, tile_begin, sfm_begin = (a.copy() for a in cached[1])
+        else:
+            desc, px_begin, tile_begin, sfm_begin = self._build_geometry(V, dshapes, counts, opt)
+            self._geom_cache = (key, tuple(a.copy() for a in (desc, px_begin, tile_begin, sfm_begin)))
+        desc["depth"], desc["mask"], desc["image"] = dptr, mptr, iptr
+        return desc, px_begin, tile_begin, sfm_begin
+
+    @staticmethod
+    def _build_geometry(V, dshapes, counts, opt):
         Hs = np.array([s[0] for s in dshapes], dtype=np.int64)
         Ws = np.array([s[1] for s in dshapes], dtype=np.int64)
         HW = Hs * Ws
         desc = np.zeros(V, dtype=L.VIEW_DTYPE)
-        desc["depth"], desc["mask"], desc["image"] = dptr, mptr, iptr
         desc["H"], desc["W"] = Hs, Ws
-        counts = (np.asarray(vin.sfm_counts, dtype=np.int64) if vin.sfm_counts is not None
-                  else np.zeros(V, dtype=np.int64))
         padded = (counts + 3) & ~3  # 16-byte aligned slot ranges (bulk copies in mdi_ransac)
         sfm_begin = np.zeros(V + 1, dtype=np.int64)
         np.cumsum(padded, out=sfm_begin[1:])

@@ -1,0 +1,30 @@
+import sys, importlib
+sys.path.insert(0, "/root/repo")
+import torch
+from torch.profiler import profile, ProfilerActivity
+PKG = "3dgs_monocular_depth_init_b200"
+mod = lambda n: importlib.import_module(PKG + "." + n)
+L = mod("_lib"); mdi = mod("monocular_depth_init"); syn = mod("synthetic")
+dev = torch.device("cuda", 0)
+cfg = mod("config").Config()
+cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum("ransac")
+cfg.mdi.subsample_factor = "adaptive"
+sc = syn.make_scene(n_views=200, H=840, W=1297, n_sfm=5000, seed=1, device=str(dev), low_conf_every=50)
+sfm = mdi.SfmTable(sc.points, sc.point_indices, sc.names, dev)
+def step():
+    return mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points, sc.point_indices, dev, L.IMAGE_U8, sfm=sfm)
+for _ in range(5): step()
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+    for _ in range(4): step()
+    torch.cuda.synchronize()
+evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+evs.sort(key=lambda e: e.time_range.start)
+# last step: find the last setup_cameras kernel
+idx = max(i for i, e in enumerate(evs) if "setup_cameras" in e.name)
+prev_end = None
+t0 = evs[idx].time_range.start
+for e in evs[idx - 3:]:
+    gap = (e.time_range.start - prev_end) if prev_end is not None else 0
+    print(f"{(e.time_range.start - t0):9.1f} us  dur {e.time_range.end - e.time_range.start:8.1f}  gap {gap:7.1f}  {e.name[:60]}")
+    prev_end = max(prev_end or 0, e.time_range.end)
