@@ -19,6 +19,9 @@
 //
 // Exact path (three streaming passes): 12/12/8-bit radix select on order-preserving keys over
 // all pixels, shared-memory histograms, one-CTA-per-view bin search after each pass.
+#include <stdlib.h>
+#include <string.h>
+
 #include "common.cuh"
 
 namespace mdi {
@@ -377,8 +380,15 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
     for (int g = 0; g < 2; ++g) {
       const uint32_t bl = s_bin[2 * g], bh = s_bin[2 * g + 1];
       // keys of bin b satisfy sort[b-1] < key <= sort[b]
-      const uint32_t L = bl == 0 ? 0u : s_sort[bl - 1] + (s_sort[bl - 1] == 0xFFFFFFFFu ? 0u : 1u);
-      const uint32_t U = bh >= 1024u ? 0xFFFFFFFFu : s_sort[bh];
+      uint32_t L = bl == 0 ? 0u : s_sort[bl - 1] + (s_sort[bl - 1] == 0xFFFFFFFFu ? 0u : 1u);
+      uint32_t U = bh >= 1024u ? 0xFFFFFFFFu : s_sort[bh];
+      // stats_main_tma_kernel tests the bracket with float comparisons, which agree with the key
+      // order for every non-NaN value as long as the bounds are finite-or-inf keys and L != key(+0),
+      // U != key(-0) (the one place where the two orders differ).  Widening a bracket is always safe.
+      if (L < 0x007FFFFFu) L = 0x007FFFFFu;        // key(-inf)
+      if (U > 0xFF800000u) U = 0xFF800000u;        // key(+inf)
+      if (L == 0x80000000u) L = 0x7FFFFFFFu;       // key(+0) -> key(-0)
+      if (U == 0x7FFFFFFFu) U = 0x80000000u;       // key(-0) -> key(+0)
       uint32_t bs = 0;
       while (((U - L) >> bs) >= (uint32_t)kBrBins) ++bs;
       h->br_lo[g] = L; h->br_hi[g] = U >= L ? U : L; h->br_shift[g] = bs;
@@ -500,6 +510,195 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   for (int i = threadIdx.x; i < 2 * kBrBins; i += kStatsThreads) {
     const uint32_t c = (&s_brhist[0][0])[i];
     if (c) atomicAdd(&ghist[i], c);
+  }
+}
+
+// ---- the same pass with the depth staged by TMA (experimental, opt-in) ---------------------------
+// The register-staged kernel above leaves the load schedule to ptxas (which sinks loads next to
+// their uses as soon as the arithmetic gets leaner) and pays ~34 instructions per pixel.  Here every
+// warp streams its share of the CTA's depth through its own ring of kTmaStages shared-memory
+// chunks with 1-D bulk copies (cp.async.bulk completing on an mbarrier; lane 0 issues, the warp
+// waits), three chunks always in flight and no CTA-wide barrier in the loop; the predicted
+// mask (whose per-view base is only 4-byte aligned in a stacked [V,H,W] tensor, too little for a
+// bulk copy) is read one chunk ahead into registers.  The per-pixel work is done in the float
+// domain -- a pixel outside the population becomes NaN, which fails every comparison and is
+// skipped by fminf / fmaxf; the bracket bounds are kept off +/-0 by stats_bracket_kernel so that
+// float and key comparisons agree -- and every lane stages its candidates in its own
+// shared-memory column: no vote, no prefix.
+constexpr int kTmaChunk = 256;    // pixels per staged chunk: one warp's step (1 KB of depth)
+constexpr int kTmaStages = 4;     // chunks in flight per warp
+constexpr int kColSlots = 24;     // candidate slots per lane
+constexpr int kTmaSmemBytes = (kStatsThreads / 32) * kTmaStages * kTmaChunk * 4 + (kStatsThreads / 32) * kColSlots * 32 * 4 + 2 * kBrBins * 4;
+
+template <bool kUseMask, bool kSentinel>
+__global__ void __launch_bounds__(kStatsThreads)
+stats_main_tma_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
+                      const int32_t* __restrict__ status, StatsWs ws) {
+  extern __shared__ __align__(128) unsigned char s_raw_tma[];
+  constexpr int kWarps = kStatsThreads / 32;
+  float* s_depth = reinterpret_cast<float*>(s_raw_tma);                                            // [warps][stages][chunk]
+  uint32_t* s_col = reinterpret_cast<uint32_t*>(s_raw_tma + kWarps * kTmaStages * kTmaChunk * 4); // [warps][slots][32]
+  uint32_t* s_brhist = s_col + kWarps * kColSlots * 32;                                            // [2][kBrBins]
+  __shared__ __align__(8) unsigned long long s_full[kWarps][kTmaStages];
+  __shared__ uint32_t s_min, s_max, s_cnt, s_below[2];
+  const int v = blockIdx.y;
+  const MdiView* vp = views + v;
+  const int first_tile = blockIdx.x * kStatsTilesPerCta;
+  if (first_tile >= vp->n_tiles) return;
+  if (status && (status[v] & MDI_STATUS_LOW_CONFIDENCE)) return;
+  StatsHdr* h = ws.hdr + v;
+  const uint32_t L0 = h->br_lo[0], L1 = h->br_lo[1];
+  const uint32_t W0 = h->br_hi[0] - L0, W1 = h->br_hi[1] - L1;
+  const uint32_t sh0 = h->br_shift[0], sh1 = h->br_shift[1];
+  const float fL0 = key_to_float(L0), fU0 = key_to_float(h->br_hi[0]);
+  const float fL1 = key_to_float(L1), fU1 = key_to_float(h->br_hi[1]);
+  const float* __restrict__ depth = vp->depth;
+  const uint8_t* __restrict__ pmask = kUseMask ? vp->mask : nullptr;
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const int64_t HW = (int64_t)vp->H * vp->W;
+  const int last_tile = min(first_tile + kStatsTilesPerCta, (int)vp->n_tiles);
+  const int64_t px_lo = (int64_t)first_tile * MDI_TILE_PX;
+  const int64_t px_hi = min((int64_t)last_tile * MDI_TILE_PX, HW);
+  const bool staged = ((reinterpret_cast<uintptr_t>(depth) & 15) == 0) &&
+                      (!pmask || (reinterpret_cast<uintptr_t>(pmask) & 3) == 0);
+  const int n_chunks = staged ? (int)((px_hi - px_lo) / kTmaChunk) : 0;  // whole chunks of the CTA
+  const int tid = threadIdx.x, lane = lane_id(), warp = warp_id();
+  // warp w takes chunks w, w + kWarps, ...
+  const int n_mine = n_chunks > warp ? (n_chunks - warp + kWarps - 1) / kWarps : 0;
+
+  for (int i = tid; i < 2 * kBrBins; i += kStatsThreads) s_brhist[i] = 0;
+  if (tid == 0) {
+    s_min = 0xFFFFFFFFu; s_max = 0u; s_cnt = 0u; s_below[0] = 0; s_below[1] = 0;
+    for (int i = 0; i < kWarps * kTmaStages; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_full[0][0] + i)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  float* my_depth = s_depth + warp * kTmaStages * kTmaChunk;
+  auto chunk_px = [&](int i) { return px_lo + (int64_t)(i * kWarps + warp) * kTmaChunk; };
+  auto issue = [&](int i) {  // lane 0: the warp's i-th chunk -> stage i % kTmaStages
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_full[warp][i % kTmaStages]);
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(my_depth + (i % kTmaStages) * kTmaChunk);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kTmaChunk * 4) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(depth + chunk_px(i)), "r"(kTmaChunk * 4), "r"(bar) : "memory");
+  };
+  if (lane == 0)
+    for (int i = 0; i < min(kTmaStages, n_mine); ++i) issue(i);
+
+  uint32_t cnt = 0, below0 = 0, below1 = 0, lcount = 0;
+  float vmin = INFINITY, vmax = -INFINITY;
+  bool any_nan = false;
+  uint32_t* cand = ws.cand + (int64_t)v * ws.c_cap;
+  uint32_t* col = s_col + (warp * kColSlots) * 32 + lane;  // slot j of this lane: col[32 * j]
+
+  auto feed = [&](float a, bool pop) {
+    if (kSentinel) pop = pop && (a != -42.0f);
+    const float g = pop ? a : __int_as_float(0x7fc00000);
+    vmin = fminf(vmin, g);
+    vmax = fmaxf(vmax, g);
+    cnt += pop ? 1u : 0u;
+    const bool lt0 = g < fL0, lt1 = g < fL1;
+    below0 += lt0 ? 1u : 0u;
+    below1 += lt1 ? 1u : 0u;
+    if ((!lt0 && g <= fU0) || (!lt1 && g <= fU1)) { col[32 * lcount] = fast_key(a); ++lcount; }
+  };
+  auto flush = [&]() {  // lane columns -> bracket histograms + the view's candidate list
+    const uint32_t total = __reduce_add_sync(0xffffffffu, lcount);
+    if (total == 0) return;
+    const uint32_t incl = (uint32_t)warp_incl_scan((int)lcount);
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(&h->n_cand, total);
+    base = __shfl_sync(0xffffffffu, base, 0) + incl - lcount;
+    for (uint32_t j = 0; j < lcount; ++j) {
+      const uint32_t key = col[32 * j];
+      const uint32_t o0 = key - L0, o1 = key - L1;
+      if (o0 <= W0) atomicAdd(&s_brhist[o0 >> sh0], 1u);
+      if (o1 <= W1) atomicAdd(&s_brhist[kBrBins + (o1 >> sh1)], 1u);
+      if ((int64_t)base + j < ws.c_cap) cand[base + j] = key;
+    }
+    __syncwarp();
+    lcount = 0;
+  };
+
+  // predicted mask of the lane's 8 pixels of a chunk: two 32-bit words, read one chunk ahead
+  auto load_mask = [&](int i, uint32_t (&mk)[2]) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+      mk[k] = pmask ? __ldg(reinterpret_cast<const uint32_t*>(pmask + chunk_px(i) + (k * 32 + lane) * 4)) : 0x01010101u;
+  };
+  uint32_t mk_cur[2] = {0, 0}, mk_next[2] = {0, 0};
+  if (n_mine > 0) load_mask(0, mk_cur);
+#pragma unroll 1
+  for (int i = 0; i < n_mine; ++i) {
+    if (i + 1 < n_mine) load_mask(i + 1, mk_next);
+    {  // wait for the chunk's bytes
+      const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_full[warp][i % kTmaStages]);
+      const uint32_t parity = (uint32_t)((i / kTmaStages) & 1);
+      uint32_t ok = 0;
+      while (!ok)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    }
+    const float4* sd = reinterpret_cast<const float4*>(my_depth + (i % kTmaStages) * kTmaChunk);
+    float a[8];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const float4 d4 = sd[k * 32 + lane];
+      a[4 * k] = align_depth(d4.x, s, t); a[4 * k + 1] = align_depth(d4.y, s, t);
+      a[4 * k + 2] = align_depth(d4.z, s, t); a[4 * k + 3] = align_depth(d4.w, s, t);
+    }
+    const float chk = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+    if (chk != chk) {  // some NaN (or inf - inf): look at the population exactly (rare, rolled)
+#pragma unroll 1
+      for (int j = 0; j < 8; ++j) {
+        const int64_t p = chunk_px(i) + ((j >> 2) * 32 + lane) * 4 + (j & 3);
+        const float av = align_depth(__ldg(&depth[p]), s, t);
+        if ((pmask ? __ldg(&pmask[p]) != 0 : true) && av != av) any_nan = true;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      feed(a[4 * k], (mk_cur[k] & 0xffu) != 0); feed(a[4 * k + 1], (mk_cur[k] & 0xff00u) != 0);
+      feed(a[4 * k + 2], (mk_cur[k] & 0xff0000u) != 0); feed(a[4 * k + 3], (mk_cur[k] & 0xff000000u) != 0);
+    }
+    mk_cur[0] = mk_next[0]; mk_cur[1] = mk_next[1];
+    __syncwarp();  // every lane is done with this stage: refill it
+    if (lane == 0 && i + kTmaStages < n_mine) issue(i + kTmaStages);
+    if (__any_sync(0xffffffffu, lcount + 8u > (uint32_t)kColSlots)) flush();  // a chunk adds <= 8 per lane
+  }
+  // whatever is not a whole staged chunk (ragged end of the view, or a misaligned view)
+  for (int64_t p0 = px_lo + (int64_t)n_chunks * kTmaChunk; p0 < px_hi; p0 += kStatsThreads) {  // uniform trips
+    const int64_t p = p0 + tid;
+    const bool in = p < px_hi;
+    const float av = align_depth(in ? __ldg(&depth[p]) : 0.f, s, t);
+    const bool pop = in && (pmask ? __ldg(&pmask[p]) != 0 : true);
+    feed(av, pop);
+    if (pop && av != av) any_nan = true;
+    if (__any_sync(0xffffffffu, lcount + 8u > (uint32_t)kColSlots)) flush();
+  }
+  flush();
+  uint32_t kmin = cnt ? fast_key(vmin) : 0xFFFFFFFFu;
+  uint32_t kmax = any_nan ? 0xFFFFFFFFu : (cnt ? fast_key(vmax) : 0u);
+  kmin = __reduce_min_sync(0xffffffffu, kmin);
+  kmax = __reduce_max_sync(0xffffffffu, kmax);
+  cnt = __reduce_add_sync(0xffffffffu, cnt);
+  below0 = __reduce_add_sync(0xffffffffu, below0);
+  below1 = __reduce_add_sync(0xffffffffu, below1);
+  if (lane == 0 && cnt) {
+    atomicMin(&s_min, kmin); atomicMax(&s_max, kmax); atomicAdd(&s_cnt, cnt);
+    atomicAdd(&s_below[0], below0); atomicAdd(&s_below[1], below1);
+  }
+  __syncthreads();
+  if (tid == 0 && s_cnt) {
+    atomicMin(&h->min_key, s_min); atomicMax(&h->max_key, s_max); atomicAdd(&h->count, s_cnt);
+    atomicAdd(&h->below[0], s_below[0]); atomicAdd(&h->below[1], s_below[1]);
+  }
+  uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;  // [2][kBrBins] of it
+  for (int i = tid; i < 2 * kBrBins; i += kStatsThreads) {
+    const uint32_t cbin = s_brhist[i];
+    if (cbin) atomicAdd(&ghist[i], cbin);
   }
 }
 
@@ -904,8 +1103,27 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     mdi::prof_mark("stats_bracket_kernel", st);
     stats_bracket_kernel<<<n_views, kBracketThreads, 0, st>>>(status, ws);
     const bool um = pop & MDI_KEEP_PRED_MASK, se = pop & MDI_KEEP_SENTINEL;
+    // 0: register-staged kernel (default), 1: TMA-staged kernel (MDI_STATS_MAIN=tma; bit-identical
+    // results, measured slower so far: 0.42 vs 0.33 ms on C2)
+    static int main_variant = -1;
+    if (main_variant < 0) {
+      const char* e = getenv("MDI_STATS_MAIN");
+      main_variant = (e && strcmp(e, "tma") == 0) ? 1 : 0;
+      if (main_variant == 1) {
+        cudaError_t a0 = cudaFuncSetAttribute(stats_main_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
+        cudaError_t a1 = cudaFuncSetAttribute(stats_main_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
+        cudaError_t a2 = cudaFuncSetAttribute(stats_main_tma_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
+        cudaError_t a3 = cudaFuncSetAttribute(stats_main_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
+        if (a0 != cudaSuccess || a1 != cudaSuccess || a2 != cudaSuccess || a3 != cudaSuccess) { cudaGetLastError(); main_variant = 0; }
+      }
+    }
     mdi::prof_mark("stats_main_kernel", st);
-    if (um && se) stats_main_kernel<true, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
+    if (main_variant == 1) {
+      if (um && se) stats_main_tma_kernel<true, true><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
+      else if (um) stats_main_tma_kernel<true, false><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
+      else if (se) stats_main_tma_kernel<false, true><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
+      else stats_main_tma_kernel<false, false><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
+    } else if (um && se) stats_main_kernel<true, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     else if (um) stats_main_kernel<true, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     else if (se) stats_main_kernel<false, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
     else stats_main_kernel<false, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
