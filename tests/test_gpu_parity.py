@@ -301,3 +301,16 @@ def test_host_views_end_to_end_path_equals_resident_path(chunks):
         assert torch.equal(res.view_counts, ref.view_counts) and torch.equal(res.status, ref.status)
         assert torch.equal(res.extras["counts_host"], ref.view_counts.cpu())
         assert h2d > sc.depth.numel() * 4 and d2h >= res.total * 12
+
+
+@pytest.mark.gpu
+def test_tma_staged_statistics_kernel_is_bit_identical():
+    """The opt-in TMA-staged statistics pass (MDI_STATS_MAIN=tma, chosen once per process) must pass
+    the same quantile and golden-view checks as the default kernel: run them in a child process."""
+    import os
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, "-m", "pytest", __file__, "-q", "-m", "gpu", "-x", "-k",
+                        "quantile_one_pass or golden or batched_scene"],
+                       capture_output=True, text=True, timeout=900, env={**os.environ, "MDI_STATS_MAIN": "tma"})
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
