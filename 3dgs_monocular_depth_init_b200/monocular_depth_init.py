@@ -44,6 +44,33 @@ def gather_scene(parser, device, depth_source: Callable):
     return depths, masks, images, torch.stack(Ks), torch.stack(c2ws), names
 
 
+class _PinnedPool:
+    """Grow-only pinned staging buffers reused across calls (a fresh pinned allocation is a
+    cudaHostAlloc: tens of milliseconds).  A buffer is handed out again only after the copy that
+    last used it has completed (event recorded by `mark`)."""
+
+    def __init__(self):
+        self._buf, self._ev = {}, {}
+
+    def get(self, name: str, shape, dtype) -> torch.Tensor:
+        n = int(np.prod(shape)) if len(shape) else 1
+        ev = self._ev.pop(name, None)
+        if ev is not None:
+            ev.synchronize()
+        t = self._buf.get(name)
+        if t is None or t.dtype != dtype or t.numel() < n:
+            t = self._buf[name] = torch.empty(max(n, 1), dtype=dtype, pin_memory=True)
+        return t[:n].view(*shape)
+
+    def mark(self, name: str) -> None:
+        ev = torch.cuda.Event()
+        ev.record()
+        self._ev[name] = ev
+
+
+_PINNED = _PinnedPool()
+
+
 class SfmTable:
     """Device-resident SfM inputs of a scene: parser.points and the per-view index lists
     (parser.point_indices) concatenated into 16-byte aligned slot ranges."""
@@ -54,21 +81,30 @@ class SfmTable:
         padded = (counts + 3) & ~3
         begin = np.zeros(len(lists) + 1, dtype=np.int64)
         np.cumsum(padded, out=begin[1:])
-        # staged in pinned memory (torch caches the allocation) so both uploads are asynchronous
+        # staged in reused pinned memory so both uploads are asynchronous
         use_pin = torch.device(device).type == "cuda"
-        idx_t = torch.zeros(int(begin[-1]) + 4, dtype=torch.int32, pin_memory=use_pin)
+        n_idx = int(begin[-1]) + 4
+        pts_np = np.asarray(points)
+        if use_pin:
+            idx_t = _PINNED.get("sfm_idx", (n_idx,), torch.int32)
+            idx_t.zero_()
+            xyz_t = _PINNED.get("sfm_xyz", (int(pts_np.shape[0]), 3), torch.float32)
+        else:
+            idx_t = torch.zeros(n_idx, dtype=torch.int32)
+            xyz_t = torch.empty((int(pts_np.shape[0]), 3), dtype=torch.float32)
         idx = idx_t.numpy()
         for b, a in zip(begin[:-1].tolist(), lists):  # one slice copy per view
             idx[b:b + len(a)] = a
-        pts_np = np.asarray(points)
-        xyz_t = torch.empty((int(pts_np.shape[0]), 3), dtype=torch.float32, pin_memory=use_pin)
         np.copyto(xyz_t.numpy(), pts_np.reshape(-1, 3), casting="same_kind")
         self.counts = counts
         self.begin = begin
         self.host_bytes = int(pts_np.shape[0]) * 12 + idx.nbytes
         self.xyz = xyz_t.to(device, non_blocking=True)
         self.index = idx_t.to(device, non_blocking=True)
-        self._staging = (xyz_t, idx_t)  # keep the pinned buffers alive until the copies have run
+        if use_pin:
+            with torch.cuda.device(self.xyz.device):
+                _PINNED.mark("sfm_idx"); _PINNED.mark("sfm_xyz")
+        self._staging = (xyz_t, idx_t)
 
     def slice(self, a: int, b: int) -> "SfmTable":
         """The table of views a..b-1 (shares the uploaded arrays)."""
@@ -167,7 +203,8 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     depth [V,H,W] float32 and mask [V,H,W] bool in pinned host memory are copied to the device,
     the image [V,H,W,3] stays in pinned host memory and only its kept pixels are read over PCIe by
     the gather kernel; rgb comes back to the host (the reference returns rgbs on the CPU,
-    monocular_depth_init.py:168), xyz stays on the device.
+    monocular_depth_init.py:168), xyz stays on the device.  rgb_host is a view of a reused pinned
+    buffer: copy it if it has to outlive the next call.
     With chunks > 1 the views go through in blocks: all host->device copies are queued on a copy
     stream up front and block c is processed while blocks c+1.. are still in flight.  Measured on a
     B200 this does NOT pay (23.4 ms at 1 block, 24.8 at 4, 26.4 at 8 for the 200-view C2 scene): the
@@ -221,9 +258,10 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
         rgb_local = res.rgb[r0:r0 + res.total]
     else:
         rgb_local = res.rgb
-    rgb_h = torch.empty(rgb_local.shape, dtype=torch.float32, pin_memory=True)
+    # reused pinned result buffers: rgb_h / counts_host are valid until the next call
+    rgb_h = _PINNED.get("e2e_rgb", tuple(rgb_local.shape), torch.float32)
     rgb_h.copy_(rgb_local, non_blocking=True)
-    counts_h = torch.empty(res.view_counts.shape, dtype=torch.int64, pin_memory=True)
+    counts_h = _PINNED.get("e2e_counts", tuple(res.view_counts.shape), torch.int64)
     counts_h.copy_(res.view_counts, non_blocking=True)
     main.synchronize()
     h2d = depth_h.numel() * 4 + mask_h.numel() + res.total * 3 * image_h.element_size() \

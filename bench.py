@@ -293,12 +293,15 @@ def run_ours(args):
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     e2e_steps = max(1, min(args.steps, 5))
+    e2e_step_ms = []
     for _ in range(e2e_steps):
+        t_step = time.perf_counter()
         r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names,
                                                          sc.points, sc.point_indices, dev, L.IMAGE_U8,
                                                          exchange=exchange)
         if world > 1 and exchange is None:
             dmod.allgather_points(r2.xyz, r2.rgb)
+        e2e_step_ms.append(round(1e3 * (time.perf_counter() - t_step), 2))
     f1.record()
     barrier()
     e2e_ms = torch.tensor([max(f0.elapsed_time(f1), 1e3 * (time.perf_counter() - t0))], device=dev)
@@ -358,7 +361,7 @@ def run_ours(args):
         "cpu_baseline": {"value": nv / dt, "unit": "views/s", "cores": cores, "kind": "port",
                          "sample": f"{nv} of {V} views of the same workload, oracle port of the reference loop on the host"},
         "e2e": {"value": e2e_views_per_s, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps},
+                "steps": e2e_steps, "step_ms": e2e_step_ms},
         "gpu_launches": launches, "clocks": clk,
     }
     print(json.dumps(out))
