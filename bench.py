@@ -185,8 +185,9 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "init views/sec (align+subsample+unproject)", "value": vps, "unit": "views/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "views_per_step": nv, "H": H, "W": W, "sfm_points_per_view": n_sfm,
-                   "aligner": aligner, "subsample": subsample},
+        # same config as our arm; the CPU run covers `sample_views_per_step` of the views per step
+        "config": {"workload": args.workload, "views_per_gpu": V, "H": H, "W": W, "sfm_points_per_view": n_sfm,
+                   "aligner": aligner, "subsample": subsample, "patch_mask": True, "sample_views_per_step": nv},
         "mpts_per_s": kept_pts / t / 1e6,
         "cpu_baseline": {"value": vps, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": vps, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
