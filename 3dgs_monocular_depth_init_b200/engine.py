@@ -142,7 +142,8 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
-    "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_min_extents": 1,
+    "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
+    "mdi_min_extents": 1,
 }
 
 
