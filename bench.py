@@ -286,14 +286,18 @@ def run_ours(args):
     # ---- end to end: host buffers in, rgb out, through the public API --------------------------
     depth_h = depth.cpu().pin_memory(); mask_h = mask.cpu().pin_memory(); image_h = image.cpu().pin_memory()
     h2d = d2h = 0
-    for _ in range(2):
-        mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names, sc.points,
-                                   sc.point_indices, dev, L.IMAGE_U8)
+    for _ in range(3):  # warm-up with the timed loop's own binding pattern: the previous result is still alive
+        # while the next call allocates, so the caching allocator needs its second set of blocks before timing
+        r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names,
+                                                         sc.points, sc.point_indices, dev, L.IMAGE_U8,
+                                                         exchange=exchange)
+        if world > 1 and exchange is None:
+            dmod.allgather_points(r2.xyz, r2.rgb)
     barrier()
     t0 = time.perf_counter()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    e2e_steps = max(1, min(args.steps, 5))
+    e2e_steps = max(1, min(args.steps, 10))
     e2e_step_ms = []
     for _ in range(e2e_steps):
         t_step = time.perf_counter()
