@@ -314,3 +314,34 @@ def test_tma_staged_statistics_kernel_is_bit_identical():
                         "quantile_one_pass or golden or batched_scene"],
                        capture_output=True, text=True, timeout=900, env={**os.environ, "MDI_STATS_MAIN": "tma"})
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("subsample", ["adaptive", 7])
+def test_mixed_size_views_in_one_batch(subsample):
+    """Views of different sizes passed as lists in ONE batch (the lattice grid is sized for the
+    largest view, patch geometry is per view) equal the same views run scene by scene."""
+    syn = mod("synthetic")
+    mdi = mod("monocular_depth_init")
+    L = mod("_lib")
+    a = syn.make_scene(n_views=2, H=120, W=160, n_sfm=2500, seed=21, low_conf_every=50)
+    b = syn.make_scene(n_views=3, H=208, W=96, n_sfm=2000, seed=22, low_conf_every=50)
+    cfg = mod("config").Config()
+    cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum("lstsqrs")
+    cfg.mdi.subsample_factor = subsample
+    run = lambda sc: mdi.points_from_views(cfg, [d.to(DEV) for d in sc.depth], [m.to(DEV) for m in sc.mask],
+                                           [im.to(DEV) for im in sc.image], sc.K, sc.c2w, sc.names, sc.points,
+                                           sc.point_indices, DEV, L.IMAGE_U8)
+    ra, rb = run(a), run(b)
+    names = [f"a_{n}" for n in a.names] + [f"b_{n}" for n in b.names]
+    points = np.concatenate([a.points, b.points])
+    pidx = {f"a_{n}": a.point_indices[n] for n in a.names}
+    pidx.update({f"b_{n}": np.asarray(b.point_indices[n]) + a.points.shape[0] for n in b.names})
+    both = mdi.points_from_views(cfg, [d.to(DEV) for d in list(a.depth) + list(b.depth)],
+                                 [m.to(DEV) for m in list(a.mask) + list(b.mask)],
+                                 [im.to(DEV) for im in list(a.image) + list(b.image)],
+                                 torch.cat([a.K, b.K]), torch.cat([a.c2w, b.c2w]), names, points, pidx, DEV, L.IMAGE_U8)
+    assert both.view_counts.cpu().tolist() == ra.view_counts.cpu().tolist() + rb.view_counts.cpu().tolist()
+    assert torch.equal(both.xyz, torch.cat([ra.xyz, rb.xyz])) and torch.equal(both.rgb, torch.cat([ra.rgb, rb.rgb]))
+    assert torch.equal(both.keep, torch.cat([ra.keep, rb.keep]))
+    assert both.total == ra.total + rb.total > 0
