@@ -788,14 +788,20 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
         const uint32_t i = base + u * kSelThreads + tid;
         kk[u] = i < n_cand ? cand[i] : 0u;
       }
+      // one bracket test per key and bracket, then the two bins of that bracket; hits are rare
+      // (a bin holds a few dozen of the ~10^5 candidates), so the appends stay off the hot path
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        if (base + u * kSelThreads + tid >= n_cand) continue;
+        const bool valid = base + u * kSelThreads + tid < n_cand;
 #pragma unroll
-        for (int j = 0; j < kTargets; ++j) {
-          if (slot[j] != j) continue;
-          const uint32_t o = kk[u] - L[j >> 1];
-          if (o <= Wd[j >> 1] && (o >> sft[j >> 1]) == bin[j]) {
+        for (int g = 0; g < 2; ++g) {
+          const uint32_t o = kk[u] - L[g];
+          const uint32_t b = o >> sft[g];
+          const bool inb = valid && o <= Wd[g];
+          const bool hit0 = inb && b == bin[2 * g];
+          const bool hit1 = inb && !hit0 && b == bin[2 * g + 1];  // only when the two bins differ
+          if (hit0 || hit1) {
+            const int j = hit0 ? 2 * g : 2 * g + 1;
             const uint32_t at = atomicAdd(&s_len[j], 1u);
             if (at < (uint32_t)kListCap) s_list[j][at] = kk[u];
           }
