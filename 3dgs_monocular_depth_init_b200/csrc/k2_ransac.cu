@@ -169,55 +169,86 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
       h1[k] = __shfl_sync(0xffffffffu, hs1, k);
       act[k] = it0 + k < cfg.max_iters;
     }
-    // ---- phase A: sample loss and inlier normal equations of the KH hypotheses ---------------
+    // ---- phase A: sample loss of the KH hypotheses; inlier normal equations of the candidates ---
+    // Only a hypothesis whose sample loss beats the best one so far is ever refitted, and after
+    // the first round that is a few per round: the 5 double-precision sums per (point, hypothesis)
+    // are left to a second pass over the candidates alone.  While there is nothing to beat yet
+    // (first round) every hypothesis is a candidate and one fused pass does both.
+    const bool fused = !(cutoff < (double)INFINITY);
     Sums in[KH];
     int n_out[KH];
     double msac[KH];
 #pragma unroll
     for (int k = 0; k < KH; ++k) { in[k] = {0, 0, 0, 0, 0}; n_out[k] = 0; msac[k] = 0.0; }
     if (act[0]) {
+      if (fused) {
+        for (int i = lane; i < n; i += 32) {
+          const float dv = dp[i], gv = gp[i];
+          const double dd = (double)dv, gd = (double)gv;
+          const double ddd = dd * dd, ddg = dd * gd;
+#pragma unroll
+          for (int k = 0; k < KH; ++k) {
+            const float r = residual_sq(h0[k], h1[k], dv, gv);
+            if (r < thr) { in[k].dd += ddd; in[k].d += dd; in[k].n += 1.0; in[k].dg += ddg; in[k].g += gd; }
+            if (r >= thr) ++n_out[k];
+            if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
+          }
+        }
+      } else {
+        for (int i = lane; i < n; i += 32) {
+          const float dv = dp[i], gv = gp[i];
+#pragma unroll
+          for (int k = 0; k < KH; ++k) {
+            const float r = residual_sq(h0[k], h1[k], dv, gv);
+            if (r >= thr) ++n_out[k];
+            if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
+          }
+        }
+      }
+    }
+    bool candk[KH];
+    bool any_cand = false;
+    double loss_s_mine = INFINITY;
+#pragma unroll
+    for (int k = 0; k < KH; ++k) {
+      double ls;
+      if (msac_loss) ls = (double)(float)warp_sum_f64(msac[k]);
+      else ls = (double)warp_sum_i32(n_out[k]);
+      candk[k] = act[k] && ls < cutoff;   // warp-uniform
+      any_cand = any_cand || candk[k];
+      if (lane == k) loss_s_mine = act[k] ? ls : INFINITY;
+    }
+    if (!fused && any_cand) {
       for (int i = lane; i < n; i += 32) {
         const float dv = dp[i], gv = gp[i];
         const double dd = (double)dv, gd = (double)gv;
         const double ddd = dd * dd, ddg = dd * gd;
 #pragma unroll
         for (int k = 0; k < KH; ++k) {
+          if (!candk[k]) continue;
           const float r = residual_sq(h0[k], h1[k], dv, gv);
           if (r < thr) { in[k].dd += ddd; in[k].d += dd; in[k].n += 1.0; in[k].dg += ddg; in[k].g += gd; }
-          if (r >= thr) ++n_out[k];
-          if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
         }
       }
     }
     float hl0 = 0.f, hl1 = 0.f;   // lane k keeps the local-optimisation fit of hypothesis k
-    double loss_s_mine = INFINITY;
 #pragma unroll
     for (int k = 0; k < KH; ++k) {
+      if (!candk[k]) continue;
       Sums t;
       t.dd = warp_sum_f64(in[k].dd); t.d = warp_sum_f64(in[k].d); t.n = warp_sum_f64(in[k].n);
       t.dg = warp_sum_f64(in[k].dg); t.g = warp_sum_f64(in[k].g);
-      double ls;
-      if (msac_loss) ls = (double)(float)warp_sum_f64(msac[k]);
-      else ls = (double)warp_sum_i32(n_out[k]);
-      if (lane == k) {
-        loss_s_mine = act[k] ? ls : INFINITY;
-        if (act[k]) solve(t, &hl0, &hl1);
-      }
+      if (lane == k) solve(t, &hl0, &hl1);
     }
     if (lane < KH && it0 + lane < cfg.max_iters) {
       s_loss_sample[warp * KH + lane] = loss_s_mine;
       s_hlo[warp * KH + lane][0] = hl0; s_hlo[warp * KH + lane][1] = hl1;
     }
     // ---- phase B: local-optimisation loss of the candidates --------------------------------------
-    bool candk[KH];
-    bool any_cand = false;
 #pragma unroll
     for (int k = 0; k < KH; ++k) {
       h0[k] = __shfl_sync(0xffffffffu, hl0, k);
       h1[k] = __shfl_sync(0xffffffffu, hl1, k);
-      const double ls = __shfl_sync(0xffffffffu, loss_s_mine, k);
-      candk[k] = act[k] && ls < cutoff;
-      any_cand = any_cand || candk[k];
       n_out[k] = 0; msac[k] = 0.0;
     }
     int n_in[KH];

@@ -10,6 +10,11 @@ cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategy
 cfg.mdi.subsample_factor = "adaptive"
 sc = syn.make_scene(n_views=200, H=840, W=1297, n_sfm=5000, seed=1, device=str(dev), low_conf_every=50)
 res = mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points, sc.point_indices, dev, L.IMAGE_U8)
-it = res.n_iter.cpu().numpy() if hasattr(res, "n_iter") else None
+it = res.ransac_iters.cpu().numpy()
 print("n_iter percentiles", None if it is None else np.percentile(it, [0, 10, 50, 90, 100]))
-print([k for k in vars(res).keys()])
+nv = res.n_valid.cpu().numpy(); ni = res.ransac_inliers.cpu().numpy()
+print("n_valid percentiles", np.percentile(nv, [0, 10, 50, 90, 100]))
+print("inlier ratio percentiles", np.percentile(ni / np.maximum(nv, 1), [0, 10, 50, 90, 100]))
+print("hist of iters", np.bincount(np.minimum(it // 16, 20)))
+a = cfg.mdi.alignment
+print({k: getattr(a.ransac, k) for k in dir(a.ransac) if not k.startswith("_")} if hasattr(a, "ransac") else dir(a))
