@@ -97,6 +97,9 @@ struct EmitDst {
   // NVSwitch multicast addresses of the same clouds (n == 0): one multimem store reaches every GPU
   float* mc_xyz;
   float* mc_rgb;
+  // speculative launch (mdi_emit_points_capped): nothing is written when *total_rows > capacity
+  const int64_t* total_rows;
+  int64_t capacity;
 };
 
 __device__ __forceinline__ void multicast_store(float* addr, float v) {
@@ -122,6 +125,7 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
   const int incl = warp_incl_scan(cnt);
   const int tot = __shfl_sync(0xffffffffu, incl, 31);
   if (tot == 0) return;
+  if (dst.total_rows && __ldg(dst.total_rows) > dst.capacity) return;
   const int v = find_view_fast(views, n_views, tile, total_tiles);
   const MdiView& vw = views[v];
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
@@ -289,6 +293,19 @@ extern "C" int mdi_emit_points(const MdiView* views, int n_views, int64_t total_
   dst.n = 1; dst.row_offset = 0; dst.xyz[0] = xyz; dst.rgb[0] = rgb;
   return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
                      dst, stream, "mdi_emit_points");
+}
+
+extern "C" int mdi_emit_points_capped(const MdiView* views, int n_views, int64_t total_tiles,
+                                      const float* scale_shift, const uint32_t* bits,
+                                      const int64_t* tile_offsets, const int64_t* view_offsets,
+                                      int image_kind, float* xyz, float* rgb, const int64_t* total_rows,
+                                      int64_t capacity_rows, void* stream) {
+  MDI_REQUIRE(total_rows && capacity_rows >= 0, "mdi_emit_points_capped: null total_rows / negative capacity");
+  mdi::EmitDst dst{};
+  dst.n = 1; dst.row_offset = 0; dst.xyz[0] = xyz; dst.rgb[0] = rgb;
+  dst.total_rows = total_rows; dst.capacity = capacity_rows;
+  return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
+                     dst, stream, "mdi_emit_points_capped");
 }
 
 extern "C" int mdi_emit_points_multi(const MdiView* views, int n_views, int64_t total_tiles,

@@ -81,6 +81,7 @@ class RunOptions:
     stop_after: Optional[str] = None             # "project" | "fit" | "mask": partial pipelines
     stats_exact: bool = False                    # force the three-pass exact quantile select
     exchange: object = None                      # distributed.CloudExchange: emit into every rank's cloud
+    speculative_emit: bool = True                # launch a10/a11 before the output size reaches the host
 
 
 @dataclass
@@ -146,7 +147,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
-    "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
+    "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_capped": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
     "mdi_min_extents": 1,
 }
 
@@ -457,8 +458,18 @@ class Engine:
             zero_done.record(zs)
         prezeroed = [True]
 
-        def mask_stage(stats_mode: int):
-            """a7 statistics -> a5-a10 keep mask -> compaction offsets; returns (total, retry)."""
+        want_xyz = bool(opt.want_xyz)
+        want_rgb = bool(opt.want_rgb and vin.image is not None)
+        # The output size is data dependent.  With the size of the previous run as a hint, a10/a11 are
+        # launched into buffers of hint + 12.5 % rows right behind the scan, and the 16-byte size
+        # read-back goes through a side stream, so the device never waits for the host; the kernel
+        # writes nothing when the real size exceeds the buffers, and the plain path below re-emits.
+        hint = getattr(self, "_emit_hint", 0)
+        may_speculate = bool(opt.speculative_emit and opt.exchange is None and opt.stop_after != "mask"
+                             and (want_xyz or want_rgb) and hint > 0)
+
+        def mask_stage(stats_mode: int, speculate: bool = False):
+            """a7 statistics -> a5-a10 keep mask -> compaction offsets; returns (total, retry, spec)."""
             if use_stats:
                 L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
                                             (flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)) | stats_mode,
@@ -479,18 +490,40 @@ class Engine:
             L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
                                        res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
                                        meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
-            # the output size is data dependent: one 16-byte read-back (the only sync of the pipeline)
-            tail = meta[2 * V:].cpu()
-            return int(tail[0]), bool(tail[1])
+            if not speculate:
+                # one 16-byte read-back (the only sync of the pipeline)
+                tail = meta[2 * V:].cpu()
+                return int(tail[0]), bool(tail[1]), None
+            if not hasattr(self, "_rb_stream"):
+                self._rb_stream = torch.cuda.Stream(self.device)
+                self._tail_pin = torch.empty(2, dtype=torch.int64, pin_memory=True)
+            scanned = torch.cuda.Event()
+            scanned.record(main)
+            cap = hint + (hint >> 3) + 4096
+            xyz = torch.empty((cap, 3), dtype=f32, device=self.device) if want_xyz else None
+            rgb = torch.empty((cap, 3), dtype=f32, device=self.device) if want_rgb else None
+            L.check(lib.mdi_emit_points_capped(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
+                                               res.view_offsets.data_ptr(), int(vin.image_kind), L.ptr(xyz), L.ptr(rgb),
+                                               meta[2 * V:].data_ptr(), cap, st), "mdi_emit_points_capped")
+            rb = self._rb_stream
+            rb.wait_event(scanned)
+            with torch.cuda.stream(rb):
+                meta.record_stream(rb)
+                self._tail_pin.copy_(meta[2 * V:], non_blocking=True)
+                copied = torch.cuda.Event()
+                copied.record(rb)
+            copied.synchronize()
+            return int(self._tail_pin[0]), bool(self._tail_pin[1]), (cap, xyz, rgb)
 
         # views under 64K pixels give the one-pass path too small a sample to bracket: exact select
-        res.total, retry = mask_stage(L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0)
+        res.total, retry, spec = mask_stage(L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0, may_speculate)
         if retry:
             # a view's one-pass quantile brackets could not be certified (e.g. a constant depth
             # map): exact three-pass select for the flagged views, then mask + scan again
             meta[2 * V + 1] = 0
             res.extras["stats_retry"] = True
-            res.total, retry = mask_stage(L.STATS_RETRY_FLAGGED)
+            spec = None
+            res.total, retry, _ = mask_stage(L.STATS_RETRY_FLAGGED)
             assert not retry
         if opt.stop_after == "mask" or not (opt.want_xyz or opt.want_rgb):
             return res
@@ -515,9 +548,16 @@ class Engine:
             res.extras["rank_counts"] = counts
             res.extras["row_offset"] = row_offset
             return res
-        if opt.want_xyz:
+        self._emit_hint = N
+        if spec is not None and N <= spec[0]:
+            # the speculative launch covered it; a much too large buffer is not kept alive by the result
+            shrink = N < spec[0] // 2
+            res.xyz = None if spec[1] is None else (spec[1][:N].clone() if shrink else spec[1][:N])
+            res.rgb = None if spec[2] is None else (spec[2][:N].clone() if shrink else spec[2][:N])
+            res.extras["speculative_emit"] = True
+            return res
+        if want_xyz:
             res.xyz = torch.empty((N, 3), dtype=f32, device=self.device)
-        want_rgb = opt.want_rgb and vin.image is not None
         if want_rgb:
             res.rgb = torch.empty((N, 3), dtype=f32, device=self.device)
         if N:

@@ -267,6 +267,17 @@ int mdi_emit_points(const MdiView* views, int n_views, int64_t total_tiles,
                     void* stream);
 
 /*
+ * The same, launched BEFORE the host knows the output size (which is data dependent and otherwise
+ * costs a stream sync between mdi_scan_tiles and this call): xyz / rgb hold capacity_rows rows, and
+ * the kernel writes nothing at all when *total_rows (device, the `total` of mdi_scan_tiles) exceeds
+ * that, in which case the caller re-emits with mdi_emit_points once it has read the size.
+ */
+int mdi_emit_points_capped(const MdiView* views, int n_views, int64_t total_tiles,
+                           const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
+                           const int64_t* view_offsets, int image_kind, float* xyz, float* rgb,
+                           const int64_t* total_rows, int64_t capacity_rows, void* stream);
+
+/*
  * a10/a11 with the exchange step of a multi-GPU run fused in (replaces the torch.cat of
  * monocular_depth_init.py:183-184 across ranks): every kept point of this GPU is written to n_dst
  * clouds -- its own and its NVLink peers', mapped into this address space by the caller (CUDA IPC /

@@ -345,3 +345,34 @@ def test_mixed_size_views_in_one_batch(subsample):
     assert torch.equal(both.xyz, torch.cat([ra.xyz, rb.xyz])) and torch.equal(both.rgb, torch.cat([ra.rgb, rb.rgb]))
     assert torch.equal(both.keep, torch.cat([ra.keep, rb.keep]))
     assert both.total == ra.total + rb.total > 0
+
+
+@pytest.mark.gpu
+def test_speculative_emit_equals_plain_emit():
+    """The emit kernel launched ahead of the size read-back (buffers sized from the previous run)
+    returns the same cloud as the plain path when the guess covers the output, when it is far too
+    large, and when it is too small (the kernel must then write nothing and the engine re-emit)."""
+    syn = mod("synthetic")
+    mdi = mod("monocular_depth_init")
+    L = mod("_lib")
+    eng = mod("engine").get_engine(DEV)
+    cfg = mod("config").Config()
+    cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum("lstsqrs")
+    cfg.mdi.subsample_factor = 2
+    sc = syn.make_scene(n_views=5, H=120, W=160, n_sfm=2500, seed=21, device=str(DEV), low_conf_every=4)
+
+    def run():
+        return mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points,
+                                     sc.point_indices, DEV, L.IMAGE_U8)
+
+    eng._emit_hint = 0
+    ref = run()                                   # no hint yet: plain path
+    assert not ref.extras.get("speculative_emit", False) and ref.total > 10000
+    for hint, expect in ((ref.total, True), (ref.total * 50, True), (ref.total // 3, False), (1, False)):
+        assert (ref.total <= hint + (hint >> 3) + 4096) == expect   # the engine's buffer rule
+        eng._emit_hint = hint
+        res = run()
+        assert bool(res.extras.get("speculative_emit", False)) == expect, hint
+        assert res.total == ref.total and eng._emit_hint == ref.total
+        assert res.xyz.shape == ref.xyz.shape and torch.equal(res.xyz, ref.xyz) and torch.equal(res.rgb, ref.rgb)
+        assert res.xyz.is_contiguous() and res.rgb.is_contiguous()
