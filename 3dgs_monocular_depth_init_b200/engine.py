@@ -197,6 +197,7 @@ class Engine:
         L.check(self.lib.mdi_check_device(idx), "mdi_check_device")
         self._ws: dict[str, torch.Tensor] = {}
         self._pin: dict[str, torch.Tensor] = {}
+        self._plan = None   # (key, descriptor table + its uploaded image) of the previous run
         self.launches = 0   # kernels launched through this engine (bench `gpu_launches`)
         self.profile = False
         self.events: list = []  # (entry point, start event, end event) when profile is on
@@ -284,6 +285,24 @@ class Engine:
             desc["patch_h"] = desc["patch_w"] = 1
         return desc, px_begin, tile_begin, sfm_begin
 
+    @staticmethod
+    def _plan_key(vin: ViewInputs, opt: RunOptions, V: int, kn: np.ndarray, c2wn: np.ndarray):
+        """Identity of everything the uploaded descriptor table depends on, or None when the inputs
+        are per-view lists / carry an externally supplied P (those always take the full path)."""
+        if vin.P_override is not None:
+            return None
+        parts = []
+        for x in (vin.depth, vin.mask, vin.image):
+            if x is None:
+                parts.append(None)
+            elif isinstance(x, torch.Tensor) and x.is_contiguous() and x.shape[0] == V:
+                parts.append((x.data_ptr(), tuple(x.shape), x.dtype, x.is_cuda))
+            else:
+                return None
+        counts = None if vin.sfm_counts is None else np.asarray(vin.sfm_counts, dtype=np.int64).tobytes()
+        return (V, tuple(parts), counts, kn.tobytes(), c2wn.tobytes(), bool(opt.use_patch_mask),
+                int(opt.num_patches_small_axis))
+
     def _upload(self, name: str, parts) -> torch.Tensor:
         """One H2D copy of the concatenated byte images of `parts` (numpy arrays) through a
         persistent pinned staging buffer.  Safe to reuse across calls: every run() ends with a
@@ -308,7 +327,19 @@ class Engine:
         run_start = torch.cuda.Event()
         run_start.record()
         V = int(vin.K.shape[0])
-        desc, px_begin, tile_begin, sfm_begin = self.build_views(vin, opt)
+        kn = np.ascontiguousarray(vin.K.detach().cpu().numpy(), dtype=np.float32).reshape(V, 3, 3)
+        c2wn = np.ascontiguousarray(vin.c2w.detach().cpu().numpy(), dtype=np.float32).reshape(V, 4, 4)
+        # The same resident views again (every step of a training-set sweep, every bench step): the
+        # descriptor table, K and cam2world already sit on the device from the previous call, and
+        # rebuilding + re-uploading them is ~0.1 ms of host time in front of the first launch.
+        key = self._plan_key(vin, opt, V, kn, c2wn) if V else None
+        plan = self._plan[1] if key is not None and self._plan is not None and self._plan[0] == key else None
+        if plan is not None:
+            desc, px_begin, tile_begin, sfm_begin, blob, pinhole = plan
+            px_begin, sfm_begin = px_begin.copy(), sfm_begin.copy()
+        else:
+            self._plan = None
+            desc, px_begin, tile_begin, sfm_begin = self.build_views(vin, opt)
         total_tiles = int(tile_begin[-1])
         max_tiles = int(desc["n_tiles"].max()) if V else 0
         slots = int(sfm_begin[-1]) + 4
@@ -322,19 +353,20 @@ class Engine:
                 res.extras["rank_counts"] = counts
                 res.extras["row_offset"] = row_offset
             return res
-        # a1: cameras.  One upload: [descriptors][K][cam2world][inv(K) unless pinhole]
-        kn = np.ascontiguousarray(vin.K.detach().cpu().numpy(), dtype=np.float32).reshape(V, 3, 3)
-        c2wn = np.ascontiguousarray(vin.c2w.detach().cpu().numpy(), dtype=np.float32).reshape(V, 4, 4)
-        pinhole = bool(((kn[:, 0, 1] == 0) & (kn[:, 1, 0] == 0) & (kn[:, 2, 0] == 0) & (kn[:, 2, 1] == 0)
-                        & (kn[:, 2, 2] == 1)).all())
-        # zero-skew pinhole intrinsics: inv(K) in closed form on the device (bit-identical to
-        # torch.linalg.inv); anything else: batched LU inverse on the host like the reference
-        if vin.P_override is not None:  # stage-wise parity / project_and_filter_sfm_pts: P as given
-            desc["P"] = vin.P_override.reshape(V, 12).numpy()
-        parts = [desc.view(np.uint8).reshape(-1), kn, c2wn]
-        if not pinhole:
-            parts.append(torch.linalg.inv(torch.from_numpy(kn)).numpy())
-        blob = self._upload("views", parts)
+        if plan is None:
+            # a1: cameras.  One upload: [descriptors][K][cam2world][inv(K) unless pinhole]
+            pinhole = bool(((kn[:, 0, 1] == 0) & (kn[:, 1, 0] == 0) & (kn[:, 2, 0] == 0) & (kn[:, 2, 1] == 0)
+                            & (kn[:, 2, 2] == 1)).all())
+            # zero-skew pinhole intrinsics: inv(K) in closed form on the device (bit-identical to
+            # torch.linalg.inv); anything else: batched LU inverse on the host like the reference
+            if vin.P_override is not None:  # stage-wise parity / project_and_filter_sfm_pts: P as given
+                desc["P"] = vin.P_override.reshape(V, 12).numpy()
+            parts = [desc.view(np.uint8).reshape(-1), kn, c2wn]
+            if not pinhole:
+                parts.append(torch.linalg.inv(torch.from_numpy(kn)).numpy())
+            blob = self._upload("views", parts)
+            if key is not None:
+                self._plan = (key, (desc, px_begin.copy(), tile_begin, sfm_begin.copy(), blob, pinhole))
         vp = blob.data_ptr()
         kp = vp + desc.nbytes
         c2wp = kp + 4 * 9 * V

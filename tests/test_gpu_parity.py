@@ -376,3 +376,34 @@ def test_speculative_emit_equals_plain_emit():
         assert res.total == ref.total and eng._emit_hint == ref.total
         assert res.xyz.shape == ref.xyz.shape and torch.equal(res.xyz, ref.xyz) and torch.equal(res.rgb, ref.rgb)
         assert res.xyz.is_contiguous() and res.rgb.is_contiguous()
+
+
+@pytest.mark.gpu
+def test_cached_descriptor_upload_follows_camera_changes():
+    """A repeated call on the same resident tensors reuses the uploaded descriptor table; the reuse
+    must notice a camera edited in place (same tensors, new values) and give what a cold engine gives."""
+    syn = mod("synthetic")
+    mdi = mod("monocular_depth_init")
+    L = mod("_lib")
+    eng = mod("engine").get_engine(DEV)
+    cfg = mod("config").Config()
+    cfg.mdi.alignment.aligner = mod("depth_alignment.config").DepthAlignmentStrategyEnum("lstsqrs")
+    cfg.mdi.subsample_factor = 4
+    sc = syn.make_scene(n_views=4, H=96, W=128, n_sfm=2000, seed=5, device=str(DEV))
+
+    def run():
+        return mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points,
+                                     sc.point_indices, DEV, L.IMAGE_U8)
+
+    eng._plan = None
+    cold = run()
+    assert eng._plan is not None
+    warm = run()                                   # served from the cached table
+    assert torch.equal(warm.xyz, cold.xyz) and torch.equal(warm.rgb, cold.rgb) and torch.equal(warm.P, cold.P)
+    sc.c2w[:, :3, 3] += 0.25                       # move every camera, in place
+    moved = run()
+    eng._plan = None
+    moved_cold = run()
+    assert not torch.equal(moved.xyz, cold.xyz)
+    assert torch.equal(moved.xyz, moved_cold.xyz) and torch.equal(moved.P, moved_cold.P)
+    assert torch.equal(moved.view_counts, moved_cold.view_counts)
