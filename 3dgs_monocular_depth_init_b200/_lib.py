@@ -84,6 +84,7 @@ _SIGNATURES = {
     "mdi_keep_mask": (_INT, [_P, _INT, _I64, _I64, _INT, _INT, _P, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),
     "mdi_scan_tiles": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P]),
     "mdi_emit_points": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _P]),
+    "mdi_upload_table": (_INT, [_P, _P, _I64, _P]),
     "mdi_emit_points_capped": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _P, _I64, _P]),
     "mdi_emit_points_multi": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _INT, _P, _P, _I64, _P]),
     "mdi_emit_points_multicast": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _I64, _P]),

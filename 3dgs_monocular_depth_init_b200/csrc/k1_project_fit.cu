@@ -175,7 +175,27 @@ __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_
     out[i] = align_depth(depth[i], s, t);
 }
 
+// small host table -> device, read by the SMs from mapped pinned memory (see mdi_upload_table)
+__global__ void upload_table_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, int64_t n_words) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += stride) dst[i] = src[i];
+}
+
 }  // namespace mdi
+
+extern "C" int mdi_upload_table(void* dst, const void* src_pinned, int64_t bytes, void* stream) {
+  MDI_REQUIRE(bytes >= 0 && bytes % 4 == 0, "mdi_upload_table: size %lld is not a multiple of 4", (long long)bytes);
+  if (bytes == 0) return MDI_OK;
+  MDI_REQUIRE(dst && src_pinned && ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src_pinned)) & 3) == 0,
+              "mdi_upload_table: null or unaligned pointer");
+  const int64_t n_words = bytes / 4;
+  const unsigned grid = (unsigned)((n_words + 255) / 256 < 296 ? (n_words + 255) / 256 : 296);
+  mdi::prof_mark("upload_table_kernel", (cudaStream_t)stream);
+  mdi::upload_table_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      static_cast<uint32_t*>(dst), static_cast<const uint32_t*>(src_pinned), n_words);
+  MDI_CHECK_LAUNCH("mdi_upload_table");
+  return MDI_OK;
+}
 
 extern "C" int mdi_setup_cameras(MdiView* views, int n_views, const float* K, const float* c2w,
                                  const float* Kinv, float* P_out, int keep_P, void* stream) {

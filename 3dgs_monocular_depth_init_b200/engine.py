@@ -82,6 +82,7 @@ class RunOptions:
     stats_exact: bool = False                    # force the three-pass exact quantile select
     exchange: object = None                      # distributed.CloudExchange: emit into every rank's cloud
     speculative_emit: bool = True                # launch a10/a11 before the output size reaches the host
+    defer_emit: bool = False                     # stop after the mask; Engine.emit_deferred() writes the cloud later
 
 
 @dataclass
@@ -145,7 +146,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 
 # kernels launched by each C-ABI entry point (for the bench's `gpu_launches` claim)
 KERNELS_PER_CALL = {
-    "mdi_setup_cameras": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
+    "mdi_setup_cameras": 1, "mdi_upload_table": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_capped": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
     "mdi_min_extents": 1,
@@ -303,7 +304,7 @@ class Engine:
         return (V, tuple(parts), counts, kn.tobytes(), c2wn.tobytes(), bool(opt.use_patch_mask),
                 int(opt.num_patches_small_axis))
 
-    def _upload(self, name: str, parts) -> torch.Tensor:
+    def _upload(self, name: str, parts, owned: bool = False) -> torch.Tensor:
         """One H2D copy of the concatenated byte images of `parts` (numpy arrays) through a
         persistent pinned staging buffer.  Safe to reuse across calls: every run() ends with a
         stream synchronisation (the read-back of the point count)."""
@@ -317,7 +318,13 @@ class Engine:
         for a, sz in zip(parts, sizes):
             host[o:o + sz] = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
             o += sz
-        dev = self._buf(name, n, torch.uint8)
+        if owned and n % 4 == 0:
+            # a block of a chunked host run: bulk copies of later blocks are already queued on the copy
+            # engine, and a memcpy would wait behind all of them -- the SMs fetch the table instead
+            dev = torch.empty(n, dtype=torch.uint8, device=self.device)
+            L.check(self.lib.mdi_upload_table(dev.data_ptr(), pin.data_ptr(), n, _stream()), "mdi_upload_table")
+            return dev
+        dev = torch.empty(n, dtype=torch.uint8, device=self.device) if owned else self._buf(name, n, torch.uint8)
         dev.copy_(pin[:n], non_blocking=True)
         return dev
 
@@ -364,7 +371,7 @@ class Engine:
             parts = [desc.view(np.uint8).reshape(-1), kn, c2wn]
             if not pinhole:
                 parts.append(torch.linalg.inv(torch.from_numpy(kn)).numpy())
-            blob = self._upload("views", parts)
+            blob = self._upload("views", parts, owned=opt.defer_emit)
             if key is not None:
                 self._plan = (key, (desc, px_begin.copy(), tile_begin, sfm_begin.copy(), blob, pinhole))
         vp = blob.data_ptr()
@@ -470,9 +477,13 @@ class Engine:
                                   float(opt.grad_thresh) if opt.grad_thresh is not None else 0.0)
         if opt.want_keep_mask:
             res.keep = torch.empty(int(px_begin[-1]), dtype=torch.uint8, device=self.device)
-        bits = self._buf("bits", total_tiles * L.TILE_WORDS, i32)
+        if opt.defer_emit:  # the emit of this run comes after later runs: its inputs must not be recycled
+            bits = torch.empty(total_tiles * L.TILE_WORDS, dtype=i32, device=self.device)
+            tile_offsets = torch.empty(total_tiles, dtype=torch.int64, device=self.device)
+        else:
+            bits = self._buf("bits", total_tiles * L.TILE_WORDS, i32)
+            tile_offsets = self._buf("tile_offsets", total_tiles, torch.int64)
         tile_counts = self._buf("tile_counts", total_tiles, i32)
-        tile_offsets = self._buf("tile_offsets", total_tiles, torch.int64)
         # zero-fill of the mask outputs on a side stream: it only has to wait for what was queued before
         # this call, so it runs under the alignment / statistics kernels instead of after them
         main = torch.cuda.current_stream(self.device)
@@ -498,7 +509,7 @@ class Engine:
         # writes nothing when the real size exceeds the buffers, and the plain path below re-emits.
         hint = getattr(self, "_emit_hint", 0)
         may_speculate = bool(opt.speculative_emit and opt.exchange is None and opt.stop_after != "mask"
-                             and (want_xyz or want_rgb) and hint > 0)
+                             and not opt.defer_emit and (want_xyz or want_rgb) and hint > 0)
 
         def mask_stage(stats_mode: int, speculate: bool = False):
             """a7 statistics -> a5-a10 keep mask -> compaction offsets; returns (total, retry, spec)."""
@@ -522,13 +533,17 @@ class Engine:
             L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
                                        res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
                                        meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
-            if not speculate:
-                # one 16-byte read-back (the only sync of the pipeline)
-                tail = meta[2 * V:].cpu()
-                return int(tail[0]), bool(tail[1]), None
             if not hasattr(self, "_rb_stream"):
                 self._rb_stream = torch.cuda.Stream(self.device)
                 self._tail_pin = torch.empty(2, dtype=torch.int64, pin_memory=True)
+            if not speculate:
+                # one 16-byte read-back (the only sync of the pipeline), into pinned memory: a pageable
+                # destination makes the driver stage the copy and wait on the bulk copies in flight
+                self._tail_pin.copy_(meta[2 * V:], non_blocking=True)
+                done = torch.cuda.Event()
+                done.record(main)
+                done.synchronize()
+                return int(self._tail_pin[0]), bool(self._tail_pin[1]), None
             scanned = torch.cuda.Event()
             scanned.record(main)
             cap = hint + (hint >> 3) + 4096
@@ -560,6 +575,11 @@ class Engine:
         if opt.stop_after == "mask" or not (opt.want_xyz or opt.want_rgb):
             return res
         N = res.total
+        if opt.defer_emit:
+            res.extras["emit_state"] = dict(blob=blob, n_views=V, total_tiles=total_tiles, scale_shift=res.scale_shift,
+                                            bits=bits, tile_offsets=tile_offsets, view_offsets=res.view_offsets,
+                                            image_kind=int(vin.image_kind), has_image=vin.image is not None, total=N)
+            return res
         if opt.exchange is not None:
             # multi-GPU: the emit kernel writes this rank's points into every rank's cloud
             ex = opt.exchange
@@ -597,6 +617,27 @@ class Engine:
                                         res.view_offsets.data_ptr(), int(vin.image_kind), L.ptr(res.xyz), L.ptr(res.rgb), st),
                     "mdi_emit_points")
         return res
+
+    def emit_deferred(self, states, want_xyz: bool = True, want_rgb: bool = True):
+        """a10/a11 of runs made with RunOptions.defer_emit, in order, into ONE cloud: run i's points go
+        to rows sum(total[:i]) .. (the row_offset form of the emit kernel).  Returns (xyz, rgb)."""
+        lib, st = self.lib, _stream()
+        total = sum(s["total"] for s in states)
+        f32 = torch.float32
+        want_rgb = bool(want_rgb and all(s["has_image"] for s in states))
+        xyz = torch.empty((total, 3), dtype=f32, device=self.device) if want_xyz else None
+        rgb = torch.empty((total, 3), dtype=f32, device=self.device) if want_rgb else None
+        row = 0
+        for s in states:
+            if s["total"]:
+                xp = (C.c_void_p * 1)(xyz.data_ptr()) if xyz is not None else None
+                rp = (C.c_void_p * 1)(rgb.data_ptr()) if rgb is not None else None
+                L.check(lib.mdi_emit_points_multi(s["blob"].data_ptr(), s["n_views"], s["total_tiles"], L.ptr(s["scale_shift"]),
+                                                  s["bits"].data_ptr(), s["tile_offsets"].data_ptr(),
+                                                  s["view_offsets"].data_ptr(), s["image_kind"], 1, xp, rp, row, st),
+                        "mdi_emit_points_multi")
+            row += s["total"]
+        return xyz, rgb
 
 
 _engines: dict[int, Engine] = {}

@@ -121,7 +121,7 @@ class SfmTable:
 @torch.no_grad()
 def points_from_views(config, depths, masks, images, K, c2w, names, points: np.ndarray, point_indices: dict,
                       device, image_kind: int = L.IMAGE_F32_255, sample_idx: Optional[torch.Tensor] = None,
-                      sfm: Optional[SfmTable] = None, exchange=None):
+                      sfm: Optional[SfmTable] = None, exchange=None, defer_emit: bool = False):
     """The batched hot path.  depths / masks / images: stacked tensors or per-view lists; images
     are [H,W,3] float32 0..255 or uint8, on the device or in pinned host memory.  `sfm` is an
     already uploaded SfmTable of (points, point_indices, names); built here when omitted.
@@ -139,6 +139,7 @@ def points_from_views(config, depths, masks, images, K, c2w, names, points: np.n
         else:
             opt.ransac_seed = ransac_seed()
     opt.exchange = exchange
+    opt.defer_emit = bool(defer_emit)
     vin = ViewInputs(depth=depths, mask=masks, image=images, image_kind=image_kind, K=K, c2w=c2w,
                      sfm_xyz=sfm.xyz, sfm_index=sfm.index, sfm_counts=sfm.counts)
     return eng.run(vin, opt)
@@ -195,6 +196,16 @@ def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth
     return pts, rgbs, scales
 
 
+_TRACE: Optional[list] = None   # debugging: a list here collects (label, timing event) marks of the host path
+
+
+def _mark(label: str):
+    if _TRACE is not None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        _TRACE.append((label, ev))
+
+
 @torch.no_grad()
 def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, points, point_indices, device,
                            image_kind: int = L.IMAGE_U8, sample_idx: Optional[torch.Tensor] = None, exchange=None,
@@ -206,10 +217,14 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     monocular_depth_init.py:168), xyz stays on the device.  rgb_host is a view of a reused pinned
     buffer: copy it if it has to outlive the next call.
     With chunks > 1 the views go through in blocks: all host->device copies are queued on a copy
-    stream up front and block c is processed while blocks c+1.. are still in flight.  Measured on a
-    B200 this does NOT pay (23.4 ms at 1 block, 24.8 at 4, 26.4 at 8 for the 200-view C2 scene): the
-    in-place image reads of a block's emit kernel compete with the bulk copies for the same PCIe
-    direction, so the default stays one block (always one when `exchange` is given).
+    stream up front, block c is aligned / masked while blocks c+1.. are still in flight, and the
+    clouds of all blocks are written at the end (Engine.emit_deferred) -- the in-place image reads of
+    the emit kernel use the same PCIe direction as the bulk copies and must not overlap them.
+    Measured on a B200 (200-view C2 scene) this still does NOT pay: 23.4 ms at 1 block, 24.1 at 2,
+    25.3 at 4 -- although the same 4-block step takes 23.2 ms under the torch profiler, whose time
+    line shows the intended overlap (copies back to back, each block's kernels inside the next
+    block's copy).  The cause of the un-profiled slowdown is not understood; the default stays one
+    block.  Always one block when `exchange` is given.
     Returns (RunResult, rgb_host, h2d_bytes, d2h_bytes)."""
     eng = get_engine(device)
     dev = eng.device
@@ -224,17 +239,26 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     if not hasattr(eng, "_copy_stream"):
         eng._copy_stream = torch.cuda.Stream(dev)
     cs = eng._copy_stream
+    _mark("start")
     cs.wait_stream(main)  # earlier work may still be reading the staging buffers
     arrived = []
-    with torch.cuda.stream(cs):
-        for c in range(n_chunks):
-            a, b = bounds[c], bounds[c + 1]
+
+    def queue_block(c):
+        a, b = bounds[c], bounds[c + 1]
+        with torch.cuda.stream(cs):
             depth_d[a:b].copy_(depth_h[a:b], non_blocking=True)
             mask_d[a:b].copy_(mask_u8[a:b], non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(cs)
             arrived.append(ev)
-    sfm = SfmTable(points, point_indices, names, dev)  # host work, overlaps the copies
+
+    # the copy engine serves host->device copies in the order they are handed over, whatever their
+    # stream: the SfM table goes right behind the first block (its host-side build hides under that
+    # copy), and nothing else of a block's processing uses the copy engine (mdi_upload_table)
+    queue_block(0)
+    sfm = SfmTable(points, point_indices, names, dev)
+    for c in range(1, n_chunks):
+        queue_block(c)
     parts = []
     for c in range(n_chunks):
         a, b = bounds[c], bounds[c + 1]
@@ -242,17 +266,21 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
         parts.append(points_from_views(config, depth_d[a:b], mask_d[a:b], image_h[a:b], K[a:b], c2w[a:b], names[a:b],
                                        points, point_indices, dev, image_kind,
                                        sample_idx[a:b] if sample_idx is not None else None,
-                                       sfm=sfm if n_chunks == 1 else sfm.slice(a, b), exchange=exchange))
+                                       sfm=sfm if n_chunks == 1 else sfm.slice(a, b), exchange=exchange,
+                                       defer_emit=n_chunks > 1))
+    _mark("masks done")
     if n_chunks == 1:
         res = parts[0]
     else:
+        # every block's cloud is written after the last copy has landed: the image reads of the emit
+        # kernel and the bulk copies use the same PCIe direction and must not overlap
         res = RunResult(n_views=V, px_begin=None, sfm_begin=None)
-        res.xyz = torch.cat([p.xyz for p in parts], dim=0)
-        res.rgb = torch.cat([p.rgb for p in parts], dim=0)
+        res.xyz, res.rgb = eng.emit_deferred([p.extras["emit_state"] for p in parts])
         res.view_counts = torch.cat([p.view_counts for p in parts])
         res.status = torch.cat([p.status for p in parts])
         res.scale_shift = torch.cat([p.scale_shift for p in parts])
         res.total = sum(p.total for p in parts)
+    _mark("clouds written")
     if exchange is not None:  # res.rgb is the whole scene: this rank's rows go back to its host
         r0 = res.extras["row_offset"]
         rgb_local = res.rgb[r0:r0 + res.total]
@@ -263,6 +291,7 @@ def points_from_host_views(config, depth_h, mask_h, image_h, K, c2w, names, poin
     rgb_h.copy_(rgb_local, non_blocking=True)
     counts_h = _PINNED.get("e2e_counts", tuple(res.view_counts.shape), torch.int64)
     counts_h.copy_(res.view_counts, non_blocking=True)
+    _mark("results on host")
     main.synchronize()
     h2d = depth_h.numel() * 4 + mask_h.numel() + res.total * 3 * image_h.element_size() \
         + sfm.host_bytes + len(names) * (L.VIEW_DTYPE.itemsize + 25 * 4)

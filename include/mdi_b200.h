@@ -148,6 +148,14 @@ void mdi_profile_enable(int on);
 int mdi_profile_collect(char* names_buf, int buf_len, float* ms, int32_t* calls, int cap);
 
 /*
+ * Copies a small host table (descriptors, K, cam2world) to the device with a kernel that reads the
+ * page-locked, device-mapped source directly.  Unlike an async memcpy it does not queue behind bulk
+ * host->device copies already handed to the copy engine, which is what lets a block of views be
+ * processed while the depth maps of the next blocks are still in flight.  bytes % 4 == 0.
+ */
+int mdi_upload_table(void* dst, const void* src_pinned, int64_t bytes, void* stream);
+
+/*
  * a1: fills P, Kinv and c2w of every descriptor on the device.  K float32 [V,9], c2w float32
  * [V,16] (row-major 4x4), Kinv float32 [V,9] (inv(K) computed by the caller) or NULL when every K
  * is a zero-skew pinhole matrix (then the closed form is used); P_out float32 [V,12] or NULL.
