@@ -22,6 +22,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace mdi {
@@ -52,6 +54,13 @@ struct StatsHdr {
   long long tgt_rank[kTargets];
   float w[2];
   uint32_t gmin_key, gmax_key;
+  // depth-domain form of the brackets (stats_bracket_kernel -> stats_main_kernel): with a finite
+  // scale > 0 and a finite shift, d -> fl(fl(d * s) + t) is monotone, so the tests on the aligned key
+  // become float comparisons on the raw depth
+  uint32_t fast;        // 1: d_lo / d_hi / ds_* are valid and the view takes the depth-domain loop
+  uint32_t force_retry; // set by the depth-domain loop: NaN / inf in the population or a pixel that may hit the sentinel
+  float d_lo[2], d_hi[2];
+  float ds_lo, ds_hi;   // depths whose aligned value is exactly -42.0 (empty when ds_lo > ds_hi)
 };
 
 struct StatsWs {
@@ -282,7 +291,10 @@ stats_sample_kernel(const MdiView* __restrict__ views, const float* __restrict__
 // bracket of each quantile is the span of bins between its lower and upper sample ranks.
 constexpr int kBracketThreads = 1024;
 __global__ void __launch_bounds__(kBracketThreads)
-stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
+stats_bracket_kernel(const float* __restrict__ scale_shift, const int32_t* __restrict__ status, int sentinel, StatsWs ws) {
+  __shared__ uint32_t s_LU[kTargets];      // L0, U0, L1, U1
+  __shared__ uint32_t s_dkey[kTargets + 2]; // depth-domain bounds as order keys (+ sentinel interval)
+  __shared__ int s_fast;
   __shared__ uint32_t s_sort[1024];
   __shared__ uint32_t s_hist[kBrBins];
   __shared__ uint16_t s_guide[kBrBins + 2];
@@ -382,24 +394,69 @@ stats_bracket_kernel(const int32_t* __restrict__ status, StatsWs ws) {
       // keys of bin b satisfy sort[b-1] < key <= sort[b]
       uint32_t L = bl == 0 ? 0u : s_sort[bl - 1] + (s_sort[bl - 1] == 0xFFFFFFFFu ? 0u : 1u);
       uint32_t U = bh >= 1024u ? 0xFFFFFFFFu : s_sort[bh];
+      if (L < kKeyNegInf) L = kKeyNegInf;
+      if (U > kKeyPosInf) U = kKeyPosInf;
+      s_LU[2 * g] = L; s_LU[2 * g + 1] = U >= L ? U : L;
+    }
+    s_fast = 1;
+  }
+  __syncthreads();
+  // Depth-domain form of the brackets.  F(d) = key(fl(fl(d * s) + t)) is monotone non-decreasing in
+  // the order key of d when s is finite and > 0 and t is finite, so {key(aligned) >= L} = {d >= D_lo}
+  // with D_lo the smallest depth whose aligned key reaches L (binary search over the order keys of
+  // all non-NaN floats, 32 steps), and likewise for U and for the sentinel value -42.0.
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const bool mono = s > 0.f && s < INFINITY && fabsf(t) < INFINITY;
+  if (tid < kTargets + 2 && mono) {
+    const uint32_t kSent = fast_key(-42.0f);
+    const uint32_t bound = tid < kTargets ? s_LU[tid] : kSent;
+    auto F = [&](uint32_t kd) { return fast_key(align_depth(key_to_float(kd), s, t)); };
+    uint32_t lo = kKeyNegInf, hi = kKeyPosInf;
+    if ((tid & 1) == 0) {  // smallest kd with F(kd) >= bound
+      if (F(hi) < bound) s_fast = 0;
+      while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if (F(mid) >= bound) hi = mid; else lo = mid + 1; }
+      if (tid < kTargets && lo == 0x80000000u) lo = 0x7FFFFFFFu;  // +0 -> -0: a float test cannot tell them apart
+    } else {               // largest kd with F(kd) <= bound
+      if (F(lo) > bound) s_fast = 0;
+      while (lo < hi) { const uint32_t mid = lo + ((hi - lo + 1) >> 1); if (F(mid) <= bound) lo = mid; else hi = mid - 1; }
+      if (tid < kTargets && lo == 0x7FFFFFFFu) lo = 0x80000000u;  // -0 -> +0
+    }
+    s_dkey[tid] = lo;
+    if (tid < kTargets) {
+      // the depth bounds were only ever widened: make the key bracket cover what they let in
+      const uint32_t fk = F(lo);
+      if ((tid & 1) == 0) { if (fk < s_LU[tid]) s_LU[tid] = fk; }
+      else if (fk > s_LU[tid]) s_LU[tid] = fk;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int g = 0; g < 2; ++g) {
+      uint32_t L = s_LU[2 * g], U = s_LU[2 * g + 1];
       // stats_main_tma_kernel tests the bracket with float comparisons, which agree with the key
       // order for every non-NaN value as long as the bounds are finite-or-inf keys and L != key(+0),
       // U != key(-0) (the one place where the two orders differ).  Widening a bracket is always safe.
-      if (L < 0x007FFFFFu) L = 0x007FFFFFu;        // key(-inf)
-      if (U > 0xFF800000u) U = 0xFF800000u;        // key(+inf)
       if (L == 0x80000000u) L = 0x7FFFFFFFu;       // key(+0) -> key(-0)
       if (U == 0x7FFFFFFFu) U = 0x80000000u;       // key(-0) -> key(+0)
       uint32_t bs = 0;
       while (((U - L) >> bs) >= (uint32_t)kBrBins) ++bs;
       h->br_lo[g] = L; h->br_hi[g] = U >= L ? U : L; h->br_shift[g] = bs;
+      if (mono) { h->d_lo[g] = key_to_float(s_dkey[2 * g]); h->d_hi[g] = key_to_float(s_dkey[2 * g + 1]); }
     }
+    if (mono) { h->ds_lo = key_to_float(s_dkey[kTargets]); h->ds_hi = key_to_float(s_dkey[kTargets + 1]); }
+    // 1: no pixel of the SAMPLE comes near the sentinel -- the loop only certifies that none does
+    //    (thread-level range check, else force_retry); 2: the loop tests every pixel against ds_*
+    const uint32_t kSent = fast_key(-42.0f);
+    const bool far = !sentinel || kSent < h->smp_min || kSent > h->smp_max;
+    h->fast = (mono && s_fast) ? (far ? 1u : 2u) : 0u;
   }
 }
 
 constexpr int kWarpStage = 768;  // keys staged per warp; flushed once fewer than 512 slots remain
 
 template <bool kUseMask, bool kSentinel>
-__global__ void __launch_bounds__(kStatsThreads)
+__global__ void __launch_bounds__(kStatsThreads, 5)  // 48 registers: five CTAs per SM (41 KB of shared memory each)
 stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
                   const int32_t* __restrict__ status, StatsWs ws) {
   __shared__ uint32_t s_stage[kStatsThreads / 32][kWarpStage];
@@ -464,6 +521,126 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   };
 
   const int last_tile = min(first_tile + kStatsTilesPerCta, (int)vp->n_tiles);
+  if (h->fast) {
+    // Depth-domain loop (stats_bracket_kernel): the bracket tests are float comparisons on the raw
+    // depth, a pixel outside the population becomes NaN (fails every comparison, skipped by
+    // fminf / fmaxf), the stage holds raw depths and flush_raw() aligns them.  NaN / inf in the
+    // population and pixels that may equal the sentinel after alignment are only DETECTED here;
+    // such a view goes through the exact path (force_retry).
+    const float D0lo = h->d_lo[0], D0hi = h->d_hi[0], D1lo = h->d_lo[1], D1hi = h->d_hi[1];
+    float fmn = INFINITY, fmx = -INFINITY, nanacc = 0.f;
+    constexpr int kColSlotsF = kWarpStage / 32;  // 24 candidates per lane between flushes
+    const uint32_t sp0 = (uint32_t)__cvta_generic_to_shared(stage + lane);
+    uint32_t sp = sp0;
+    const uint32_t* col = stage + lane;
+    const float Slo = h->ds_lo, Shi = h->ds_hi;
+    auto feedf = [&](float dv, bool pop, auto count_tag, auto sent_tag) {
+      constexpr bool kCount = decltype(count_tag)::value;
+      if (decltype(sent_tag)::value) {  // exact sentinel test: aligned == -42.0 <=> Slo <= depth <= Shi
+        const bool hit = pop & (dv >= Slo) & (dv <= Shi);
+        if (!kCount) cnt -= hit ? 1u : 0u;  // (the caller counted the mask bytes)
+        pop = pop & !hit;
+      }
+      const float x = pop ? dv : __uint_as_float(0x7FC00000u);
+      fmn = fminf(fmn, x);
+      fmx = fmaxf(fmx, x);
+      if (kCount) cnt += pop ? 1u : 0u;
+      if (pop) nanacc = __fmaf_rn(dv, 0.f, nanacc);
+      const bool lt0 = x < D0lo, lt1 = x < D1lo;
+      below0 += lt0 ? 1u : 0u;
+      below1 += lt1 ? 1u : 0u;
+      // no short circuit: a NaN fails the <= tests, so !lt alone letting it through is harmless
+      const bool c = (!lt0 & (x <= D0hi)) | (!lt1 & (x <= D1hi));
+      // candidates go to the lane's own column of the warp's stage: no vote, no prefix
+      // (one 32-bit shared-window address: a generic pointer costs four predicated adds per pixel)
+      if (c) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(sp), "f"(dv) : "memory"); sp += 128; }
+    };
+    const uint32_t cap32 = (uint32_t)(ws.c_cap < (int64_t)0x7fffffff ? ws.c_cap : (int64_t)0x7fffffff);
+    auto flush_raw = [&]() {
+      const uint32_t n = (sp - sp0) >> 7;  // this lane's candidates
+      const uint32_t maxn = __reduce_max_sync(0xffffffffu, n);
+      const uint32_t tot = __reduce_add_sync(0xffffffffu, n);
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(&h->n_cand, tot);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      for (uint32_t j = 0; j < maxn; ++j) {  // row by row: coalesced appends (each lane reads its own column)
+        const bool has = j < n;
+        const uint32_t m = __ballot_sync(0xffffffffu, has);
+        if (has) {
+          const uint32_t key = fast_key(align_depth(__uint_as_float(col[j * 32]), s, t));
+          const uint32_t o0 = key - L0, o1 = key - L1;
+          if (o0 <= W0) atomicAdd(&s_brhist[0][o0 >> sh0], 1u);
+          if (o1 <= W1) atomicAdd(&s_brhist[1][o1 >> sh1], 1u);
+          const uint32_t at = base + __popc(m & lt);
+          if (at < cap32) cand[at] = key;
+        }
+        base += __popc(m);
+      }
+      sp = sp0;
+    };
+    // L2 prefetch two tiles ahead (one 128-byte line per thread: 128 lines of depth + 32 of mask per
+    // tile): the loop holds only one tile of loads per warp in registers, the prefetches keep more
+    // DRAM requests in flight without registers, and the register loads then hit L2
+    constexpr int kPrefetchAhead = 2;
+    auto prefetch_tile = [&](int tile) {
+      if (tile >= last_tile) return;
+      const int64_t px0 = (int64_t)tile * MDI_TILE_PX;
+      const int t = threadIdx.x;
+      if (t < 128) {
+        const int64_t p = px0 + t * 32;
+        if (p < HW) asm volatile("prefetch.global.L2 [%0];" ::"l"(depth + p));
+      } else if (t < 160 && pmask) {
+        const int64_t p = px0 + (t - 128) * 128;
+        if (p < HW) asm volatile("prefetch.global.L2 [%0];" ::"l"(pmask + p));
+      }
+    };
+    auto stream_tiles = [&](auto sent_tag) {
+#pragma unroll 1
+      for (int tile = first_tile; tile < last_tile; ++tile) {
+        const int64_t px0 = (int64_t)tile * MDI_TILE_PX;
+        prefetch_tile(tile + kPrefetchAhead);
+        if (vec_ok && px0 + MDI_TILE_PX <= HW) {
+          // 4 x (128-bit depth + 32-bit mask) loads in flight per thread, then the arithmetic
+          float4 d4[4];
+          uint32_t mk[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int64_t p = px0 + (int64_t)(k * kStatsThreads + threadIdx.x) * 4;
+            d4[k] = __ldg(reinterpret_cast<const float4*>(depth + p));
+            mk[k] = pmask ? __ldg(reinterpret_cast<const uint32_t*>(pmask + p)) : 0x01010101u;
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            // bit 7 of every non-zero mask byte: the population of 4 pixels counted by one popc
+            const uint32_t nz = (mk[k] | ((mk[k] & 0x7f7f7f7fu) + 0x7f7f7f7fu)) & 0x80808080u;
+            cnt += __popc(nz);
+            feedf(d4[k].x, (nz & 0x80u) != 0, std::false_type{}, sent_tag); feedf(d4[k].y, (nz & 0x8000u) != 0, std::false_type{}, sent_tag);
+            feedf(d4[k].z, (nz & 0x800000u) != 0, std::false_type{}, sent_tag); feedf(d4[k].w, (nz & 0x80000000u) != 0, std::false_type{}, sent_tag);
+          }
+        } else {
+          for (int k = threadIdx.x; k < MDI_TILE_PX; k += kStatsThreads) {  // uniform trip count
+            const int64_t p = px0 + k;
+            const bool in = p < HW;
+            feedf(in ? __ldg(&depth[p]) : 0.f, in && (pmask ? __ldg(&pmask[p]) != 0 : true), std::true_type{}, sent_tag);
+          }
+        }
+        // a tile adds at most 16 candidates per lane
+        if (__any_sync(0xffffffffu, sp - sp0 > (uint32_t)((kColSlotsF - 16) * 128))) flush_raw();
+      }
+    };
+    prefetch_tile(first_tile);
+    prefetch_tile(first_tile + 1);
+    const bool per_pixel_sentinel = kSentinel && h->fast == 2u;
+    if (per_pixel_sentinel) stream_tiles(std::true_type{}); else stream_tiles(std::false_type{});
+    if (__any_sync(0xffffffffu, sp != sp0)) flush_raw();
+    // thread-level detection of what this loop does not handle
+    bool bad = !(fabsf(nanacc) == 0.f) || (cnt && (fmn == -INFINITY || fmx == INFINITY));
+    if (kSentinel && !per_pixel_sentinel) bad = bad || (cnt && Slo <= Shi && fmn <= Shi && fmx >= Slo);
+    if (bad) h->force_retry = 1u;
+    // monotone alignment: the extreme aligned values are those of the extreme depths
+    kmin = fast_key(align_depth(fmn, s, t));
+    kmax = fast_key(align_depth(fmx, s, t));
+  } else {
 #pragma unroll 1
   for (int tile = first_tile; tile < last_tile; ++tile) {
     const int64_t px0 = (int64_t)tile * MDI_TILE_PX;
@@ -492,6 +669,7 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
     if (wcount > (uint32_t)(kWarpStage - 512)) flush();  // a tile adds at most 512 keys per warp
   }
   if (wcount) flush();
+  }
   kmin = __reduce_min_sync(0xffffffffu, kmin);
   kmax = __reduce_max_sync(0xffffffffu, kmax);
   cnt = __reduce_add_sync(0xffffffffu, cnt);
@@ -748,7 +926,8 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
   const uint32_t Wd[2] = {h->br_hi[0] - L[0], h->br_hi[1] - L[1]};
   const uint32_t sft[2] = {h->br_shift[0], h->br_shift[1]};
   if (tid < kTargets) { s_len[tid] = 0; s_bin[tid] = 0xFFFFFFFFu; s_out[tid] = 0; }
-  if (tid == 0) s_fail = (int64_t)n_cand > ws.c_cap ? 1u : 0u;   // 1: candidate list overflow
+  // 1: candidate list overflow, 6: the depth-domain loop met NaN / inf or a possible sentinel hit
+  if (tid == 0) s_fail = (int64_t)n_cand > ws.c_cap ? 1u : (h->force_retry ? 6u : 0u);
   __syncthreads();
   if (!has_nan && !s_fail) {
     // 1. bin of each target rank in its bracket histogram (2 bins per thread)
@@ -1107,7 +1286,7 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     stats_sample_kernel<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n_views), 256, 0, st>>>(
         views, scale_shift, status, pop, ws);
     mdi::prof_mark("stats_bracket_kernel", st);
-    stats_bracket_kernel<<<n_views, kBracketThreads, 0, st>>>(status, ws);
+    stats_bracket_kernel<<<n_views, kBracketThreads, 0, st>>>(scale_shift, status, (pop & MDI_KEEP_SENTINEL) ? 1 : 0, ws);
     const bool um = pop & MDI_KEEP_PRED_MASK, se = pop & MDI_KEEP_SENTINEL;
     // 0: register-staged kernel (default), 1: TMA-staged kernel (MDI_STATS_MAIN=tma; bit-identical
     // results, measured slower so far: 0.42 vs 0.33 ms on C2)

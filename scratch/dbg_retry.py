@@ -18,7 +18,7 @@ class P:
         if n != "mdi_depth_range": return f
         def g(*a):
             rc = f(*a); torch.cuda.synchronize()
-            snaps.append(eng._ws["stats_ws"][:200 * 184].cpu().numpy().view(np.uint32).reshape(200, 46).copy()); return rc
+            snaps.append(eng._ws["stats_ws"][:200 * 216].cpu().numpy().view(np.uint32).reshape(200, 54).copy()); return rc
         return g
 eng.lib = P(eng.lib)
 torch.manual_seed(1234)
@@ -29,9 +29,11 @@ for step in range(40):
     h = snaps[0]
     fc = h[:, 32]
     bad = np.nonzero(fc)[0]
+    if step == 0: print('fast views', int(h[:, 46].sum()), 'of', len(h), 'force_retry', int(h[:, 47].sum()))
     if len(bad) == 0: continue
     print(step, "retry", res.extras.get("stats_retry"), "bad views", bad.tolist(), [int(fc[i]) for i in bad])
     for i in bad[:3]:
         d = dict(zip(names, h[i, :14].tolist()))
         n = d["count"]
+        print("    fast", int(h[i, 46]), "force", int(h[i, 47]), "dlo/dhi/ds", h[i, 48:54].view(np.float32).tolist())
         print("   ", d, "r1", 0.25 * (n - 1), "r3", 0.75 * (n - 1), "ss", res.scale_shift[i].tolist())

@@ -278,6 +278,70 @@ def test_quantile_one_pass_path_equals_exact_path_and_torch():
 
 
 @pytest.mark.gpu
+def test_quantile_depth_domain_loop_with_scale_shift_and_odd_populations():
+    """a7 with a scale/shift applied on the fly: the one-pass kernel tests raw depths against
+    depth-domain brackets (monotone alignment, stats_bracket_kernel).  Positive scales take that
+    loop, a negative scale the key-domain loop; NaN / inf in the population and pixels that hit
+    the -42.0 sentinel after alignment must be noticed and sent through the exact path.  All
+    bit-identical to torch.quantile on the aligned values."""
+    L = mod("_lib")
+    single = mod("_single")
+    E = mod("engine")
+    g = torch.Generator().manual_seed(11)
+    H, W = 600, 800
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    d = 4 + 1.5 * torch.sin(xx / 123.0) + torch.cos(yy / 107.0) + 0.01 * torch.randn(H, W, generator=g)
+    mask = torch.ones(H, W, dtype=torch.bool); mask[50:200, 100:500] = False
+    odd_mask = mask.to(torch.uint8) * 7  # any non-zero byte counts
+    d_nan = d.clone(); d_nan[300, 400] = float("nan")
+    d_nan_out = d.clone(); d_nan_out[100, 200] = float("nan")   # outside the population: harmless
+    d_inf = d.clone(); d_inf[10, 10] = float("inf")
+    s_sent, t_sent = 2.0, -50.0
+    d_sent = d.clone(); d_sent[400:420, 300:340] = 4.0            # 4 * 2 - 50 = -42 exactly
+    d_far = d.clone(); d_far[77, 99] = -42.0
+    cases = [("plain", d, mask, 2.37, -0.81, False, False),
+             ("cross_zero", d, mask, 1.7, -7.0, False, False),
+             ("tiny_scale", d, mask, 1e-30, 0.0, False, None),
+             ("neg_scale", d, mask, -1.3, 9.0, False, False),
+             ("nan_in", d_nan, mask, 1.5, 0.25, False, True),
+             ("nan_out", d_nan_out, mask, 1.5, 0.25, False, False),
+             ("inf_in", d_inf, mask, 1.5, 0.25, False, True),
+             ("sentinel_hit", d_sent, mask, s_sent, t_sent, True, False),   # in the sample's range: tested per pixel
+             ("sentinel_far_hit", d_far, mask, 1.0, 0.0, True, True),        # outside it: noticed, exact path
+             ("sentinel_flag_no_hit", d, mask, 2.37, -0.81, True, False)]
+    for name, dd, m, sc, sh, sentinel, expect_retry in cases:
+        a = dd * torch.tensor(sc, dtype=torch.float32) + torch.tensor(sh, dtype=torch.float32)
+        pop = m & (a != -42.0) if sentinel else m
+        lo, hi = O.adaptive_range(a, pop)[:2]
+        flags = L.KEEP_PRED_MASK | L.KEEP_SUBSAMPLE | (L.KEEP_SENTINEL if sentinel else 0)
+        out = {}
+        for exact in (False, True):
+            eng = E.get_engine(DEV)
+            vin = single.single_view_inputs(dd.to(DEV), m.to(DEV), DEV)
+            opt = E.RunOptions(aligner=None, scale_shift=torch.tensor([[sc, sh]], dtype=torch.float32, device=DEV),
+                               subsample="adaptive", use_patch_mask=False, flags=flags, want_xyz=False,
+                               want_rgb=False, stop_after="mask", stats_exact=exact)
+            out[exact] = eng.run(vin, opt)
+            lh = out[exact].lo_hi[0].cpu()
+            ref = torch.tensor([float(lo), float(hi)])
+            assert torch.equal(lh.isnan(), ref.isnan()) and torch.equal(lh.nan_to_num(0.0), ref.nan_to_num(0.0)), \
+                (name, exact, lh, lo, hi)
+        qf, qe = out[False].quantiles.cpu(), out[True].quantiles.cpu()
+        assert torch.equal(qf.isnan(), qe.isnan()) and torch.equal(qf.nan_to_num(0.0), qe.nan_to_num(0.0)), name
+        assert torch.equal(out[False].keep.cpu(), out[True].keep.cpu()), name
+        if expect_retry is not None:
+            assert bool(out[False].extras.get("stats_retry", False)) == expect_retry, name
+    # a mask whose non-zero bytes are not 1
+    eng = E.get_engine(DEV)
+    base = dict(aligner=None, scale_shift=torch.tensor([[2.37, -0.81]], dtype=torch.float32, device=DEV),
+                subsample="adaptive", use_patch_mask=False, flags=L.KEEP_PRED_MASK | L.KEEP_SUBSAMPLE,
+                want_xyz=False, want_rgb=False, stop_after="mask")
+    r1 = eng.run(single.single_view_inputs(d.to(DEV), mask.to(DEV), DEV), E.RunOptions(**base))
+    r7 = eng.run(single.single_view_inputs(d.to(DEV), odd_mask.to(DEV), DEV), E.RunOptions(**base))
+    assert torch.equal(r1.quantiles.cpu(), r7.quantiles.cpu()) and torch.equal(r1.lo_hi.cpu(), r7.lo_hi.cpu())
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("chunks", [1, 3, 16])
 def test_host_views_end_to_end_path_equals_resident_path(chunks):
     """points_from_host_views (pinned host depth / mask / image, chunked copy-compute overlap, rgb
