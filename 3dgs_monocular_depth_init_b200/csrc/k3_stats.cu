@@ -413,11 +413,20 @@ stats_bracket_kernel(const float* __restrict__ scale_shift, const int32_t* __res
     const uint32_t bound = tid < kTargets ? s_LU[tid] : kSent;
     auto F = [&](uint32_t kd) { return fast_key(align_depth(key_to_float(kd), s, t)); };
     uint32_t lo = kKeyNegInf, hi = kKeyPosInf;
+    // the answer is usually within a few floats of (bound - t) / s: try a 33-float window first
+    const float guess = fdiv(fsub(key_to_float(bound), t), s);
+    uint32_t wlo = kKeyNegInf, whi = kKeyPosInf;
+    if (guess == guess) {
+      const uint32_t kg = fast_key(guess);
+      if (kg > kKeyNegInf + 16u && kg < kKeyPosInf - 16u) { wlo = kg - 16u; whi = kg + 16u; }
+    }
     if ((tid & 1) == 0) {  // smallest kd with F(kd) >= bound
+      if (wlo != kKeyNegInf && F(whi) >= bound && F(wlo) < bound) { lo = wlo + 1u; hi = whi; }
       if (F(hi) < bound) s_fast = 0;
       while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if (F(mid) >= bound) hi = mid; else lo = mid + 1; }
       if (tid < kTargets && lo == 0x80000000u) lo = 0x7FFFFFFFu;  // +0 -> -0: a float test cannot tell them apart
     } else {               // largest kd with F(kd) <= bound
+      if (wlo != kKeyNegInf && F(wlo) <= bound && F(whi) > bound) { lo = wlo; hi = whi - 1u; }
       if (F(lo) > bound) s_fast = 0;
       while (lo < hi) { const uint32_t mid = lo + ((hi - lo + 1) >> 1); if (F(mid) <= bound) lo = mid; else hi = mid - 1; }
       if (tid < kTargets && lo == 0x7FFFFFFFu) lo = 0x80000000u;  // -0 -> +0
@@ -458,7 +467,7 @@ constexpr int kWarpStage = 768;  // keys staged per warp; flushed once fewer tha
 template <bool kUseMask, bool kSentinel>
 __global__ void __launch_bounds__(kStatsThreads, 5)  // 48 registers: five CTAs per SM (41 KB of shared memory each)
 stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
-                  const int32_t* __restrict__ status, StatsWs ws) {
+                  const int32_t* __restrict__ status, StatsWs ws, int prefetch_ahead) {
   __shared__ uint32_t s_stage[kStatsThreads / 32][kWarpStage];
   __shared__ uint32_t s_brhist[2][kBrBins];
   __shared__ uint32_t s_min, s_max, s_cnt, s_below[2];
@@ -541,9 +550,7 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
         if (!kCount) cnt -= hit ? 1u : 0u;  // (the caller counted the mask bytes)
         pop = pop & !hit;
       }
-      const float x = pop ? dv : __uint_as_float(0x7FC00000u);
-      fmn = fminf(fmn, x);
-      fmx = fmaxf(fmx, x);
+      const float x = pop ? dv : __uint_as_float(0x7FC00000u);  // returned: the caller folds it into min / max
       if (kCount) cnt += pop ? 1u : 0u;
       if (pop) nanacc = __fmaf_rn(dv, 0.f, nanacc);
       const bool lt0 = x < D0lo, lt1 = x < D1lo;
@@ -554,7 +561,11 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
       // candidates go to the lane's own column of the warp's stage: no vote, no prefix
       // (one 32-bit shared-window address: a generic pointer costs four predicated adds per pixel)
       if (c) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(sp), "f"(dv) : "memory"); sp += 128; }
+      return x;
     };
+    // three-input min / max (FMNMX3, NaN operands skipped like fminf / fmaxf): two pixels per instruction
+    auto min3 = [](float a, float b, float c) { float d; asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d; };
+    auto max3 = [](float a, float b, float c) { float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d; };
     const uint32_t cap32 = (uint32_t)(ws.c_cap < (int64_t)0x7fffffff ? ws.c_cap : (int64_t)0x7fffffff);
     auto flush_raw = [&]() {
       const uint32_t n = (sp - sp0) >> 7;  // this lane's candidates
@@ -581,7 +592,6 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
     // L2 prefetch two tiles ahead (one 128-byte line per thread: 128 lines of depth + 32 of mask per
     // tile): the loop holds only one tile of loads per warp in registers, the prefetches keep more
     // DRAM requests in flight without registers, and the register loads then hit L2
-    constexpr int kPrefetchAhead = 2;
     auto prefetch_tile = [&](int tile) {
       if (tile >= last_tile) return;
       const int64_t px0 = (int64_t)tile * MDI_TILE_PX;
@@ -598,7 +608,7 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
 #pragma unroll 1
       for (int tile = first_tile; tile < last_tile; ++tile) {
         const int64_t px0 = (int64_t)tile * MDI_TILE_PX;
-        prefetch_tile(tile + kPrefetchAhead);
+        prefetch_tile(tile + prefetch_ahead);
         if (vec_ok && px0 + MDI_TILE_PX <= HW) {
           // 4 x (128-bit depth + 32-bit mask) loads in flight per thread, then the arithmetic
           float4 d4[4];
@@ -614,22 +624,27 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
             // bit 7 of every non-zero mask byte: the population of 4 pixels counted by one popc
             const uint32_t nz = (mk[k] | ((mk[k] & 0x7f7f7f7fu) + 0x7f7f7f7fu)) & 0x80808080u;
             cnt += __popc(nz);
-            feedf(d4[k].x, (nz & 0x80u) != 0, std::false_type{}, sent_tag); feedf(d4[k].y, (nz & 0x8000u) != 0, std::false_type{}, sent_tag);
-            feedf(d4[k].z, (nz & 0x800000u) != 0, std::false_type{}, sent_tag); feedf(d4[k].w, (nz & 0x80000000u) != 0, std::false_type{}, sent_tag);
+            const float x0 = feedf(d4[k].x, (nz & 0x80u) != 0, std::false_type{}, sent_tag);
+            const float x1 = feedf(d4[k].y, (nz & 0x8000u) != 0, std::false_type{}, sent_tag);
+            const float x2 = feedf(d4[k].z, (nz & 0x800000u) != 0, std::false_type{}, sent_tag);
+            const float x3 = feedf(d4[k].w, (nz & 0x80000000u) != 0, std::false_type{}, sent_tag);
+            fmn = min3(min3(fmn, x0, x1), x2, x3);
+            fmx = max3(max3(fmx, x0, x1), x2, x3);
           }
         } else {
           for (int k = threadIdx.x; k < MDI_TILE_PX; k += kStatsThreads) {  // uniform trip count
             const int64_t p = px0 + k;
             const bool in = p < HW;
-            feedf(in ? __ldg(&depth[p]) : 0.f, in && (pmask ? __ldg(&pmask[p]) != 0 : true), std::true_type{}, sent_tag);
+            const float x = feedf(in ? __ldg(&depth[p]) : 0.f, in && (pmask ? __ldg(&pmask[p]) != 0 : true), std::true_type{}, sent_tag);
+            fmn = fminf(fmn, x);
+            fmx = fmaxf(fmx, x);
           }
         }
         // a tile adds at most 16 candidates per lane
         if (__any_sync(0xffffffffu, sp - sp0 > (uint32_t)((kColSlotsF - 16) * 128))) flush_raw();
       }
     };
-    prefetch_tile(first_tile);
-    prefetch_tile(first_tile + 1);
+    for (int a = 0; a < prefetch_ahead; ++a) prefetch_tile(first_tile + a);
     const bool per_pixel_sentinel = kSentinel && h->fast == 2u;
     if (per_pixel_sentinel) stream_tiles(std::true_type{}); else stream_tiles(std::false_type{});
     if (__any_sync(0xffffffffu, sp != sp0)) flush_raw();
@@ -1302,16 +1317,22 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
         if (a0 != cudaSuccess || a1 != cudaSuccess || a2 != cudaSuccess || a3 != cudaSuccess) { cudaGetLastError(); main_variant = 0; }
       }
     }
+    static int prefetch_ahead = -1;  // tiles of L2 prefetch in the depth-domain loop (MDI_STATS_PREFETCH, 0 = off)
+    if (prefetch_ahead < 0) {
+      const char* e = getenv("MDI_STATS_PREFETCH");
+      prefetch_ahead = e ? atoi(e) : 2;
+      if (prefetch_ahead < 0 || prefetch_ahead > 16) prefetch_ahead = 2;
+    }
     mdi::prof_mark("stats_main_kernel", st);
     if (main_variant == 1) {
       if (um && se) stats_main_tma_kernel<true, true><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
       else if (um) stats_main_tma_kernel<true, false><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
       else if (se) stats_main_tma_kernel<false, true><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
       else stats_main_tma_kernel<false, false><<<grid, kStatsThreads, kTmaSmemBytes, st>>>(views, scale_shift, status, ws);
-    } else if (um && se) stats_main_kernel<true, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
-    else if (um) stats_main_kernel<true, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
-    else if (se) stats_main_kernel<false, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
-    else stats_main_kernel<false, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws);
+    } else if (um && se) stats_main_kernel<true, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws, prefetch_ahead);
+    else if (um) stats_main_kernel<true, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws, prefetch_ahead);
+    else if (se) stats_main_kernel<false, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws, prefetch_ahead);
+    else stats_main_kernel<false, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws, prefetch_ahead);
     mdi::prof_mark("stats_finish_kernel", st);
     stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
   } else {
