@@ -3,7 +3,7 @@
 // (adaptive_subsampling.py:82-95).  Also the gradient-map range for a9.
 //
 // Fast path ("sample-select", ONE streaming pass over depth + mask, HBM-bound):
-//   1. stats_sample_kernel   reads one hashed 32-byte sector (8 pixels) out of every 16: HW/16 keys
+//   1. stats_sample_kernel   reads one hashed 128-byte line (32 pixels) out of every 16: HW/16 keys
 //   2. stats_bracket_kernel  radix-selects, in that sample, key brackets [L, U] around each
 //                            quantile wide enough to hold the true order statistics
 //   3. stats_main_kernel     the one full pass: min / max / count, the number of keys below each
@@ -224,7 +224,12 @@ stats_sample_kernel(const MdiView* __restrict__ views, const float* __restrict__
   const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
   const float* __restrict__ depth = vp->depth;
   const uint8_t* __restrict__ pmask = vp->mask;
-  const int64_t p0 = group * kSampleGroup + (hash32((uint32_t)group * 2654435761u + (uint32_t)v) & 15u) * 8;
+  // Four consecutive groups (512 pixels) sample the four sectors of ONE hashed 128-byte depth line
+  // of the 16 they span: DRAM serves 128-byte lines, so a lone 32-byte sector per group costs a
+  // whole line of depth and a whole line of mask (4x the traffic for the same sample size)
+  const int64_t super = group >> 2;
+  const uint32_t hsh = hash32((uint32_t)super * 2654435761u + (uint32_t)v);
+  const int64_t p0 = super * (4 * kSampleGroup) + (int64_t)(hsh & 15u) * 32 + (group & 3) * 8;
   uint32_t keys[8];
   uint32_t valid = 0;  // bit k: keys[k] is in the population
   if (p0 < HW) {
