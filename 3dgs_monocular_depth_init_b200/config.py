@@ -6,6 +6,7 @@ from dataclasses import dataclass, field
 from typing import Literal, Optional, Union
 
 from .depth_alignment.config import DepthAlignmentConfig
+from .depth_prediction.configs import DepthAnythingV2Config, Metric3dV2Config, MogeConfig, UnidepthConfig
 from .depth_subsampling.config import AdaptiveSubsamplingConfig, NumSfMPointsMaskConfig
 from .point_cloud_postprocess.config import PointCloudPostprocessConfig
 
@@ -13,6 +14,11 @@ from .point_cloud_postprocess.config import PointCloudPostprocessConfig
 @dataclass
 class MonocularDepthInitConfig:
     predictor: Optional[Literal["metric3d", "moge", "unidepth", "depth_anything_v2", "depth_pro"]] = "metric3d"
+    # predictor sub-configs: only their `name` matters here (component of the depth-cache path)
+    metric3d: Metric3dV2Config = field(default_factory=Metric3dV2Config)
+    unidepth: UnidepthConfig = field(default_factory=UnidepthConfig)
+    depthanything: DepthAnythingV2Config = field(default_factory=DepthAnythingV2Config)
+    moge: MogeConfig = field(default_factory=MogeConfig)
     alignment: DepthAlignmentConfig = field(default_factory=DepthAlignmentConfig)
     depth_grad_mask_thresh: Optional[float] = None
     include_sfm_points: bool = True

@@ -76,6 +76,7 @@ def get_pts_from_depth(predicted_depth: PredictedDepth, image: InputImage, parse
             opt.sample_idx = sample_idx.to(device=dev, dtype=torch.int32).contiguous()[None]
         else:
             opt.ransac_seed = ransac_seed()
+        opt.want_inliers = bool(return_result)   # RunResult.inlier_mask: the final inlier set (ransacs.py:150-151)
     vin = single_view_inputs(predicted_depth.depth, predicted_depth.mask, dev, K=image.K, c2w=image.cam2world,
                              sfm_xyz=sfm.contiguous(), sfm_counts=[M])
     res = eng.run(vin, opt)

@@ -17,6 +17,12 @@ class PredictedDepth:
     normal_confidence: Optional[torch.Tensor] = None
 
 
+# torch.load(weights_only=True) of a cached PredictedDepth (reference :42-43).  Cache files written
+# by the reference name the class by ITS module path; both spellings resolve to this dataclass.
+REFERENCE_QUALNAME = "gs_init_compare.depth_prediction.predictors.depth_predictor_interface.PredictedDepth"
+torch.serialization.add_safe_globals([PredictedDepth, (PredictedDepth, REFERENCE_QUALNAME)])
+
+
 class CameraIntrinsics(NamedTuple):
     K: torch.Tensor
 

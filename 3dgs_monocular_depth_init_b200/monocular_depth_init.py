@@ -7,6 +7,8 @@ PredictedDepth` (cached depth, a predictor, or synthetic depth)."""
 from __future__ import annotations
 
 import logging
+import sys
+from pathlib import Path
 from typing import Callable, List, Optional
 
 import numpy as np
@@ -145,35 +147,84 @@ def points_from_views(config, depths, masks, images, K, c2w, names, points: np.n
     return eng.run(vin, opt)
 
 
+def _export_per_image(out_dir, parser, names, images, K_all, c2w_all, res, counts, status):
+    """`mdi.pts_output_per_image`: the four clouds the reference dumps per view
+    (points_from_depth.py:47-108 `debug_export_point_clouds`): the image plane in world space, the
+    view's SfM points projected onto that plane, the SfM points, and the view's unprojected points.
+    (The matplotlib depth / alignment plots of :33-45 and pipeline.py:30-167 are not produced.)"""
+    from .utils.point_cloud_export import export_point_cloud_to_ply
+    P_all = res.P.cpu()
+    xyz, rgb = res.xyz.cpu().numpy(), (res.rgb.cpu().numpy() if res.rgb is not None else None)
+    offs = np.concatenate([[0], np.cumsum(counts)])
+    for i, name in enumerate(names):
+        if status[i] & L.STATUS_LOW_CONFIDENCE:   # the reference raises before its export
+            continue
+        d = Path(out_dir) / name
+        d.mkdir(exist_ok=True, parents=True)
+        im = images[i].cpu()
+        H, W = int(im.shape[0]), int(im.shape[1])
+        K, c2w = K_all[i].float(), c2w_all[i].float()
+
+        def to_world(pc):   # points_from_depth.py:302-312
+            cam = torch.linalg.inv(K) @ pc.reshape(-1, 3).T
+            return (c2w @ torch.vstack([cam, torch.ones(cam.shape[1])]))[:3].T
+
+        plane = torch.dstack([torch.from_numpy(np.mgrid[0:W, 0:H].T).float(), torch.ones((W, H)).T]).reshape(-1, 3)
+        export_point_cloud_to_ply(to_world(plane).numpy(), (im.float() / 255.0).reshape(-1, 3).numpy(), d, "camera_plane")
+        idx = np.asarray(parser.point_indices[name])
+        sfm = torch.from_numpy(np.ascontiguousarray(parser.points[idx])).float()
+        sfm_rgb = parser.points_rgb[idx] / 255.0
+        proj = P_all[i] @ torch.vstack([sfm.T, torch.ones(sfm.shape[0])])
+        proj = proj / proj[2]
+        export_point_cloud_to_ply(to_world(proj.T).numpy(), sfm_rgb, d, "sfm_points_plane_proj")
+        export_point_cloud_to_ply(sfm.numpy(), sfm_rgb, d, "sfm_points_world")
+        a, b = int(offs[i]), int(offs[i + 1])
+        export_point_cloud_to_ply(xyz[a:b], None if rgb is None else rgb[a:b], d, "my_points_world")
+
+
 @torch.no_grad()
 def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth_source: Optional[Callable] = None):
     """-> (pts float32 [N,3] on device, rgbs float32 [N,3] on CPU, scales [N,3] | None);
-    monocular_depth_init.py:95-224."""
-    depth_source = depth_source or DEPTH_SOURCE
-    if depth_source is None:
-        raise ValueError("no depth source: the depth predictors are outside the B200 path; pass "
-                         "depth_source=(image, data, device) -> PredictedDepth or set DEPTH_SOURCE")
+    monocular_depth_init.py:95-224, same signature (runner.py:77-78 calls it unchanged).
+
+    Depth per view comes from `depth_source(image, data, device) -> PredictedDepth` (image.data is
+    the dataset's 0..255 image); the default is the reference's predicted-depth cache
+    (`depth_prediction.depth_cache.CachedDepthSource`:
+    `<mdi.cache_dir>/<model.name>/<parser.dataset_name>/<image_name>.pth`), which raises
+    `DepthCacheMiss` for an image that is not cached unless a predictor has been registered."""
     eng = get_engine(device)
     dev = eng.device
+    depth_source = depth_source or DEPTH_SOURCE
+    model_label = getattr(depth_source, "name", None)
+    if depth_source is None:
+        from .depth_prediction.depth_cache import CachedDepthSource
+        depth_source = CachedDepthSource(config, getattr(parser, "dataset_name", "dataset"), dev)
+        model_label = depth_source.name
+    if config.mdi.pts_output_dir is not None and model_label is None:
+        from .depth_prediction.depth_cache import model_name
+        model_label = model_name(config)
     depths, masks, images, K, c2w, names = gather_scene(parser, dev, depth_source)
     # images stay where the dataset put them (CPU in the reference): pin so the gather kernel
     # reads only the kept pixels over PCIe instead of copying 12 B/px
     imgs = [im if im.is_cuda else im.contiguous().pin_memory() for im in images]
     kind = L.IMAGE_U8 if imgs and imgs[0].dtype == torch.uint8 else L.IMAGE_F32_255
     res = points_from_views(config, depths, masks, imgs, K, c2w, names, parser.points, parser.point_indices, dev, kind)
-    status = res.status.cpu().numpy()
-    counts = res.view_counts.cpu().numpy()
+    status = res.status.cpu().numpy() if res.status is not None else np.zeros(0, np.int32)
+    counts = res.view_counts.cpu().numpy() if res.view_counts is not None else np.zeros(0, np.int64)
     for i in np.nonzero(status & L.STATUS_LOW_CONFIDENCE)[0]:
         _LOGGER.warning("Low depth alignment confidence for image %s", names[i])
     if (status & L.STATUS_EMPTY_STATS).any():
         raise RuntimeError("quantile() input tensor must be non-empty")
-    pts, rgbs = res.xyz, res.rgb
+    pts = res.xyz if res.xyz is not None else torch.zeros((0, 3), dtype=torch.float32, device=dev)
+    rgbs = res.rgb if res.rgb is not None else torch.zeros((0, 3), dtype=torch.float32, device=dev)
+    if config.mdi.pts_output_dir and config.mdi.pts_output_per_image:   # monocular_depth_init.py:142-146
+        _export_per_image(config.mdi.pts_output_dir, parser, names, images, K, c2w, res, counts, status)
     if config.mdi.noise_std_scene_frac is not None:
         pts = add_noise_to_point_cloud(pts, parser.scene_scale * config.mdi.noise_std_scene_frac)
     rgbs = rgbs.cpu()
     ok = (status & L.STATUS_LOW_CONFIDENCE) == 0
     Kn = K.cpu().numpy()
-    Pn = res.P.cpu().numpy()
+    Pn = res.P.cpu().numpy() if res.P is not None else np.zeros((0, 3, 4), np.float32)
     intrinsic_matrices = [Kn[i] for i in range(len(names)) if ok[i]]
     proj_matrices = [Pn[i] for i in range(len(names)) if ok[i]]
     # deviation from the reference (SURVEY 3.1): image_sizes is compacted to the kept views
@@ -186,6 +237,18 @@ def pts_and_rgb_from_monocular_depth(config, parser, device: str = "cuda", depth
     pts, rgbs = postprocess_point_cloud(pts, rgbs, intrinsic_matrices, proj_matrices, image_sizes,
                                         config.mdi.postprocess, dev)
     _LOGGER.info("Num points after postprocess: %d", pts.shape[0])
+    if config.mdi.pts_output_dir is not None:   # monocular_depth_init.py:198-211
+        from .utils.point_cloud_export import export_point_cloud_to_ply
+        output_dir = Path(config.mdi.pts_output_dir) / getattr(parser, "dataset_name", "dataset")
+        output_dir.mkdir(exist_ok=True, parents=True)
+        # the reference formats the `str, Enum` members under Python 3.10, i.e. by value
+        seg, alg = config.mdi.alignment.segmenter, config.mdi.alignment.aligner
+        filename = (f"{model_label}_{config.mdi.subsample_factor}_{getattr(seg, 'value', seg)}_"
+                    f"{getattr(alg, 'value', alg)}")
+        export_point_cloud_to_ply(pts.cpu().numpy(), rgbs.cpu().numpy(), output_dir, filename, outlier_std_dev=None)
+        export_point_cloud_to_ply(parser.points, parser.points_rgb / 255.0, output_dir, "sfm")
+    if config.mdi.pts_only:                     # :212-213
+        sys.exit(0)
     scales = None
     if config.mdi.limit_init_scale:  # monocular_depth_init.py:215-223
         dist2_avg = (knn(pts, 4)[:, 1:] ** 2).mean(dim=-1)

@@ -19,6 +19,8 @@ def mod(name=""):
 SMALL_CASES = ["small_lstsq_static4", "small_ransac_adaptive", "small_msac_static3_grad", "small_lowconf",
                "small_ransac_nopatch", "small_adaptive_range_3_9", "tall_lstsq_adaptive", "tall_msac_static5"]
 FULL_CASES = ["c1_lstsq_static10", "c2_ransac_adaptive"]
+# one view of each larger BASELINE shape (C3 1920x1080, C4 3840x2160, C5 1600x1200), RANSAC + adaptive
+BIG_CASES = ["c3_view_1920x1080", "c4_view_3840x2160", "c5_view_1600x1200"]
 
 _scene_cache = {}
 
@@ -53,7 +55,20 @@ def load_case(name):
     if not c.raised:
         H, W = c.depth.shape
         c.ref_keep = np.unpackbits(c.ref_keep)[: H * W].astype(bool)
+        if hasattr(c, "ref_ransac_inlier_mask"):  # final inlier set of the reference loop (ransacs.py:150-151)
+            c.ref_ransac_inlier_mask = np.unpackbits(c.ref_ransac_inlier_mask)[: c.ref_uv.shape[1]].astype(bool)
     return c
+
+
+def rgb_matches(c, rgb) -> bool:
+    """Bit-exact comparison of a gathered rgb array [Nk,3] float32 with the reference's: against the
+    stored array, or (large views) against the SHA-256 of the reference's bytes."""
+    import hashlib
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+    if hasattr(c, "ref_rgb"):
+        return np.array_equal(rgb, c.ref_rgb)
+    return rgb.shape[0] == int(c.ref_rgb_rows) and \
+        hashlib.sha256(rgb.tobytes()).digest() == bytes(c.ref_rgb_sha256.tobytes())
 
 
 def case_config(c):
