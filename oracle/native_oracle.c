@@ -3,9 +3,13 @@
  * tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may load the library this
  * file builds into (oracle/_build/libmdi_native_oracle.so, see oracle/build_oracle.py).
  *
- * PARITY UNPINNED: the reference module needs Eigen 3.4 + Conan + CMake, none of which exist
- * in the build container, and the reference holds no test or golden vector for it.  The Eigen
- * expressions are restated from their published evaluation rules:
+ * PARITY PIN: tests/test_native_ref_pin.py compares this file, bit for bit (extents, output count,
+ * emission order, positions, colours), with the reference's OWN impl.cpp / pointcloud_subsampling.cpp
+ * compiled unmodified into oracle/_ref/ by oracle/build_ref_native.py.  That build replaces Eigen
+ * 3.4 (third-party, absent here: no Conan, no network) by the stand-in headers of
+ * oracle/eigen_standin/, so the reference's control flow, partition rule, stack discipline and
+ * emission order are the reference's own code; what remains restated (here and in the stand-in
+ * alike) are Eigen's published evaluation rules for the few expressions used:
  *   - `P * point.homogeneous()` (impl.cpp:19-21) evaluates as leftCols(3)*p + col(3)
  *     (Eigen/src/Geometry/Homogeneous.h), each 3-term dot product reduced by the unrolled
  *     non-vectorised redux as a0 + (a1 + a2) (Eigen/src/Core/Redux.h);

@@ -1,5 +1,6 @@
 """TEST INFRASTRUCTURE -- ctypes loader for oracle/_build/libmdi_native_oracle.so (the C
-restatement of native_modules/subsampling/src/impl.cpp; parity unpinned, see native_oracle.c).
+restatement of native_modules/subsampling/src/impl.cpp; pinned against the reference's own compiled
+module in oracle/_ref by tests/test_native_ref_pin.py, see native_oracle.c).
 Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this."""
 import ctypes as C
 

@@ -1,9 +1,9 @@
 """a13/a14: minimal Gaussian extents and the k-d merge subsampling.
 
-CPU tests pin the C restatement (oracle/native_oracle.c) to hand-derived answers of the reference
-algorithm (impl.cpp:70-126, :313-426) -- the reference module itself cannot be built here (Eigen),
-so the parity of this row is UNPINNED beyond these.  GPU tests compare libmdi_b200.so with the
-restatement bit for bit (counts, order, fp32 values)."""
+CPU tests check the C restatement (oracle/native_oracle.c) against hand-derived answers of the
+reference algorithm (impl.cpp:70-126, :313-426); tests/test_native_ref_pin.py pins it bit for bit
+against the reference's own module compiled into oracle/_ref.  GPU tests compare libmdi_b200.so with
+the restatement bit for bit (counts, order, fp32 values)."""
 import numpy as np
 import pytest
 import torch
