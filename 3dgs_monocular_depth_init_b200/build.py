@@ -43,7 +43,7 @@ def _fingerprint() -> str:
     for f in files:
         h.update(f.name.encode())
         h.update(f.read_bytes())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(NVCC_FLAGS + ["-cudart shared"]).encode())
     return h.hexdigest()
 
 
@@ -70,7 +70,9 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         objs = list(ex.map(compile_one, _sources()))
-    cmd = [nvcc, "-shared", "-o", str(LIB_PATH), *map(str, objs)]
+    # shared cudart: the process already holds one CUDA runtime (torch's); a second, statically linked
+    # copy would only add its symbol table to the shipped binary
+    cmd = [nvcc, "-shared", "-cudart", "shared", "-o", str(LIB_PATH), *map(str, objs)]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

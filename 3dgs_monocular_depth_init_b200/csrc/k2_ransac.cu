@@ -347,12 +347,11 @@ extern "C" int mdi_ransac(const MdiView* views, int n_views, const float* d, con
   const int pts = (max_points + 3) & ~3;
   const size_t smem = (size_t)pts * 8;
   if (smem <= 200 * 1024) {
-    static size_t attr_set = 0;
-    if (smem > 32 * 1024 && smem > attr_set) {  // static + dynamic may not exceed 48 KB by default
+    // static + dynamic may not exceed 48 KB by default.  The opt-in is a per-device (context)
+    // attribute: set on every call that needs it (microseconds), never cached process-wide
+    if (smem > 32 * 1024)
       MDI_CUDA(cudaFuncSetAttribute(ransac_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     200 * 1024), "mdi_ransac attr");
-      attr_set = 200 * 1024;
-    }
     mdi::prof_mark("ransac_kernel", st);
     ransac_kernel<true><<<n_views, kRansacThreads, smem, st>>>(
         views, d, z, n_valid, status, sample_idx, *cfg, pts, scale_shift, inliers, n_iter, n_inliers);

@@ -1312,23 +1312,22 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     const bool um = pop & MDI_KEEP_PRED_MASK, se = pop & MDI_KEEP_SENTINEL;
     // 0: register-staged kernel (default), 1: TMA-staged kernel (MDI_STATS_MAIN=tma; bit-identical
     // results, measured slower so far: 0.42 vs 0.33 ms on C2)
-    static int main_variant = -1;
-    if (main_variant < 0) {
+    // process-wide choices read once from the environment (thread-safe static initialisation); the
+    // per-DEVICE function attributes below are set before every launch that needs them
+    static const int main_variant = [] {
       const char* e = getenv("MDI_STATS_MAIN");
-      main_variant = (e && strcmp(e, "tma") == 0) ? 1 : 0;
-      if (main_variant == 1) {
-        cudaError_t a0 = cudaFuncSetAttribute(stats_main_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
-        cudaError_t a1 = cudaFuncSetAttribute(stats_main_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
-        cudaError_t a2 = cudaFuncSetAttribute(stats_main_tma_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
-        cudaError_t a3 = cudaFuncSetAttribute(stats_main_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes);
-        if (a0 != cudaSuccess || a1 != cudaSuccess || a2 != cudaSuccess || a3 != cudaSuccess) { cudaGetLastError(); main_variant = 0; }
-      }
-    }
-    static int prefetch_ahead = -1;  // tiles of L2 prefetch in the depth-domain loop (MDI_STATS_PREFETCH, 0 = off)
-    if (prefetch_ahead < 0) {
+      return (e && strcmp(e, "tma") == 0) ? 1 : 0;
+    }();
+    static const int prefetch_ahead = [] {  // tiles of L2 prefetch in the depth-domain loop (MDI_STATS_PREFETCH, 0 = off)
       const char* e = getenv("MDI_STATS_PREFETCH");
-      prefetch_ahead = e ? atoi(e) : 2;
-      if (prefetch_ahead < 0 || prefetch_ahead > 16) prefetch_ahead = 2;
+      const int p = e ? atoi(e) : 2;
+      return (p < 0 || p > 16) ? 2 : p;
+    }();
+    if (main_variant == 1) {
+      MDI_CUDA(cudaFuncSetAttribute(stats_main_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes), "mdi_depth_range attr");
+      MDI_CUDA(cudaFuncSetAttribute(stats_main_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes), "mdi_depth_range attr");
+      MDI_CUDA(cudaFuncSetAttribute(stats_main_tma_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes), "mdi_depth_range attr");
+      MDI_CUDA(cudaFuncSetAttribute(stats_main_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes), "mdi_depth_range attr");
     }
     mdi::prof_mark("stats_main_kernel", st);
     if (main_variant == 1) {
@@ -1343,12 +1342,9 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     mdi::prof_mark("stats_finish_kernel", st);
     stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
   } else {
-    static bool attr_done = false;
-    if (!attr_done) {
-      MDI_CUDA(cudaFuncSetAttribute(stats_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    kTargets * kBins * 4), "mdi_depth_range attr");
-      attr_done = true;
-    }
+    // per device (context) attribute: set on every call (microseconds), never cached process-wide
+    MDI_CUDA(cudaFuncSetAttribute(stats_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  kTargets * kBins * 4), "mdi_depth_range attr");
     mdi::prof_mark("stats_pass_kernel", st);
     stats_pass_kernel<0><<<grid, kStatsThreads, kBins * 4, st>>>(views, scale_shift, status, pop, ws);
     mdi::prof_mark("stats_select_kernel", st);

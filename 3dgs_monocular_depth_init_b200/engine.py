@@ -198,6 +198,7 @@ class Engine:
         L.check(self.lib.mdi_check_device(idx), "mdi_check_device")
         self._ws: dict[str, torch.Tensor] = {}
         self._pin: dict[str, torch.Tensor] = {}
+        self._pin_ev: dict[str, torch.cuda.Event] = {}   # last device read of each pinned staging buffer
         self._plan = None   # (key, descriptor table + its uploaded image) of the previous run
         self.launches = 0   # kernels launched through this engine (bench `gpu_launches`)
         self.profile = False
@@ -306,10 +307,14 @@ class Engine:
 
     def _upload(self, name: str, parts, owned: bool = False) -> torch.Tensor:
         """One H2D copy of the concatenated byte images of `parts` (numpy arrays) through a
-        persistent pinned staging buffer.  Safe to reuse across calls: every run() ends with a
-        stream synchronisation (the read-back of the point count)."""
+        persistent pinned staging buffer.  The buffer is rewritten only after the copy that last read
+        it has completed (partial pipelines -- stop_after="project" / "fit" -- return without a
+        stream synchronisation)."""
         sizes = [int(a.nbytes) for a in parts]
         n = sum(sizes)
+        ev = self._pin_ev.pop(name, None)
+        if ev is not None:
+            ev.synchronize()
         pin = self._pin.get(name)
         if pin is None or pin.numel() < n:
             pin = self._pin[name] = torch.empty(max(int(n * 1.25), 256), dtype=torch.uint8, pin_memory=True)
@@ -323,9 +328,12 @@ class Engine:
             # engine, and a memcpy would wait behind all of them -- the SMs fetch the table instead
             dev = torch.empty(n, dtype=torch.uint8, device=self.device)
             L.check(self.lib.mdi_upload_table(dev.data_ptr(), pin.data_ptr(), n, _stream()), "mdi_upload_table")
-            return dev
-        dev = torch.empty(n, dtype=torch.uint8, device=self.device) if owned else self._buf(name, n, torch.uint8)
-        dev.copy_(pin[:n], non_blocking=True)
+        else:
+            dev = torch.empty(n, dtype=torch.uint8, device=self.device) if owned else self._buf(name, n, torch.uint8)
+            dev.copy_(pin[:n], non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
+        self._pin_ev[name] = done
         return dev
 
     # ---- the pipeline -------------------------------------------------------------------------
@@ -339,7 +347,8 @@ class Engine:
         # The same resident views again (every step of a training-set sweep, every bench step): the
         # descriptor table, K and cam2world already sit on the device from the previous call, and
         # rebuilding + re-uploading them is ~0.1 ms of host time in front of the first launch.
-        key = self._plan_key(vin, opt, V, kn, c2wn) if V else None
+        # (a deferred-emit run owns its table until Engine.emit_deferred: it neither takes nor leaves a plan)
+        key = self._plan_key(vin, opt, V, kn, c2wn) if V and not opt.defer_emit else None
         plan = self._plan[1] if key is not None and self._plan is not None and self._plan[0] == key else None
         if plan is not None:
             desc, px_begin, tile_begin, sfm_begin, blob, pinhole = plan

@@ -26,6 +26,9 @@ def knn_search(x: torch.Tensor, k: int, exclude_self: bool):
         raise ValueError("knn: expected points of shape (N, 3)")
     pts = x.to(torch.float32).contiguous()
     n = pts.shape[0]
+    if n and not bool(torch.isfinite(pts).all()):
+        # sklearn's check_array (NearestNeighbors / LocalOutlierFactor .fit) rejects such input
+        raise ValueError("Input X contains NaN or infinity.")
     with torch.cuda.device(pts.device):
         ws = torch.empty(int(lib.mdi_knn_workspace_bytes(n)), dtype=torch.uint8, device=pts.device)
         idx = torch.empty((n, k), dtype=torch.int32, device=pts.device)
@@ -54,12 +57,12 @@ def local_outlier_factor(x: torch.Tensor, n_neighbors: int = 40):
     lib = L.load()
     n = x.shape[0]
     k = n_neighbors
+    if n < 2:
+        raise ValueError("local_outlier_factor needs at least 2 points")
     if k >= n:  # sklearn _lof.py: clamps with this warning
         warnings.warn(f"n_neighbors ({k}) is greater than the total number of samples ({n}). "
                       f"n_neighbors will be set to (n_samples - 1) for estimation.")
         k = max(1, n - 1)
-    if n < 2:
-        raise ValueError("local_outlier_factor needs at least 2 points")
     pts = x.to(torch.float32).contiguous()
     idx, dist, kdist = knn_search(pts, k, exclude_self=True)
     with torch.cuda.device(pts.device):

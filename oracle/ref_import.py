@@ -34,6 +34,12 @@ def load():
         raise RuntimeError(f"reference not present at {REFERENCE_ROOT}")
     import numpy, scipy, sklearn.neighbors, torch, tyro  # noqa: F401,E401  real deps first
 
+    # The repo root holds an ALIAS package of the same name (gs_init_compare/ -> the B200 implementation).
+    # If anything imported it in this process, drop it and its finder: the oracle must never be checked
+    # against the product by accident.
+    for k in [k for k in sys.modules if k == "gs_init_compare" or k.startswith("gs_init_compare.")]:
+        del sys.modules[k]
+    sys.meta_path[:] = [f for f in sys.meta_path if type(f).__name__ != "_AliasFinder"]
     sys.path.insert(0, REFERENCE_ROOT)
     orig = dataclasses.dataclass
 
@@ -84,6 +90,10 @@ def load():
         from gs_init_compare.types import InputImage
     finally:
         dataclasses.dataclass = orig
+    import gs_init_compare
+    where = os.path.realpath(os.path.dirname(gs_init_compare.__file__))
+    assert where.startswith(os.path.realpath(REFERENCE_ROOT)), f"gs_init_compare resolved to {where}, not the reference"
+    assert "3dgs_monocular_depth_init_b200" not in points_from_depth.get_pts_from_depth.__module__
     ns = types.SimpleNamespace(
         Config=Config, lstsqrs=lstsqrs, ransacs=ransacs,
         DepthAlignmentStrategyEnum=DepthAlignmentStrategyEnum,

@@ -156,12 +156,18 @@ def test_cache_written_by_the_reference_loads(tmp_path):
     PredictedDepth.__module__ = ref_mod
     PredictedDepth.__qualname__ = "PredictedDepth"
     fake.PredictedDepth = PredictedDepth
+    before = set(sys.modules)
     sys.modules[ref_mod] = fake
     try:
         f = tmp_path / "x.pth"
         torch.save(PredictedDepth(torch.arange(6.0).view(2, 3), torch.ones(2, 3, dtype=torch.bool)), f)
     finally:
-        del sys.modules[ref_mod]
+        # pickle imports the parent packages of the class's module: leave no `gs_init_compare*` entry
+        # behind (this process may import the real reference under that name, oracle/ref_import.py)
+        for k in set(sys.modules) - before:
+            if k == "gs_init_compare" or k.startswith("gs_init_compare."):
+                del sys.modules[k]
+        sys.meta_path[:] = [m for m in sys.meta_path if type(m).__name__ != "_AliasFinder"]
     got = dc.load_cached_depth(f, "cpu")
     assert isinstance(got, dpi.PredictedDepth) and got.depth.tolist() == [[0, 1, 2], [3, 4, 5]] and got.normal is None
 
