@@ -50,26 +50,47 @@ def allgather_points(xyz: torch.Tensor, rgb: torch.Tensor, group=None):
 class CloudExchange:
     """The exchange step of SURVEY 8e fused into the emit kernel: every rank owns a symmetric
     (peer-mapped over NVLink / NVSwitch) pair of output clouds, and each rank's emit kernel writes
-    its points into ALL of them at the rank's global row offset (mdi_emit_points_multi).  After a
-    barrier every rank holds the whole scene in view order: no NCCL data collective, no padding,
-    no compaction pass.  Only the per-rank counts travel through NCCL (one 8-byte all-gather).
+    its points into ALL of them at the rank's global row offset (mdi_emit_points_exchange, 16-byte
+    stores; one multimem store per 16 bytes through the NVSwitch multicast address when the fabric
+    offers one).  After a device barrier every rank holds the whole scene in view order: no NCCL data
+    collective, no padding, no compaction pass.
 
-    The returned clouds alias the exchange buffers: they are valid until the next `begin` on any
-    rank (the count exchange of the next scene doubles as the "everybody is done reading" barrier
-    for work enqueued on the current stream).  Construction and growth are collective.
+    The per-rank row counts travel on the device too (mdi_exchange_counts: each rank stores its count
+    into every rank's peer-mapped header and spins until all counts of the step have arrived), so the
+    emit kernel is launched without a host synchronisation or an NCCL call in front of it; the host
+    reads the counts back once, after everything has been queued.
+
+    The returned clouds alias the exchange buffers: they are valid until the next step on any rank
+    (the count exchange of the next step doubles as the "everybody is done reading" barrier for work
+    enqueued on the current stream).  Construction and growth are collective.
     Raises if torch's symmetric memory is unavailable; callers then use `allgather_points`."""
+
+    MAX_RANKS = 16   # MDI_MAX_EMIT_DST
 
     def __init__(self, device, group=None, capacity_rows: int = 1 << 20):
         import torch.distributed._symmetric_memory as symm_mem
-        self._symm = symm_mem
+        from . import _lib as L
+        self._symm, self._L = symm_mem, L
         self.group = group if group is not None else dist.group.WORLD
         self.device = torch.device(device)
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
-        if self.world > 16:
+        if self.world > self.MAX_RANKS:
             raise ValueError("CloudExchange: at most 16 ranks (MDI_MAX_EMIT_DST)")
         self.capacity = 0
         self._alloc(int(capacity_rows))
+        # count-exchange headers: 2 slot sets x world int64 per rank, zero before anybody publishes
+        self._hdr = symm_mem.empty(2 * self.MAX_RANKS, dtype=torch.int64, device=self.device)
+        self._hdr.zero_()
+        self._hh = symm_mem.rendezvous(self._hdr, group=self.group)
+        self.hdr_ptrs = [int(p) for p in self._hh.buffer_ptrs]
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)   # every header is zero before the first publish
+        self.epoch = 0
+        self.record = torch.zeros(3 + self.MAX_RANKS, dtype=torch.int64, device=self.device)
+        self._record_pin = torch.zeros(3 + self.MAX_RANKS + 2, dtype=torch.int64, pin_memory=True)
+        self._zero2 = torch.zeros(2, dtype=torch.int64, device=self.device)
+        self.counts, self.total = [0] * self.world, 0
 
     def _alloc(self, rows: int) -> None:
         self.xyz = self._symm.empty(rows * 3, dtype=torch.float32, device=self.device)
@@ -81,29 +102,52 @@ class CloudExchange:
         # NVSwitch multicast addresses of the two clouds (0 when the fabric has no NVLS)
         self.xyz_mc = int(getattr(self._hx, "multicast_ptr", 0) or 0)
         self.rgb_mc = int(getattr(self._hr, "multicast_ptr", 0) or 0)
-        # opt-in: with scalar multimem stores the multicast emit measured slower than the unicast one
-        # on 2 GPUs (0.36 vs 0.18 ms); it needs 16-byte vector stores to pay off
-        self.use_multicast = bool(self.xyz_mc and self.rgb_mc) and os.environ.get("MDI_MULTICAST") == "1"
+        # MDI_MULTICAST=1 / 0 forces the choice; default: unicast peer stores
+        env = os.environ.get("MDI_MULTICAST")
+        self.use_multicast = bool(self.xyz_mc and self.rgb_mc) and env == "1"
         self.capacity = rows
 
-    def begin(self, n_local: int):
-        """Collective.  -> (row_offset of this rank, total rows, counts list)."""
-        n = torch.tensor([int(n_local)], dtype=torch.int64, device=self.device)
-        counts = torch.empty(self.world, dtype=torch.int64, device=self.device)
-        dist.all_gather_into_tensor(counts, n, group=self.group)
-        cnt = [int(c) for c in counts.cpu()]
-        total = sum(cnt)
-        if total > self.capacity:  # same decision on every rank
-            rows = self.capacity
-            while rows < total:
-                rows *= 2
-            self._alloc(rows)
-        self.counts = cnt
-        self.total = total
-        return sum(cnt[: self.rank]), total, cnt
+    # ---- device-side protocol --------------------------------------------------------------------
+    def publish_counts(self, local_ptr, stream: int) -> None:
+        """Collective, stream ordered.  local_ptr: device int64 [2] = (rows of this rank, retry flag),
+        None for a rank without views.  Fills self.record (see mdi_exchange_counts)."""
+        import ctypes as C
+        L = self._L
+        self.epoch += 1
+        hp = (C.c_void_p * self.world)(*self.hdr_ptrs)
+        L.check(L.load().mdi_exchange_counts(hp, self.rank, self.world, self.epoch,
+                                             local_ptr if local_ptr is not None else self._zero2.data_ptr(),
+                                             self.record.data_ptr(), stream), "mdi_exchange_counts")
 
-    def finish(self):
-        """Collective, stream ordered: returns once every rank's emit kernel has completed, i.e.
-        this rank's clouds are whole.  -> (xyz [total,3], rgb [total,3]) views of the buffers."""
+    def barrier(self) -> None:
+        """Collective, stream ordered: returns (on the stream) once every rank's emit kernel of this
+        step has completed, i.e. this rank's clouds are whole."""
         self._hx.barrier()
+
+    def read_record(self, extra: torch.Tensor = None):
+        """One pinned read-back + stream synchronisation: -> (row_offset, total rows of all ranks,
+        any-rank retry flag, counts list, extra values).  `extra`: up to 2 more device int64 to fetch."""
+        n = 3 + self.world
+        self._record_pin[:n].copy_(self.record[:n], non_blocking=True)
+        if extra is not None:
+            self._record_pin[n:n + extra.numel()].copy_(extra, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        vals = self._record_pin.tolist()
+        if vals[1] < 0:
+            raise self._L.MdiError("CloudExchange: a peer rank did not publish its row count (mdi_exchange_counts timed out)")
+        self.counts = [int(c) for c in vals[3:n]]
+        self.total = int(vals[1])
+        return int(vals[0]), self.total, bool(vals[2]), self.counts, vals[n:n + (extra.numel() if extra is not None else 0)]
+
+    def grow(self, rows_needed: int) -> None:
+        """Collective (every rank sees the same total): reallocate clouds that hold rows_needed rows."""
+        rows = max(self.capacity, 1)
+        while rows < rows_needed:
+            rows *= 2
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)   # nobody still writes into the old clouds
+        self._alloc(rows)
+
+    def clouds(self):
+        """-> (xyz [total,3], rgb [total,3]) views of the exchange buffers."""
         return self.xyz[: 3 * self.total].view(-1, 3), self.rgb[: 3 * self.total].view(-1, 3)

@@ -149,6 +149,7 @@ KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_upload_table": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_capped": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
+    "mdi_emit_points_exchange": 1, "mdi_exchange_counts": 1,
     "mdi_min_extents": 1,
 }
 
@@ -363,11 +364,7 @@ class Engine:
         if V == 0:
             if opt.exchange is not None and opt.stop_after is None and (opt.want_xyz or opt.want_rgb):
                 # a rank without views still takes part in the collective exchange
-                row_offset, _, counts = opt.exchange.begin(0)
-                res.total = 0
-                res.xyz, res.rgb = opt.exchange.finish()
-                res.extras["rank_counts"] = counts
-                res.extras["row_offset"] = row_offset
+                self._exchange_rounds(opt.exchange, res, None, None, None)
             return res
         if plan is None:
             # a1: cameras.  One upload: [descriptors][K][cam2world][inv(K) unless pinhole]
@@ -520,8 +517,8 @@ class Engine:
         may_speculate = bool(opt.speculative_emit and opt.exchange is None and opt.stop_after != "mask"
                              and not opt.defer_emit and (want_xyz or want_rgb) and hint > 0)
 
-        def mask_stage(stats_mode: int, speculate: bool = False):
-            """a7 statistics -> a5-a10 keep mask -> compaction offsets; returns (total, retry, spec)."""
+        def launch_mask(stats_mode: int):
+            """a7 statistics -> a5-a10 keep mask -> compaction offsets (launches only)."""
             if use_stats:
                 L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
                                             (flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)) | stats_mode,
@@ -542,6 +539,10 @@ class Engine:
             L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
                                        res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
                                        meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
+
+        def mask_stage(stats_mode: int, speculate: bool = False):
+            """launch_mask + the read-back of (total, retry); returns (total, retry, spec)."""
+            launch_mask(stats_mode)
             if not hasattr(self, "_rb_stream"):
                 self._rb_stream = torch.cuda.Stream(self.device)
                 self._tail_pin = torch.empty(2, dtype=torch.int64, pin_memory=True)
@@ -572,7 +573,35 @@ class Engine:
             return int(self._tail_pin[0]), bool(self._tail_pin[1]), (cap, xyz, rgb)
 
         # views under 64K pixels give the one-pass path too small a sample to bracket: exact select
-        res.total, retry, spec = mask_stage(L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0, may_speculate)
+        first_mode = L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0
+        if (opt.exchange is not None and opt.stop_after is None and not opt.defer_emit
+                and (opt.want_xyz or opt.want_rgb)):
+            # multi-GPU: counts travel on the device, the emit kernel writes this rank's points into every
+            # rank's cloud; the host synchronises once, after everything has been queued
+            def launch_emit():
+                ex = opt.exchange
+                xp = rp = None
+                n_dst = 0 if ex.use_multicast else ex.world
+                if n_dst:
+                    xp = (C.c_void_p * n_dst)(*ex.xyz_ptrs) if want_xyz else None
+                    rp = (C.c_void_p * n_dst)(*ex.rgb_ptrs) if want_rgb else None
+                L.check(lib.mdi_emit_points_exchange(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
+                                                     res.view_offsets.data_ptr(), int(vin.image_kind), n_dst, xp, rp,
+                                                     ex.xyz_mc if (not n_dst and want_xyz) else None,
+                                                     ex.rgb_mc if (not n_dst and want_rgb) else None,
+                                                     ex.record.data_ptr(), int(ex.capacity), st),
+                        "mdi_emit_points_exchange")
+
+            def remask(mode):
+                if mode == L.STATS_RETRY_FLAGGED:
+                    meta[2 * V + 1] = 0
+                    res.extras["stats_retry"] = True
+                launch_mask(mode)
+
+            self._exchange_rounds(opt.exchange, res, lambda: remask(first_mode), lambda: remask(L.STATS_RETRY_FLAGGED),
+                                  launch_emit, meta[2 * V:])
+            return res
+        res.total, retry, spec = mask_stage(first_mode, may_speculate)
         if retry:
             # a view's one-pass quantile brackets could not be certified (e.g. a constant depth
             # map): exact three-pass select for the flagged views, then mask + scan again
@@ -588,26 +617,6 @@ class Engine:
             res.extras["emit_state"] = dict(blob=blob, n_views=V, total_tiles=total_tiles, scale_shift=res.scale_shift,
                                             bits=bits, tile_offsets=tile_offsets, view_offsets=res.view_offsets,
                                             image_kind=int(vin.image_kind), has_image=vin.image is not None, total=N)
-            return res
-        if opt.exchange is not None:
-            # multi-GPU: the emit kernel writes this rank's points into every rank's cloud
-            ex = opt.exchange
-            row_offset, total_all, counts = ex.begin(N)
-            if N and ex.use_multicast:
-                L.check(lib.mdi_emit_points_multicast(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
-                                                      res.view_offsets.data_ptr(), int(vin.image_kind), ex.xyz_mc,
-                                                      ex.rgb_mc if vin.image is not None else None, int(row_offset),
-                                                      st), "mdi_emit_points_multicast")
-            elif N:
-                n_dst = ex.world
-                xp = (C.c_void_p * n_dst)(*ex.xyz_ptrs)
-                rp = (C.c_void_p * n_dst)(*ex.rgb_ptrs) if vin.image is not None else None
-                L.check(lib.mdi_emit_points_multi(vp, V, total_tiles, ssp, bits.data_ptr(), tile_offsets.data_ptr(),
-                                                  res.view_offsets.data_ptr(), int(vin.image_kind), n_dst, xp, rp,
-                                                  int(row_offset), st), "mdi_emit_points_multi")
-            res.xyz, res.rgb = ex.finish()
-            res.extras["rank_counts"] = counts
-            res.extras["row_offset"] = row_offset
             return res
         self._emit_hint = N
         if spec is not None and N <= spec[0]:
@@ -626,6 +635,39 @@ class Engine:
                                         res.view_offsets.data_ptr(), int(vin.image_kind), L.ptr(res.xyz), L.ptr(res.rgb), st),
                     "mdi_emit_points")
         return res
+
+    def _exchange_rounds(self, ex, res: RunResult, first_mask, retry_mask, launch_emit, local=None):
+        """The collective part of a multi-GPU step.  Every rank runs the same sequence of rounds:
+        [mask stage] -> publish counts -> emit into all clouds -> barrier -> one read-back.  A rank
+        whose one-pass statistics need the exact retry raises its flag in the count exchange, and
+        then EVERY rank goes through a second round (ranks without flagged views just emit again),
+        so the collective calls stay matched; clouds that turn out too small are grown collectively
+        and the emit repeated (the kernel writes nothing when the scene exceeds the capacity)."""
+        st = _stream()
+        if first_mask is not None:
+            first_mask()
+        while True:
+            ex.publish_counts(None if local is None else local.data_ptr(), st)
+            if launch_emit is not None:
+                launch_emit()
+            ex.barrier()
+            row_offset, total_all, retry_any, counts, mine = ex.read_record(local)
+            if retry_any:
+                # ranks whose own flag is clear keep their masks and simply emit again next round
+                if local is not None and retry_mask is not None and mine[1]:
+                    retry_mask()
+                continue
+            if total_all > ex.capacity:
+                ex.grow(total_all)
+                if launch_emit is not None:
+                    launch_emit()
+                ex.barrier()
+                torch.cuda.current_stream(self.device).synchronize()
+            break
+        res.total = counts[ex.rank]
+        res.xyz, res.rgb = ex.clouds()
+        res.extras["rank_counts"] = counts
+        res.extras["row_offset"] = row_offset
 
     def emit_deferred(self, states, want_xyz: bool = True, want_rgb: bool = True):
         """a10/a11 of runs made with RunOptions.defer_emit, in order, into ONE cloud: run i's points go

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define MDI_ABI_VERSION 2
+#define MDI_ABI_VERSION 3
 
 /* error codes */
 #define MDI_OK 0
@@ -309,6 +309,32 @@ int mdi_emit_points_multicast(const MdiView* views, int n_views, int64_t total_t
                               const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
                               const int64_t* view_offsets, int image_kind, float* xyz_mc, float* rgb_mc,
                               int64_t row_offset, void* stream);
+
+/*
+ * Count exchange of a multi-GPU step on the device (no NCCL call, no host synchronisation in front
+ * of the emit kernel).  hdr_ptrs: HOST array of `world` device pointers, hdr_ptrs[q] = rank q's
+ * peer-mapped header of 2 * world int64 slots (zero-filled once, before the first call, on every
+ * rank).  local: device int64 [2] = (rows of this rank, retry flag) -- the `total` / retry_flag pair
+ * written by mdi_scan_tiles / mdi_depth_range.  epoch: 1, 2, 3, ... -- the same on every rank for the
+ * same step (the call is collective: every rank launches it once per step, in the same order).
+ * out: device int64 [3 + world] = (first row of this rank in the scene cloud, rows of all ranks,
+ * 1 if any rank's retry flag is set, rows of rank 0, 1, ...).
+ */
+int mdi_exchange_counts(int64_t* const* hdr_ptrs, int rank, int world, uint32_t epoch,
+                        const int64_t* local, int64_t* out, void* stream);
+
+/*
+ * mdi_emit_points_multi / _multicast with the row offset taken from the record written by
+ * mdi_exchange_counts (device): rows go to exchange_record[0] + local slot.  Nothing is written when
+ * exchange_record[1] (rows of all ranks) exceeds capacity_rows; the caller, who reads the record
+ * after the launch, then grows the clouds and launches again.  n_dst == 0 selects the multicast
+ * addresses.  Destination base pointers must be 16-byte aligned (records leave as 128-bit stores).
+ */
+int mdi_emit_points_exchange(const MdiView* views, int n_views, int64_t total_tiles,
+                             const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
+                             const int64_t* view_offsets, int image_kind, int n_dst,
+                             float* const* xyz_dst, float* const* rgb_dst, float* xyz_mc, float* rgb_mc,
+                             const int64_t* exchange_record, int64_t capacity_rows, void* stream);
 
 /*
  * a13: minimal Gaussian extent per point over all cameras that see it (else -1).
