@@ -151,3 +151,34 @@ class CloudExchange:
     def clouds(self):
         """-> (xyz [total,3], rgb [total,3]) views of the exchange buffers."""
         return self.xyz[: 3 * self.total].view(-1, 3), self.rgb[: 3 * self.total].view(-1, 3)
+
+
+def bind_process_to_gpu_node(device_index: int) -> dict:
+    """Pins this process (and with it the first-touch placement of the pinned staging buffers it
+    allocates afterwards) to the CPUs of the NUMA node its GPU hangs off.  One process per GPU: without
+    this every rank's host buffers land on the node the launcher happened to start on, and the
+    host->device copies of the far GPUs cross the socket interconnect.  Reads sysfs only; returns what
+    it found ({"numa_node": n | None, "cpus": k, "bound": bool}) and does nothing when the topology is
+    not exposed (containers often report node -1)."""
+    info = {"numa_node": None, "cpus": 0, "bound": False}
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return info
+        info["numa_node"] = node
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & set(os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info.update(cpus=len(allowed), bound=True)
+    except (OSError, ValueError, AttributeError):
+        pass
+    return info

@@ -61,7 +61,9 @@ class _PinnedPool:
             ev.synchronize()
         t = self._buf.get(name)
         if t is None or t.dtype != dtype or t.numel() < n:
-            t = self._buf[name] = torch.empty(max(n, 1), dtype=dtype, pin_memory=True)
+            # 25 % headroom: result sizes vary from call to call (RANSAC seeds), and every growth is a
+            # cudaHostAlloc of tens of milliseconds
+            t = self._buf[name] = torch.empty(max(n + (n >> 2), 1), dtype=dtype, pin_memory=True)
         return t[:n].view(*shape)
 
     def mark(self, name: str) -> None:

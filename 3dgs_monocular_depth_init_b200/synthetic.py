@@ -53,12 +53,17 @@ def gt_depth(H: int, W: int, device, phase: float = 0.0) -> torch.Tensor:
 
 def make_scene(n_views: int, H: int, W: int, n_sfm: int = 5000, seed: int = 20261104,
                device: str = "cpu", low_conf_every: int = 50, image_u8: bool = True,
-               outlier_frac: Optional[float] = None) -> SyntheticScene:
+               outlier_frac: Optional[float] = None, keep_views: Optional[range] = None) -> SyntheticScene:
+    """`keep_views` (a contiguous range): generate the scene of n_views views -- SfM table, foreign
+    indices and all -- but materialise depth / mask / image, K, cam2world and names of those views only
+    (a rank's block of a sharded scene; identical to slicing the full scene)."""
     dev = torch.device(device)
     rng = np.random.default_rng(seed)
-    depth = torch.empty((n_views, H, W), dtype=torch.float32, device=dev)
-    mask = torch.ones((n_views, H, W), dtype=torch.bool, device=dev)
-    image = torch.empty((n_views, H, W, 3), dtype=torch.uint8, device=dev)
+    kept = range(n_views) if keep_views is None else keep_views
+    k0, n_keep = (kept[0] if len(kept) else 0), len(kept)
+    depth = torch.empty((n_keep, H, W), dtype=torch.float32, device=dev)
+    mask = torch.ones((n_keep, H, W), dtype=torch.bool, device=dev)
+    image = torch.empty((n_keep, H, W, 3), dtype=torch.uint8, device=dev)
     Ks, c2ws, names, true_h = [], [], [], []
     pts_all, idx_all = [], []
     n_pts = 0
@@ -72,17 +77,21 @@ def make_scene(n_views: int, H: int, W: int, n_sfm: int = 5000, seed: int = 2026
         c2w = _look_at(eye, np.array([0.0, 0.0, 0.0]) + rng.uniform(-0.2, 0.2, 3))
         G = gt_depth(H, W, dev, phase=0.37 * v)
         s_true, t_true = rng.uniform(0.5, 3.0), rng.uniform(-0.3, 0.3)
-        D = (G - t_true) / s_true * (1 + 0.005 * torch.randn((H, W), generator=g, device=dev))
-        # 0.1 % of pixels: zero or negative-after-alignment depth
-        bad = torch.rand((H, W), generator=g, device=dev) < 0.001
-        D = torch.where(bad, -D * 0.5, D)
-        depth[v] = D
+        here = v in kept
+        if here:
+            D = (G - t_true) / s_true * (1 + 0.005 * torch.randn((H, W), generator=g, device=dev))
+            # 0.1 % of pixels: zero or negative-after-alignment depth
+            bad = torch.rand((H, W), generator=g, device=dev) < 0.001
+            D = torch.where(bad, -D * 0.5, D)
+            depth[v - k0] = D
         if v % 2 == 1:  # MoGe-like mask: one invalid rectangle of ~5 % area
             rh, rw = int(H * 0.25), int(W * 0.2)
             r0, c0 = int(rng.integers(0, H - rh)), int(rng.integers(0, W - rw))
-            mask[v, r0:r0 + rh, c0:c0 + rw] = False
-        image[v] = torch.randint(0, 256, (H, W, 3), generator=g, device=dev, dtype=torch.uint8)
-        image[v, 0, 0, 0] = 255  # the reference asserts image.max() > 1
+            if here:
+                mask[v - k0, r0:r0 + rh, c0:c0 + rw] = False
+        if here:
+            image[v - k0] = torch.randint(0, 256, (H, W, 3), generator=g, device=dev, dtype=torch.uint8)
+            image[v - k0, 0, 0, 0] = 255  # the reference asserts image.max() > 1
         # SfM points: half uniform, half in 8 blobs
         n_own = n_sfm if v % max(low_conf_every, 1) != max(low_conf_every, 1) - 1 else n_sfm // 8
         n_uni = n_own // 2
@@ -126,12 +135,13 @@ def make_scene(n_views: int, H: int, W: int, n_sfm: int = 5000, seed: int = 2026
         idx = np.concatenate([own, foreign])
         point_indices[names[v]] = idx[rng.permutation(len(idx))].astype(np.int64)
     points_rgb = rng.integers(0, 256, (n_pts, 3)).astype(np.uint8)
+    sel = slice(k0, k0 + n_keep)
     return SyntheticScene(
         depth=depth, mask=mask, image=image,
-        K=torch.from_numpy(np.stack(Ks)) if Ks else torch.zeros((0, 3, 3)),
-        c2w=torch.from_numpy(np.stack(c2ws)) if c2ws else torch.zeros((0, 4, 4)),
-        points=points, points_rgb=points_rgb, point_indices=point_indices, names=names,
-        true_scale_shift=np.array(true_h, dtype=np.float64).reshape(-1, 2),
+        K=torch.from_numpy(np.stack(Ks[sel])) if n_keep else torch.zeros((0, 3, 3)),
+        c2w=torch.from_numpy(np.stack(c2ws[sel])) if n_keep else torch.zeros((0, 4, 4)),
+        points=points, points_rgb=points_rgb, point_indices=point_indices, names=names[sel],
+        true_scale_shift=np.array(true_h[sel], dtype=np.float64).reshape(-1, 2),
     )
 
 

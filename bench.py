@@ -3,12 +3,15 @@
 
 A "step" is one pass of the hot path over one batch of synthetic views (BASELINE.json config 2:
 Mip-NeRF-360-shaped, 200 views of 1297x840, 5000 SfM points per view + 20 % foreign, RANSAC
-alignment + adaptive subsampling + default SfM-density patch mask).  N > 1 is weak scaling:
-every rank owns its own 200 views (no data-path collective) and the per-view point clouds are
-concatenated in view order by one NCCL all-gather per step.
+alignment + adaptive subsampling + default SfM-density patch mask).  N > 1 is weak scaling by
+default: every rank owns its own 200 views (no data-path collective) and the exchange step -- every
+rank ends up with the whole scene cloud in view order -- is fused into the emit kernel over
+NVLink.  `--scaling strong` shards the workload's views over the N ranks instead (BASELINE configs
+3 / 4: `--workload c3_... / c4_... --scaling strong`).
 
   python bench.py [--gpus N --steps K --warmup W]            our arm (CUDA kernels)
   python bench.py --impl reference [...]                     the reference's CPU path (oracle port)
+  python bench.py --postprocess lof|merge [...]              C5 post-processing leg (a12-a14)
 """
 from __future__ import annotations
 
@@ -32,6 +35,7 @@ WORKLOADS = {
     "c1_single_1297x840_lstsq_stride10": (1, 840, 1297, 5000, "lstsqrs", 10),
     "c3_tanks_300x1920x1080_ransac_adaptive": (300, 1080, 1920, 5000, "ransac", "adaptive"),
     "c4_4k_500x3840x2160_ransac_adaptive": (500, 2160, 3840, 5000, "ransac", "adaptive"),
+    "c5_large_2000x1600x1200_ransac_adaptive": (2000, 1200, 1600, 5000, "ransac", "adaptive"),
 }
 DEFAULT_WORKLOAD = "c2_mipnerf360_200x1297x840_ransac_adaptive"
 
@@ -148,6 +152,17 @@ def algorithmic_bytes(kernel: str, HW: int, V: int, n_kept: int, n_sfm_slots: in
     }.get(kernel, 0.0)
 
 
+def workload_config(workload: str, scaling: str, world: int) -> dict:
+    """The `config` object of the JSON line: identical in both arms for the same command line."""
+    V, H, W, n_sfm, aligner, subsample = WORKLOADS[workload]
+    per_gpu = V if scaling == "weak" else -(-V // world)
+    input_mb = per_gpu * H * W * (4 + 1 + 3) / 1e6
+    return {"workload": workload, "views_per_gpu": per_gpu, "views_total": per_gpu * world if scaling == "weak" else V,
+            "H": H, "W": W, "sfm_points_per_view": n_sfm, "aligner": aligner, "subsample": subsample,
+            "patch_mask": True, "scaling": scaling,
+            "l2": f"inputs {input_mb:.0f} MB per GPU and step > 126 MB L2, no flush needed"}
+
+
 def cpu_reference_run(workload: str, n_views_sample: int, seed: int = 20261104):
     """The reference's CPU path (oracle port: same torch ops, same python loops, including the
     per-patch loop of num_sfm_points_mask) on a bounded sample of the workload's views."""
@@ -184,10 +199,10 @@ def run_reference_arm(args):
     print(json.dumps({
         "impl": "reference", "metric": "init views/sec (align+subsample+unproject)", "value": vps, "unit": "views/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        # same config as our arm; the CPU run covers `sample_views_per_step` of the views per step
-        "config": {"workload": args.workload, "views_per_gpu": V, "H": H, "W": W, "sfm_points_per_view": n_sfm,
-                   "aligner": aligner, "subsample": subsample, "patch_mask": True, "sample_views_per_step": nv},
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        # same config as our arm; the CPU run covers `run.sample_views_per_step` of the views per step
+        "config": workload_config(args.workload, args.scaling, int(os.environ.get("WORLD_SIZE", "1"))),
+        "run": {"sample_views_per_step": nv},
         "mpts_per_s": kept_pts / t / 1e6,
         "cpu_baseline": {"value": vps, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": vps, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -204,23 +219,39 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    dmod = mod("distributed")
+    # one process per GPU: run on (and allocate the pinned staging buffers from) the GPU's own NUMA node
+    numa = dmod.bind_process_to_gpu_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     L = mod("_lib")
     mdi = mod("monocular_depth_init")
-    eng = mod("engine").get_engine(dev)
-    dmod = mod("distributed")
+    emod = mod("engine")
+    eng = emod.get_engine(dev)
 
-    V, H, W, n_sfm, aligner, subsample = WORKLOADS[args.workload]
+    V_total, H, W, n_sfm, aligner, subsample = WORKLOADS[args.workload]
     if args.views:
-        V = args.views
+        V_total = args.views
+    strong = args.scaling == "strong"
     cfg = make_config(aligner, subsample)
-    sc = mod("synthetic").make_scene(n_views=V, H=H, W=W, n_sfm=n_sfm, seed=20261104 + 7919 * rank,
-                                     device=str(dev), low_conf_every=50)
+    if strong:
+        # BASELINE configs 3 / 4: ONE scene, its views block-partitioned over the ranks in dataset order.
+        # A view is a pure function of (seed, view index), but the SfM table couples views (foreign
+        # indices), so every rank generates the scene's small per-view data for all views and keeps the
+        # depth / mask / image of its own block only.
+        mine = dmod.view_partition(V_total, world, rank)
+        sc_all = mod("synthetic").make_scene(n_views=V_total, H=H, W=W, n_sfm=n_sfm, seed=20261104, device=str(dev),
+                                             low_conf_every=50, keep_views=mine)
+        sc = sc_all
+        V = len(mine)
+    else:
+        V = V_total
+        sc = mod("synthetic").make_scene(n_views=V, H=H, W=W, n_sfm=n_sfm, seed=20261104 + 7919 * rank,
+                                         device=str(dev), low_conf_every=50)
     depth, mask, image = sc.depth, sc.mask, sc.image   # resident in HBM before the timed region
-    sfm = mdi.SfmTable(sc.points, sc.point_indices, sc.names, dev)
+    names, K, c2w = sc.names, sc.K, sc.c2w
+    sfm = mdi.SfmTable(sc.points, sc.point_indices, names, dev)
     HW = H * W
-    input_bytes = depth.numel() * 4 + mask.numel() + image.numel()
 
     torch.manual_seed(1234)   # RANSAC device-sampler seeds are drawn from torch's CPU generator
 
@@ -231,16 +262,18 @@ def run_ours(args):
     if world > 1:
         try:
             exchange = dmod.CloudExchange(dev, capacity_rows=1 << 22)
-            gather = ("emit kernel writes every rank's cloud through NVSwitch multicast (multimem.st)" if exchange.use_multicast
-                      else "emit kernel writes peer clouds over NVLink (symmetric memory)")
+            gather = ("emit kernel writes every rank's cloud through NVSwitch multicast (multimem.st.v4)" if exchange.use_multicast
+                      else "emit kernel writes peer clouds over NVLink (16-byte stores, symmetric memory); counts exchanged on the device")
         except Exception as e:  # noqa: BLE001 - any failure to map peer memory selects the NCCL path
             gather = f"nccl all_gather ({type(e).__name__})"
 
-    def step():
-        res = mdi.points_from_views(cfg, depth, mask, image, sc.K, sc.c2w, sc.names, sc.points,
-                                    sc.point_indices, dev, L.IMAGE_U8, sfm=sfm, exchange=exchange)
-        if world > 1 and exchange is None:
-            res.xyz, res.rgb, _ = dmod.allgather_points(res.xyz, res.rgb)
+    def step(ex=exchange):
+        res = mdi.points_from_views(cfg, depth, mask, image, K, c2w, names, sc.points,
+                                    sc.point_indices, dev, L.IMAGE_U8, sfm=sfm, exchange=ex)
+        if world > 1 and ex is None:
+            res.xyz, res.rgb, _ = dmod.allgather_points(
+                res.xyz if res.xyz is not None else torch.empty((0, 3), device=dev),
+                res.rgb if res.rgb is not None else torch.empty((0, 3), device=dev))
         return res
 
     def barrier():
@@ -248,47 +281,92 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed_loop(n_steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        r = None
+        for _ in range(n_steps):
+            r = step()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms), r
+
     n_warm = args.warmup if args.profile_mode else max(args.warmup, 3)
     for _ in range(n_warm):
         res = step()
     barrier()
+    # ---- multi-GPU bit-identity, visible to the driver: the fused exchange cloud against the NCCL
+    # all-gather of the per-rank clouds (same views, same RANSAC seeds), once, outside the timed region
+    exchange_parity = None
+    if world > 1 and exchange is not None and not args.profile_mode:
+        torch.manual_seed(99)
+        fused = step()
+        fx, fr = fused.xyz.clone(), fused.rgb.clone()
+        torch.manual_seed(99)
+        plain = step(ex=None)
+        ok = bool(fx.shape == plain.xyz.shape and torch.equal(fx, plain.xyz) and torch.equal(fr, plain.rgb))
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        exchange_parity = bool(int(flag))
+        del fx, fr, fused, plain
+        torch.manual_seed(1234)
+        for _ in range(2):
+            step()
+        barrier()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
     lib = L.load()
-    lib.mdi_profile_enable(1)   # CUDA events around every kernel launch of the library
+    # timed loop 1: the headline -- no per-kernel events inside the timed region
+    lib.mdi_profile_enable(0)
+    ms_total, res = timed_loop(args.steps)
+    # timed loop 2: the same steps with CUDA events around every kernel launch of the library
+    lib.mdi_profile_enable(1)
     L.profile_collect()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    for _ in range(args.steps):
-        res = step()
-    e1.record()
-    barrier()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms)
+    ms_prof, res = timed_loop(args.steps)
     ktimes = L.profile_collect()
     lib.mdi_profile_enable(0)
-    launches = sum(v["calls"] for k, v in ktimes.items() if k != "keep_zero_fill")
+    launches = sum(v["calls"] for k, v in ktimes.items() if k != "keep_zero_fill") // 1
+    n_kept_total = int(res.xyz.shape[0]) if res.xyz is not None else 0
     n_kept = int(res.total)
-    n_ok = int((res.status == 0).sum())
+    n_ok = int((res.status == 0).sum()) if res.status is not None else 0
 
     if args.profile_mode:
         if rank == 0:
             clocks.stop()
-            print(json.dumps({"profile_mode": True, "ms_per_step": ms_total / args.steps, "kernels": ktimes,
+            print(json.dumps({"profile_mode": True, "ms_per_step": ms_total / args.steps,
+                              "ms_per_step_profiled": ms_prof / args.steps, "kernels": ktimes,
                               "kept": n_kept, "views": V}))
         if world > 1:
             dist.destroy_process_group()
         return
+    # ---- cold call: what a training run sees (the init path runs ONCE, runner.py:77-78): a fresh
+    # Engine -- no cached descriptor table, no output-size hint, no workspaces -- kernels warm
+    cold = []
+    idx = dev.index
+    for _ in range(3):
+        emod._engines.pop(idx, None)
+        barrier()
+        t0 = time.perf_counter()
+        step()
+        torch.cuda.synchronize()
+        cold.append(1e3 * (time.perf_counter() - t0))
+    emod._engines[idx] = eng
+    cold_ms = torch.tensor([sorted(cold)[1]], device=dev)
+    if world > 1:
+        dist.all_reduce(cold_ms, op=dist.ReduceOp.MAX)
+    for _ in range(2):
+        step()
     # ---- end to end: host buffers in, rgb out, through the public API --------------------------
     depth_h = depth.cpu().pin_memory(); mask_h = mask.cpu().pin_memory(); image_h = image.cpu().pin_memory()
     h2d = d2h = 0
     for _ in range(3):  # warm-up with the timed loop's own binding pattern: the previous result is still alive
         # while the next call allocates, so the caching allocator needs its second set of blocks before timing
-        r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names,
+        r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, K, c2w, names,
                                                          sc.points, sc.point_indices, dev, L.IMAGE_U8,
                                                          exchange=exchange)
         if world > 1 and exchange is None:
@@ -301,7 +379,7 @@ def run_ours(args):
     e2e_step_ms = []
     for _ in range(e2e_steps):
         t_step = time.perf_counter()
-        r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, sc.K, sc.c2w, sc.names,
+        r2, rgb_h, h2d, d2h = mdi.points_from_host_views(cfg, depth_h, mask_h, image_h, K, c2w, names,
                                                          sc.points, sc.point_indices, dev, L.IMAGE_U8,
                                                          exchange=exchange)
         if world > 1 and exchange is None:
@@ -318,17 +396,19 @@ def run_ours(args):
             dist.destroy_process_group()
         return
 
+    views_step = V_total if strong else world * V      # views all ranks process per step
     ms_step = ms_total / args.steps
-    views_per_s = world * V / (ms_step * 1e-3)
-    e2e_views_per_s = world * V / (float(e2e_ms) / e2e_steps * 1e-3)
+    views_per_s = views_step / (ms_step * 1e-3)
+    e2e_views_per_s = views_step / (float(e2e_ms) / e2e_steps * 1e-3)
     # ---- roofline of the dominant launch group ---------------------------------------------------
     peaks_path = ROOT / "MEASURED_PEAKS.json"
     if peaks_path.exists():
         peak, peak_src = float(json.loads(peaks_path.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    n_slots = sum(len(sc.point_indices[n]) for n in sc.names)
-    hbm_calls = {k: v for k, v in ktimes.items() if algorithmic_bytes(k, HW, V, n_kept, n_slots, subsample == "adaptive") > 0}
+    n_slots = sum(len(sc.point_indices[n]) for n in names)
+    adaptive = subsample == "adaptive"
+    hbm_calls = {k: v for k, v in ktimes.items() if algorithmic_bytes(k, HW, V, n_kept, n_slots, adaptive) > 0}
     dom = max(hbm_calls, key=lambda k: hbm_calls[k]["ms"]) if hbm_calls else None
     traffic = None   # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu capture
     tpath = ROOT / "profiles" / "ncu_traffic.json"
@@ -338,33 +418,45 @@ def run_ours(args):
     breakdown = {}
     for k, v in ktimes.items():
         per = v["ms"] / v["calls"]
-        b = algorithmic_bytes(k, HW, V, n_kept, n_slots, subsample == "adaptive")
-        breakdown[k] = {"ms_per_call": round(per, 4), "share": round(v["ms"] / ms_total, 4),
+        b = algorithmic_bytes(k, HW, V, n_kept, n_slots, adaptive)
+        breakdown[k] = {"ms_per_call": round(per, 4), "share": round(v["ms"] / ms_prof, 4),
                         "algorithmic_GBps": round(b / (per * 1e-3) / 1e9, 1) if b else None}
     if dom:
         per = ktimes[dom]["ms"] / ktimes[dom]["calls"]
-        ach = algorithmic_bytes(dom, HW, V, n_kept, n_slots, subsample == "adaptive") / (per * 1e-3) / 1e9
+        ach = algorithmic_bytes(dom, HW, V, n_kept, n_slots, adaptive) / (per * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": traffic, "peak_source": peak_src,
-                "note": "achieved = algorithmic bytes of one launch / its mean CUDA-event duration inside the timed region"}
+                "note": "achieved = algorithmic bytes of one launch / its mean CUDA-event duration inside the (profiled) timed loop"}
+    # the a7 statistics group as a whole: ONE algorithmic read of depth + mask over the sum of its kernels
+    group = [k for k in ktimes if k.startswith("stats_")]
+    roof_group = None
+    if group and adaptive:
+        g_ms = sum(ktimes[k]["ms"] / ktimes[k]["calls"] for k in group)
+        g_ach = V * HW * 5.0 / (g_ms * 1e-3) / 1e9
+        roof_group = {"bound": "hbm", "kernels": sorted(group), "ms": round(g_ms, 4), "achieved": g_ach, "peak": peak,
+                      "unit": "GB/s", "frac": g_ach / peak}
     # whole-step algorithmic bytes: P*HW*5 + HW + 36*Nk + 16*M per view
-    P = 2 if subsample == "adaptive" else 1
+    P = 2 if adaptive else 1
     step_bytes = V * (P * HW * 5 + HW) + 36 * n_kept + 16 * n_slots
     nv, dt, kept_cpu, cores = cpu_reference_run(args.workload, args.cpu_views)
     out = {
         "metric": "init views/sec (align+subsample+unproject)", "value": views_per_s, "unit": "views/s",
         "n_gpus": world, "steps": args.steps, "warmup": n_warm, "ms_per_step": ms_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "views_per_gpu": V, "H": H, "W": W, "sfm_points_per_view": n_sfm,
-                   "aligner": aligner, "subsample": subsample, "patch_mask": True,
-                   "l2": f"inputs {input_bytes / 1e6:.0f} MB per step > 126 MB L2, no flush needed",
-                   "views_ok": n_ok, "kept_points_per_gpu": n_kept, "exchange": gather},
-        "mpts_per_s": world * n_kept / (ms_step * 1e-3) / 1e6,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, args.scaling, world),
+        "run": {"views_ok_rank0": n_ok, "kept_points_rank0": n_kept, "cloud_rows": n_kept_total, "exchange": gather,
+                "numa": numa},
+        "ms_per_step_profiled": ms_prof / args.steps,
+        "cold_call_ms": float(cold_ms),
+        "cold_call_note": "one call on a fresh Engine (no cached descriptor table, no output-size hint, no workspaces), "
+                          "kernels warm, host wall clock to completion; median of 3, max over ranks",
+        "exchange_parity": exchange_parity,
+        "mpts_per_s": (n_kept_total if world > 1 else n_kept) / (ms_step * 1e-3) / 1e6,
         "step_algorithmic_GBps": step_bytes / (ms_step * 1e-3) / 1e9,
         "step_frac_of_peak": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
-        "roofline": roof, "kernels": breakdown,
+        "roofline": roof, "roofline_group": roof_group, "kernels": breakdown,
         "cpu_baseline": {"value": nv / dt, "unit": "views/s", "cores": cores, "kind": "port",
-                         "sample": f"{nv} of {V} views of the same workload, oracle port of the reference loop on the host"},
+                         "sample": f"{nv} of {V_total} views of the same workload, oracle port of the reference loop on the host"},
         "e2e": {"value": e2e_views_per_s, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "step_ms": e2e_step_ms},
         "gpu_launches": launches, "clocks": clk,
@@ -383,6 +475,8 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
     ap.add_argument("--cpu-views", type=int, default=12, help="views in the bounded CPU sample")
     ap.add_argument("--views", type=int, default=0, help="override views per GPU (profiling runs only)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank owns the workload's views; strong: the workload's views are sharded over the ranks")
     ap.add_argument("--profile-mode", action="store_true",
                     help="short run for ncu: warm-up as given, no e2e / CPU legs (not a bench value)")
     args = ap.parse_args()
