@@ -77,6 +77,7 @@ _SIGNATURES = {
     "mdi_gather_fit": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P, _INT, _INT, _P, _P]),
     "mdi_ransac": (_INT, [_P, _INT, _P, _P, _P, _P, _P, C.POINTER(RansacConfigC), _INT, _P, _P, _P, _P, _P]),
     "mdi_apply_scale_shift": (_INT, [_P, _I64, _P, _P, _P]),
+    "mdi_apply_region_scale_shift": (_INT, [_P, _P, _I64, _P, _P, _INT, _P, _P]),
     "mdi_depth_range_workspace_bytes": (_I64, [_INT, _I64]),
     "mdi_depth_range": (_INT, [_P, _INT, _I64, _P, _P, _INT, _P, _P, _P, _P, _P]),
     "mdi_grad_range": (_INT, [_P, _INT, _I64, _P, _P, _P, _P]),
@@ -94,6 +95,8 @@ _SIGNATURES = {
     "mdi_knn_workspace_bytes": (_I64, [_I64]),
     "mdi_knn": (_INT, [_P, _I64, _INT, _INT, _P, _P, _P, _P, _P]),
     "mdi_lof": (_INT, [_I64, _INT, _P, _P, _P, _P, _P, _P, _P]),
+    "mdi_interp_workspace_bytes": (_I64, [_INT, _INT]),
+    "mdi_interp_scale_map": (_INT, [_P, _P, _P, _P, _INT, C.c_double, _INT, _INT, _P, _P, _P, _P, _P]),
     "mdi_merge_workspace_bytes": (_I64, [_I64]),
     "mdi_merge_subsample": (_INT, [_P, _P, _P, _I64, C.c_float, C.c_float, _INT, _P, _P, _P,
                                    C.POINTER(C.c_int64), C.POINTER(C.c_int32), _P]),

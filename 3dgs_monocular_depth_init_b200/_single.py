@@ -54,7 +54,7 @@ def options_from_config(config, **over) -> RunOptions:
     aligner = getattr(aligner, "value", aligner)
     rc = mdi.alignment.ransac
     opt = RunOptions(
-        aligner=str(aligner),
+        aligner=None if aligner is None else str(aligner),
         ransac_threshold=rc.inlier_threshold, ransac_max_iters=rc.max_iters,
         ransac_confidence=rc.confidence, ransac_sample_size=rc.sample_size,
         ransac_min_iters=rc.min_iters,
@@ -66,10 +66,8 @@ def options_from_config(config, **over) -> RunOptions:
         patch_threshold=mdi.num_sfm_points_mask.threshold,
         grad_thresh=mdi.depth_grad_mask_thresh,
     )
-    if mdi.alignment.segmenter is not None:
-        raise NotImplementedError("depth segmentation is outside the B200 path (SURVEY.md 8f)")
-    if opt.aligner not in ("lstsqrs", "ransac", "msac"):
-        raise NotImplementedError(f"Depth alignment strategy not on the B200 path: {opt.aligner}")
+    if opt.aligner not in ("lstsqrs", "ransac", "msac", "interp"):
+        raise NotImplementedError(f"Unknown depth alignment strategy: {opt.aligner}")
     if opt.subsample != "adaptive" and not isinstance(opt.subsample, int):
         raise ValueError(f"Unsupported subsampling factor: {opt.subsample}")
     for k, v in over.items():

@@ -175,6 +175,22 @@ __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_
     out[i] = align_depth(depth[i], s, t);
 }
 
+// Stitch of the region-wise alignment (pipeline.py:252-283): pixel p of region r gets
+// depth * s_r + t_r; pixels of a region without a fit (no SfM point in it) and pixels outside every
+// aligned region keep the sentinel -42.0.  region int32 [n]: index into the table, < 0 = none.
+__global__ void apply_region_scale_shift_kernel(const float* __restrict__ depth, const int32_t* __restrict__ region,
+                                                int64_t n, const float* __restrict__ table,
+                                                const uint8_t* __restrict__ valid, int n_regions,
+                                                float* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int r = region[i];
+    float a = -42.0f;
+    if (r >= 0 && r < n_regions && valid[r]) a = align_depth(depth[i], table[2 * r], table[2 * r + 1]);
+    out[i] = a;
+  }
+}
+
 // small host table -> device, read by the SMs from mapped pinned memory (see mdi_upload_table)
 __global__ void upload_table_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, int64_t n_words) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -237,6 +253,21 @@ extern "C" int mdi_gather_fit(const MdiView* views, int n_views, int64_t slots, 
       views, slots, uv, z, n_valid, d, sums, scale_shift, write_fit, patch_threshold,
       patch_blocked);
   MDI_CHECK_LAUNCH("mdi_gather_fit");
+  return MDI_OK;
+}
+
+extern "C" int mdi_apply_region_scale_shift(const float* depth, const int32_t* region, int64_t n,
+                                            const float* table, const uint8_t* valid, int n_regions,
+                                            float* out, void* stream) {
+  MDI_REQUIRE(n >= 0 && n_regions >= 0, "mdi_apply_region_scale_shift: negative size");
+  if (n == 0) return MDI_OK;
+  MDI_REQUIRE(depth && region && out && (n_regions == 0 || (table && valid)), "mdi_apply_region_scale_shift: null pointer");
+  int blocks = (int)((n + 1023) / 1024);
+  if (blocks > mdi::kSMs * 16) blocks = mdi::kSMs * 16;
+  mdi::prof_mark("apply_region_scale_shift_kernel", (cudaStream_t)stream);
+  mdi::apply_region_scale_shift_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(depth, region, n, table, valid,
+                                                                                 n_regions, out);
+  MDI_CHECK_LAUNCH("mdi_apply_region_scale_shift");
   return MDI_OK;
 }
 

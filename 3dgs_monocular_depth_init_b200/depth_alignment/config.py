@@ -1,8 +1,8 @@
 """Alignment configuration: same field names, types and defaults as the reference
 (gs_init_compare/depth_alignment/config.py:6-142), with default_factory so the dataclasses
-import on Python >= 3.11.  Segmentation / interp strategies are outside this path (SURVEY
-section 8f); their enum members are kept so CLI strings still parse, and selecting them raises
-NotImplementedError like an unknown strategy does in the reference (config.py:34)."""
+import on Python >= 3.11.  The SAM / SLIC segmenters themselves are outside this path (SURVEY
+section 8f): their enum members are kept so CLI strings still parse, and region-wise alignment takes
+a caller-supplied integer segmentation instead (depth_alignment/pipeline.py)."""
 from dataclasses import dataclass, field
 from enum import Enum
 from typing import Literal, Optional
@@ -27,7 +27,11 @@ class DepthAlignmentStrategyEnum(str, Enum):
             from .alignment.ransacs import DepthAlignmentMsac
 
             return DepthAlignmentMsac
-        raise NotImplementedError(f"Depth alignment strategy not on the B200 path: {self}")
+        if self == self.interp:
+            from .alignment.interp import DepthAlignmentInterpolate
+
+            return DepthAlignmentInterpolate
+        raise NotImplementedError(f"Unknown depth alignment strategy: {self}")
 
 
 class DepthSegmentationStrategyEnum(str, Enum):

@@ -72,14 +72,21 @@ def get_pts_from_depth(predicted_depth: PredictedDepth, image: InputImage, parse
     M = int(sfm.shape[0])
     opt = options_from_config(config, want_rgb=False)
     if opt.aligner in ("ransac", "msac"):
-        if sample_idx is not None:
+        if sample_idx is not None and config.mdi.alignment.segmenter is None:
             opt.sample_idx = sample_idx.to(device=dev, dtype=torch.int32).contiguous()[None]
-        else:
+        elif sample_idx is None:
             opt.ransac_seed = ransac_seed()
         opt.want_inliers = bool(return_result)   # RunResult.inlier_mask: the final inlier set (ransacs.py:150-151)
     vin = single_view_inputs(predicted_depth.depth, predicted_depth.mask, dev, K=image.K, c2w=image.cam2world,
                              sfm_xyz=sfm.contiguous(), sfm_counts=[M])
-    res = eng.run(vin, opt)
+    if config.mdi.alignment.segmenter is not None:
+        from ..depth_alignment.pipeline import run_views_materialised
+        res = run_views_materialised(eng, vin, config, opt, None if sample_idx is None else [sample_idx])
+    elif opt.aligner == "interp":
+        from ..depth_alignment.alignment.interp import run_views_with_interp
+        res = run_views_with_interp(eng, vin, config, opt, None if sample_idx is None else sample_idx[None])
+    else:
+        res = eng.run(vin, opt)
     status, n_inb = int(res.status[0].item()), int(res.n_inbounds[0].item())
     if status & L.STATUS_LOW_CONFIDENCE:
         _raise_low_confidence(n_inb, M)

@@ -138,14 +138,20 @@ def points_from_views(config, depths, masks, images, K, c2w, names, points: np.n
         sfm = SfmTable(points, point_indices, names, dev)
     opt = options_from_config(config)
     if opt.aligner in ("ransac", "msac"):
-        if sample_idx is not None:
+        if sample_idx is not None and config.mdi.alignment.segmenter is None:
             opt.sample_idx = sample_idx.to(device=dev, dtype=torch.int32).contiguous()
-        else:
+        elif sample_idx is None:
             opt.ransac_seed = ransac_seed()
     opt.exchange = exchange
     opt.defer_emit = bool(defer_emit)
     vin = ViewInputs(depth=depths, mask=masks, image=images, image_kind=image_kind, K=K, c2w=c2w,
                      sfm_xyz=sfm.xyz, sfm_index=sfm.index, sfm_counts=sfm.counts)
+    if config.mdi.alignment.segmenter is not None:   # region-wise alignment: aligned map materialised per view
+        from .depth_alignment.pipeline import run_views_materialised
+        return run_views_materialised(eng, vin, config, opt, sample_idx)
+    if opt.aligner == "interp":   # per-pixel scale map: aligned depth materialised per view, then the mask stages
+        from .depth_alignment.alignment.interp import run_views_with_interp
+        return run_views_with_interp(eng, vin, config, opt, sample_idx)
     return eng.run(vin, opt)
 
 

@@ -16,6 +16,7 @@
  *                           gs_init_compare/depth_subsampling/num_sfm_points_mask.py:7-64
  *   mdi_ransac              gs_init_compare/depth_alignment/alignment/ransacs.py:60-189
  *   mdi_apply_scale_shift   lstsqrs.py:51-54 / ransacs.py:186-189 (aligned_depth = depth*s + t)
+ *   mdi_apply_region_scale_shift  depth_alignment/pipeline.py:252-283 (per-region stitch)
  *   mdi_depth_range         gs_init_compare/depth_subsampling/adaptive_subsampling.py:82-98
  *   mdi_grad_range          points_from_depth.py:192-212 (min / max of the gradient map)
  *   mdi_factor_table        adaptive_subsampling.py:12-17,89-120 (stride as a function of depth)
@@ -28,6 +29,8 @@
  *   mdi_merge_subsample     native_modules/subsampling/src/impl.cpp:198-274,313-426
  *   mdi_knn / mdi_lof       point_cloud_postprocess/postprocess.py:16-22 (sklearn LOF),
  *                           utils/runner_utils.py:143-147 (knn)
+ *   mdi_interp_scale_map    depth_alignment/alignment/interp.py:75-110,355-361 (LinearNDInterpolator
+ *                           over the pixel grid, scale map * pre-aligned depth)
  */
 #ifndef MDI_B200_H_
 #define MDI_B200_H_
@@ -204,6 +207,16 @@ int mdi_ransac(const MdiView* views, int n_views, const float* d, const float* z
 /* aligned = depth * s + t as two separately rounded fp32 operations; scale_shift on device */
 int mdi_apply_scale_shift(const float* depth, int64_t n, const float* scale_shift, float* out,
                           void* stream);
+
+/*
+ * Region-wise alignment (pipeline.py:196-283, 8f-4): stitches the per-region fits into one aligned
+ * map.  region int32 [n] = index of each pixel's region in `table` (float32 [R,2] scale / shift),
+ * negative = no region; valid uint8 [R] = region has a fit.  Pixels without a valid region get the
+ * reference's sentinel -42.0 (masked out by the caller, pipeline.py:285-288).
+ */
+int mdi_apply_region_scale_shift(const float* depth, const int32_t* region, int64_t n,
+                                 const float* table, const uint8_t* valid, int n_regions, float* out,
+                                 void* stream);
 
 /*
  * a7 (statistics): per view, over pixels with mask & (aligned != -42): min, max and the exact
@@ -383,6 +396,23 @@ int mdi_knn(const float* pts, int64_t n, int k, int exclude_self, void* workspac
  */
 int mdi_lof(int64_t n, int k, const int32_t* idx, const float* dist, const float* kdist, float* lrd,
             float* lof, uint8_t* outlier, void* stream);
+
+/*
+ * `interp` aligner (8f-3): evaluates scipy's LinearNDInterpolator at every pixel (x, y) of an H x W
+ * view and multiplies the pre-aligned depth by it (interp.py:75-110, 355-361).
+ *   transform float64 [T,3,2], simplices int32 [T,3], points float64 [P,2] (x, y): the arrays of the
+ *   scipy.spatial.Delaunay object the host built (dt.transform, dt.simplices, dt.points), on the device;
+ *   values float64 [P] per-vertex scale factors; fill_value for pixels outside the hull.
+ *   base float32 [H*W] predicted depth and scale_shift float32 [2] (device) of the init alignment:
+ *   out[p] = float32(value(p)) * (base[p] * s + t); scale_shift NULL: out = float32(value) * base;
+ *   base NULL: out = float32(value) (the scale map itself).
+ *   workspace: mdi_interp_workspace_bytes(H, W) bytes.
+ */
+int64_t mdi_interp_workspace_bytes(int H, int W);
+int mdi_interp_scale_map(const double* transform, const int32_t* simplices, const double* points,
+                         const double* values, int n_tri, double fill_value, int H, int W,
+                         const float* base, const float* scale_shift, void* workspace, float* out,
+                         void* stream);
 
 #ifdef __cplusplus
 }

@@ -122,6 +122,59 @@ def _replay_reference_ransac(R, d, g, p, aligner):
     return h_best, inl_best
 
 
+def test_segmentation(H, W):
+    """The integer region map of the region-wise fixtures (three regions, ids 0 .. 2)."""
+    seg = torch.zeros((H, W), dtype=torch.int64)
+    seg[:, W // 2:] = 1
+    seg[H // 2:, : W // 3] = 2
+    return seg
+
+
+def run_reference_materialised(R, scene, i, aligner, subsample, seed, segmented=False, init="ransac"):
+    """Views whose alignment is not one scale / shift: the `interp` aligner (interp.py) and region-wise
+    alignment (pipeline.py:196-283, with a fixed segmentation; the SAM / SLIC segmenters and the RAG
+    region merging are out of scope, so merging is the identity here).  Stores the aligned map too."""
+    cfg = R.Config()
+    cfg.mdi.alignment.aligner = R.DepthAlignmentStrategyEnum(aligner)
+    cfg.mdi.alignment.interp.init = init
+    cfg.mdi.subsample_factor = subsample
+    # the reference's nested config defaults are shared instances: reset everything an earlier case touched
+    cfg.mdi.depth_grad_mask_thresh = None
+    cfg.mdi.use_num_sfm_points_mask = True
+    cfg.mdi.adaptive_subsampling.factor_range_min, cfg.mdi.adaptive_subsampling.factor_range_max = 5, 15
+    cfg.mdi.num_sfm_points_mask.num_patches_small_axis, cfg.mdi.num_sfm_points_mask.threshold = 20, 15
+    img01 = scene.image[i].float() / 255.0
+    depth, mask = scene.depth[i], scene.mask[i]
+    H, W = depth.shape
+    image = R.InputImage(data=img01, name=scene.names[i], cam2world=scene.c2w[i], K=scene.K[i])
+    orig_from_config, orig_merge = R.pipeline.DepthAlignmentPipeline.from_config, R.pipeline.merge_segmentation_regions
+    if segmented:
+        seg = test_segmentation(H, W)
+        R.pipeline.merge_segmentation_regions = lambda pd, c, s, cf: s
+        R.pipeline.DepthAlignmentPipeline.from_config = staticmethod(
+            lambda config: R.pipeline.DepthAlignmentPipeline(config, lambda pd, ck, cf: seg,
+                                                             config.mdi.alignment.aligner.get_implementation()))
+    try:
+        torch.manual_seed(seed)
+        with contextlib.redirect_stdout(io.StringIO()):
+            pts, keep, P = R.points_from_depth.get_pts_from_depth(R.PredictedDepth(depth.clone(), mask.clone()), image,
+                                                                  _Parser(scene), cfg, "cpu")
+        sfm = torch.from_numpy(scene.points[scene.point_indices[scene.names[i]]]).float()
+        with contextlib.redirect_stdout(io.StringIO()):
+            uv, z = R.points_from_depth.project_and_filter_sfm_pts(img01, sfm, P, depth.T.shape,
+                                                                   R.PredictedDepth(depth, mask), None)
+        torch.manual_seed(seed)
+        with contextlib.redirect_stdout(io.StringIO()):
+            res = R.pipeline.DepthAlignmentPipeline.from_config(cfg).align(
+                img01, R.PredictedDepth(depth.clone(), mask.clone()), uv, z, cfg, None)
+    finally:
+        R.pipeline.DepthAlignmentPipeline.from_config = orig_from_config
+        R.pipeline.merge_segmentation_regions = orig_merge
+    out = dict(raised=0, pts=pts.numpy(), keep=np.packbits(keep.numpy()), P=P.numpy(), rgb=img01.view(-1, 3)[keep].numpy(),
+               uv=uv.numpy(), z=z.numpy(), aligned=res.aligned_depth.numpy(), aligned_mask=np.packbits(res.mask.numpy()))
+    return out
+
+
 def save_case(name, scene, i, meta, out, store_inputs, digest_rgb=False):
     arrs = {k: np.asarray(v) for k, v in out.items()}
     if digest_rgb and "rgb" in arrs:
@@ -163,6 +216,13 @@ def main():
     for name, scene, gen, i, kw in cases:
         out = run_reference_view(R, scene, i, **kw)
         save_case(name, scene, i, dict(gen=gen, view=i, **kw), out, store_inputs=True)
+    # 8f-3 / 8f-4: interp aligner and region-wise alignment (aligned maps stored)
+    for name, i, kw in [("small_interp_ransac_init", 0, dict(aligner="interp", subsample=4, seed=31)),
+                        ("small_interp_lstsq_init", 2, dict(aligner="interp", subsample="adaptive", seed=32, init="lstsqrs")),
+                        ("small_regions_ransac", 1, dict(aligner="ransac", subsample=4, seed=33, segmented=True)),
+                        ("small_regions_lstsq", 0, dict(aligner="lstsqrs", subsample=5, seed=34, segmented=True))]:
+        out = run_reference_materialised(R, sc, i, **kw)
+        save_case(name, sc, i, dict(gen=small, view=i, **kw), out, store_inputs=True)
     # full-size views of BASELINE configs C1 / C2 (inputs regenerated from the seed)
     full = dict(n_views=2, H=840, W=1297, n_sfm=5000, seed=20261104, low_conf_every=50)
     sf = S.make_scene(**full)

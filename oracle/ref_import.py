@@ -78,9 +78,14 @@ def load():
         stub("nerfbaselines", Method=object, MethodInfo=dict, ModelInfo=dict, Dataset=dict,
              OptimizeEmbeddingOutput=dict)
         stub("nerfbaselines.utils", pad_poses=None, image_to_srgb=None, convert_image_dtype=None)
+        stub("torchrbf", RBFInterpolator=None)          # interp.py:23 (rbf method only)
+        stub("skimage.segmentation"); stub("skimage.measure"); stub("skimage.graph")
 
         from gs_init_compare.config import Config
         from gs_init_compare.depth_alignment.alignment import lstsqrs, ransacs
+        from gs_init_compare.depth_alignment.alignment import interp
+        from gs_init_compare.depth_alignment import pipeline
+        from gs_init_compare.depth_alignment.segmentation import region_margin
         from gs_init_compare.depth_alignment.config import DepthAlignmentStrategyEnum
         from gs_init_compare.depth_alignment.exceptions import LowDepthAlignmentConfidenceError
         from gs_init_compare.depth_alignment.pipeline import DepthAlignmentPipeline
@@ -95,7 +100,7 @@ def load():
     assert where.startswith(os.path.realpath(REFERENCE_ROOT)), f"gs_init_compare resolved to {where}, not the reference"
     assert "3dgs_monocular_depth_init_b200" not in points_from_depth.get_pts_from_depth.__module__
     ns = types.SimpleNamespace(
-        Config=Config, lstsqrs=lstsqrs, ransacs=ransacs,
+        Config=Config, lstsqrs=lstsqrs, ransacs=ransacs, interp=interp, pipeline=pipeline, region_margin=region_margin,
         DepthAlignmentStrategyEnum=DepthAlignmentStrategyEnum,
         LowDepthAlignmentConfidenceError=LowDepthAlignmentConfidenceError,
         DepthAlignmentPipeline=DepthAlignmentPipeline, points_from_depth=points_from_depth,

@@ -21,6 +21,19 @@ SMALL_CASES = ["small_lstsq_static4", "small_ransac_adaptive", "small_msac_stati
 FULL_CASES = ["c1_lstsq_static10", "c2_ransac_adaptive"]
 # one view of each larger BASELINE shape (C3 1920x1080, C4 3840x2160, C5 1600x1200), RANSAC + adaptive
 BIG_CASES = ["c3_view_1920x1080", "c4_view_3840x2160", "c5_view_1600x1200"]
+# 8f-3 / 8f-4: interp aligner and region-wise alignment (the fixtures also hold the aligned depth map)
+MATERIALISED_CASES = ["small_interp_ransac_init", "small_interp_lstsq_init", "small_regions_ransac", "small_regions_lstsq"]
+
+
+def case_segmentation(c):
+    """Region map of the region-wise fixtures (oracle/make_golden.py::test_segmentation), or None."""
+    if not c.meta.get("segmented"):
+        return None
+    H, W = c.depth.shape
+    seg = torch.zeros((H, W), dtype=torch.int64)
+    seg[:, W // 2:] = 1
+    seg[H // 2:, : W // 3] = 2
+    return seg
 
 _scene_cache = {}
 
@@ -55,6 +68,8 @@ def load_case(name):
     if not c.raised:
         H, W = c.depth.shape
         c.ref_keep = np.unpackbits(c.ref_keep)[: H * W].astype(bool)
+        if hasattr(c, "ref_aligned_mask"):
+            c.ref_aligned_mask = np.unpackbits(c.ref_aligned_mask)[: H * W].astype(bool).reshape(H, W)
         if hasattr(c, "ref_ransac_inlier_mask"):  # final inlier set of the reference loop (ransacs.py:150-151)
             c.ref_ransac_inlier_mask = np.unpackbits(c.ref_ransac_inlier_mask)[: c.ref_uv.shape[1]].astype(bool)
     return c
@@ -85,6 +100,7 @@ def case_config(c):
     cfg.mdi.adaptive_subsampling.factor_range_max = m.get("fmax", 15)
     cfg.mdi.num_sfm_points_mask.num_patches_small_axis = m.get("n_small", 20)
     cfg.mdi.num_sfm_points_mask.threshold = m.get("thr", 15)
+    cfg.mdi.alignment.interp.init = m.get("init", "ransac")
     return cfg
 
 
@@ -92,7 +108,8 @@ def oracle_kwargs(c):
     m = c.meta
     return dict(aligner=m["aligner"], subsample=m["subsample"], use_patch_mask=m.get("use_patch", True),
                 n_small=m.get("n_small", 20), patch_threshold=m.get("thr", 15), grad_thresh=m.get("grad"),
-                fmin=m.get("fmin", 5), fmax=m.get("fmax", 15))
+                fmin=m.get("fmin", 5), fmax=m.get("fmax", 15), interp_init=m.get("init", "ransac"),
+                segmentation=case_segmentation(c))
 
 
 class OneViewParser:

@@ -8,10 +8,11 @@ import torch
 
 import mdi_oracle as O
 import ref_import
-from helpers import BIG_CASES, FULL_CASES, GOLDEN, SMALL_CASES, load_case, oracle_kwargs, rgb_matches
+from helpers import (BIG_CASES, FULL_CASES, GOLDEN, MATERIALISED_CASES, SMALL_CASES, case_segmentation, load_case,
+                     oracle_kwargs, rgb_matches)
 
 
-@pytest.mark.parametrize("name", SMALL_CASES + FULL_CASES + BIG_CASES)
+@pytest.mark.parametrize("name", SMALL_CASES + FULL_CASES + BIG_CASES + MATERIALISED_CASES)
 def test_oracle_matches_golden(name):
     c = load_case(name)
     torch.manual_seed(c.meta["seed"])
@@ -27,7 +28,8 @@ def test_oracle_matches_golden(name):
         torch.set_num_threads(nt)
     assert np.array_equal(tr.P.numpy(), c.ref_P)
     assert np.array_equal(tr.uv.numpy(), c.ref_uv) and np.array_equal(tr.z.numpy(), c.ref_z)
-    assert np.float32(tr.scale) == c.ref_scale and np.float32(tr.shift) == c.ref_shift
+    if hasattr(c, "ref_scale"):
+        assert np.float32(tr.scale) == c.ref_scale and np.float32(tr.shift) == c.ref_shift
     assert np.array_equal(tr.keep.numpy(), c.ref_keep)
     assert np.array_equal(tr.pts_world.numpy(), c.ref_pts)
     rgb = (c.image.float() / 255.0).view(-1, 3)[tr.keep].numpy()
@@ -36,7 +38,7 @@ def test_oracle_matches_golden(name):
         assert tr.ransac.last_iter == int(c.ref_ransac_iters)
         assert tr.ransac.n_inliers == int(c.ref_ransac_inliers)
         assert np.array_equal(tr.ransac.inliers.numpy(), c.ref_ransac_inlier_mask)
-    if tr.lo_hi is not None:
+    if tr.lo_hi is not None and hasattr(c, "ref_lo"):
         assert np.float32(tr.lo_hi[0]) == c.ref_lo and np.float32(tr.lo_hi[1]) == c.ref_hi
 
 
@@ -95,3 +97,20 @@ def test_oracle_vs_reference_live():
     torch.manual_seed(99)
     tr = O.points_from_depth(c.depth, c.mask, c.K, c.c2w, c.sfm, aligner="ransac", subsample="adaptive")
     assert torch.equal(keep, tr.keep) and torch.equal(pts, tr.pts_world) and torch.equal(Pm, tr.P)
+
+
+@pytest.mark.parametrize("name", MATERIALISED_CASES)
+def test_oracle_aligned_map_matches_golden(name):
+    """interp.py:281-361 / pipeline.py:196-288: the aligned depth MAP of the reference, bit for bit."""
+    c = load_case(name)
+    uv, z = torch.from_numpy(c.ref_uv), torch.from_numpy(c.ref_z)
+    torch.manual_seed(c.meta["seed"])
+    seg = case_segmentation(c)
+    if seg is not None:
+        out, mask, _, fits = O.align_regions(c.depth, c.mask, uv, z, seg, c.meta["aligner"])
+        assert len(fits) == 3
+    else:
+        out, removed, _ = O.interp_align(c.depth, uv, z, init=c.meta.get("init", "ransac"))
+        mask = (out != -42.0) & c.mask
+        assert 0 < int(removed.sum()) < 60        # ~1 % scale-only outliers are dropped
+    assert np.array_equal(out.numpy(), c.ref_aligned) and np.array_equal(mask.numpy(), c.ref_aligned_mask)
