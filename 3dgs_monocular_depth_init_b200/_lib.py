@@ -95,6 +95,11 @@ _SIGNATURES = {
     "mdi_knn_workspace_bytes": (_I64, [_I64]),
     "mdi_knn": (_INT, [_P, _I64, _INT, _INT, _P, _P, _P, _P, _P]),
     "mdi_lof": (_INT, [_I64, _INT, _P, _P, _P, _P, _P, _P, _P]),
+    "mdi_knn_build": (_INT, [_P, _I64, _P, _P]),
+    "mdi_knn_split": (_INT, [_P, _I64, _INT, _P, _P]),
+    "mdi_knn_query": (_INT, [_P, _I64, _INT, _INT, _I64, _I64, _P, _P, _P, _P, _P]),
+    "mdi_lof_lrd": (_INT, [_I64, _INT, _P, _P, _P, _P, _P]),
+    "mdi_lof_score": (_INT, [_I64, _INT, _P, _P, _P, _P, _P, _P]),
     "mdi_interp_workspace_bytes": (_I64, [_INT, _INT]),
     "mdi_interp_scale_map": (_INT, [_P, _P, _P, _P, _INT, C.c_double, _INT, _INT, _P, _P, _P, _P, _P]),
     "mdi_merge_workspace_bytes": (_I64, [_I64]),

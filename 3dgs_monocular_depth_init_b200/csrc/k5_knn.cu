@@ -203,12 +203,18 @@ struct KnnHeap {
 __global__ void __launch_bounds__(kKnnThreads)
 knn_query_kernel(const float4* __restrict__ sorted, const int32_t* __restrict__ start, int64_t n,
                  const KnnGrid* __restrict__ grid, int k, int exclude_self, int32_t* __restrict__ out_idx,
-                 float* __restrict__ out_dist, float* __restrict__ out_kdist) {
-  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= n) return;
+                 float* __restrict__ out_dist, float* __restrict__ out_kdist, int64_t q_begin, int64_t q_end,
+                 int32_t* __restrict__ out_self) {
+  // queries = sorted positions q_begin .. q_end - 1.  out_self == nullptr: results go to the row of the
+  // point's ORIGINAL index; otherwise (query split over ranks) to the compact row p - q_begin, and
+  // out_self records the original index of that row
+  const int64_t p = q_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= q_end) return;
   const KnnGrid g = *grid;
   const float4 q = sorted[p];
   const int self = __float_as_int(q.w);
+  const int64_t row = out_self ? p - q_begin : (int64_t)self;
+  if (out_self) out_self[row] = self;
   KnnHeap h;
   h.n = 0; h.k = k;
   uint32_t stk[64];
@@ -260,10 +266,10 @@ knn_query_kernel(const float4* __restrict__ sorted, const int32_t* __restrict__ 
   }
   for (int j = 0; j < k; ++j) {
     const bool ok = j < found;
-    out_idx[(int64_t)self * k + j] = ok ? h.id[j] : -1;
-    if (out_dist) out_dist[(int64_t)self * k + j] = ok ? (float)sqrt(h.d[j]) : INFINITY;
+    out_idx[row * k + j] = ok ? h.id[j] : -1;
+    if (out_dist) out_dist[row * k + j] = ok ? (float)sqrt(h.d[j]) : INFINITY;
   }
-  if (out_kdist) out_kdist[self] = found == k ? (float)sqrt(h.d[k - 1]) : INFINITY;
+  if (out_kdist) out_kdist[row] = found == k ? (float)sqrt(h.d[k - 1]) : INFINITY;
 }
 
 // numpy's float32 mean over a contiguous axis of k values: for 8 <= k <= 128 eight running sums,
@@ -304,10 +310,10 @@ lof_lrd_kernel(int64_t n, int k, const int32_t* __restrict__ idx, const float* _
 // sklearn _lof.py fit: negative_outlier_factor_ = -mean(lrd[neighbours] / lrd[self]); offset_ = -1.5
 __global__ void __launch_bounds__(kKnnThreads)
 lof_score_kernel(int64_t n, int k, const int32_t* __restrict__ idx, const float* __restrict__ lrd,
-                 float* __restrict__ lof, uint8_t* __restrict__ outlier) {
+                 const float* __restrict__ lrd_self, float* __restrict__ lof, uint8_t* __restrict__ outlier) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const float mine = lrd[i];
+  const float mine = lrd_self[i];
   float ratio[kKnnMaxK];
   for (int j = 0; j < k; ++j) ratio[j] = lrd[idx[i * k + j]] / mine;
   const float v = numpy_mean_f32(ratio, k);
@@ -322,21 +328,43 @@ extern "C" int64_t mdi_knn_workspace_bytes(int64_t n) {
   return mdi::knn_carve(nullptr, nullptr, n > 0 ? n : 1);
 }
 
-extern "C" int mdi_knn(const float* pts, int64_t n, int k, int exclude_self, void* workspace, int32_t* idx,
-                       float* dist, float* kdist, void* stream) {
+namespace mdi {
+// rank boundaries of a query split: bounds[r] = first sorted position of the first cell that starts
+// at or after r * ceil(n / world).  Cell-aligned, because the order of the points INSIDE a cell comes
+// from atomics and differs from rank to rank: whole cells keep the ranks' query sets a partition.
+__global__ void knn_split_kernel(const int32_t* __restrict__ start, int64_t n, int world, int64_t* __restrict__ bounds) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r > world) return;
+  if (r == 0) { bounds[0] = 0; return; }
+  if (r == world) { bounds[world] = n; return; }
+  const int64_t per = (n + world - 1) / world;
+  const int64_t want = (int64_t)r * per;
+  int lo = 0, hi = kCells;   // smallest c with start[c] >= want (start[kCells] = n)
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if ((int64_t)start[mid] >= want) hi = mid; else lo = mid + 1;
+  }
+  bounds[r] = start[lo];
+}
+
+}  // namespace mdi
+
+static int knn_check(const float* pts, int64_t n, void* workspace, const char* who) {
+  MDI_REQUIRE(n >= 0 && n < (1LL << 31) - 2048, "%s: n out of range", who);
+  MDI_REQUIRE(n == 0 || (pts && workspace), "%s: null pointer", who);
+  return MDI_OK;
+}
+
+// grid build: bounding cube, Morton cell of every point, counting sort into `sorted`
+extern "C" int mdi_knn_build(const float* pts, int64_t n, void* workspace, void* stream) {
   using namespace mdi;
   cudaStream_t st = (cudaStream_t)stream;
-  MDI_REQUIRE(n >= 0 && n < (1LL << 31) - 2048, "mdi_knn: n out of range");
-  MDI_REQUIRE(k >= 1 && k <= kKnnMaxK, "mdi_knn: k must be in 1..%d", kKnnMaxK);
+  if (int rc = knn_check(pts, n, workspace, "mdi_knn_build")) return rc;
   if (n == 0) return MDI_OK;
-  // sklearn: "Expected n_neighbors <= n_samples_fit" (the sample itself does not count when excluded)
-  MDI_REQUIRE((int64_t)k + (exclude_self ? 1 : 0) <= n, "mdi_knn: Expected n_neighbors <= n_samples_fit, but "
-              "n_neighbors = %d, n_samples_fit = %lld", k + (exclude_self ? 1 : 0), (long long)n);
-  MDI_REQUIRE(pts && workspace && idx, "mdi_knn: null pointer");
   KnnWs w;
   knn_carve(&w, (char*)workspace, n);
   const unsigned grid_n = (unsigned)((n + 255) / 256);
-  MDI_CUDA(cudaMemsetAsync(w.start, 0, ((size_t)kCells + 1) * 4, st), "mdi_knn");
+  MDI_CUDA(cudaMemsetAsync(w.start, 0, ((size_t)kCells + 1) * 4, st), "mdi_knn_build");
   prof_mark("knn_bbox_kernel", st);
   knn_bbox_init_kernel<<<1, 32, 0, st>>>(w.keys);
   knn_bbox_kernel<<<kSMs * 8, 256, 0, st>>>(pts, n, w.keys);
@@ -349,11 +377,57 @@ extern "C" int mdi_knn(const float* pts, int64_t n, int k, int exclude_self, voi
   knn_scan_add_kernel<<<kCells / 1024, 1024, 0, st>>>(w.start, w.blocksum, w.cursor);
   prof_mark("knn_scatter_kernel", st);
   knn_scatter_kernel<<<grid_n, 256, 0, st>>>(pts, n, w.cell_of, w.cursor, w.sorted);
-  prof_mark("knn_query_kernel", st);
-  knn_query_kernel<<<(unsigned)((n + kKnnThreads - 1) / kKnnThreads), kKnnThreads, 0, st>>>(
-      w.sorted, w.start, n, w.grid, k, exclude_self, idx, dist, kdist);
-  MDI_CHECK_LAUNCH("mdi_knn");
+  MDI_CHECK_LAUNCH("mdi_knn_build");
   return MDI_OK;
+}
+
+extern "C" int mdi_knn_split(void* workspace, int64_t n, int world, int64_t* bounds, void* stream) {
+  using namespace mdi;
+  MDI_REQUIRE(n >= 0 && world >= 1 && world <= 1024 && bounds, "mdi_knn_split: bad argument");
+  if (n == 0) {
+    MDI_CUDA(cudaMemsetAsync(bounds, 0, sizeof(int64_t) * ((size_t)world + 1), (cudaStream_t)stream), "mdi_knn_split");
+    return MDI_OK;
+  }
+  MDI_REQUIRE(workspace, "mdi_knn_split: null workspace");
+  KnnWs w;
+  knn_carve(&w, (char*)workspace, n);
+  prof_mark("knn_split_kernel", (cudaStream_t)stream);
+  knn_split_kernel<<<(world + 1 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w.start, n, world, bounds);
+  MDI_CHECK_LAUNCH("mdi_knn_split");
+  return MDI_OK;
+}
+
+// queries at sorted positions q_begin .. q_end - 1 against the grid built by mdi_knn_build
+extern "C" int mdi_knn_query(void* workspace, int64_t n, int k, int exclude_self, int64_t q_begin, int64_t q_end,
+                             int32_t* self_idx, int32_t* idx, float* dist, float* kdist, void* stream) {
+  using namespace mdi;
+  MDI_REQUIRE(n >= 0 && n < (1LL << 31) - 2048, "mdi_knn_query: n out of range");
+  MDI_REQUIRE(k >= 1 && k <= kKnnMaxK, "mdi_knn: k must be in 1..%d", kKnnMaxK);
+  MDI_REQUIRE(q_begin >= 0 && q_begin <= q_end && q_end <= n, "mdi_knn_query: query range %lld..%lld outside 0..%lld",
+              (long long)q_begin, (long long)q_end, (long long)n);
+  if (n == 0 || q_end == q_begin) return MDI_OK;
+  // sklearn: "Expected n_neighbors <= n_samples_fit" (the sample itself does not count when excluded)
+  MDI_REQUIRE((int64_t)k + (exclude_self ? 1 : 0) <= n, "mdi_knn: Expected n_neighbors <= n_samples_fit, but "
+              "n_neighbors = %d, n_samples_fit = %lld", k + (exclude_self ? 1 : 0), (long long)n);
+  MDI_REQUIRE(workspace && idx, "mdi_knn_query: null pointer");
+  KnnWs w;
+  knn_carve(&w, (char*)workspace, n);
+  prof_mark("knn_query_kernel", (cudaStream_t)stream);
+  knn_query_kernel<<<(unsigned)((q_end - q_begin + kKnnThreads - 1) / kKnnThreads), kKnnThreads, 0, (cudaStream_t)stream>>>(
+      w.sorted, w.start, n, w.grid, k, exclude_self, idx, dist, kdist, q_begin, q_end, self_idx);
+  MDI_CHECK_LAUNCH("mdi_knn_query");
+  return MDI_OK;
+}
+
+extern "C" int mdi_knn(const float* pts, int64_t n, int k, int exclude_self, void* workspace, int32_t* idx,
+                       float* dist, float* kdist, void* stream) {
+  MDI_REQUIRE(k >= 1 && k <= mdi::kKnnMaxK, "mdi_knn: k must be in 1..%d", mdi::kKnnMaxK);
+  if (n == 0) return MDI_OK;
+  MDI_REQUIRE(n < 0 || (int64_t)k + (exclude_self ? 1 : 0) <= n, "mdi_knn: Expected n_neighbors <= n_samples_fit, but "
+              "n_neighbors = %d, n_samples_fit = %lld", k + (exclude_self ? 1 : 0), (long long)n);
+  MDI_REQUIRE(idx, "mdi_knn: null pointer");
+  if (int rc = mdi_knn_build(pts, n, workspace, stream)) return rc;
+  return mdi_knn_query(workspace, n, k, exclude_self, 0, n, nullptr, idx, dist, kdist, stream);
 }
 
 extern "C" int mdi_lof(int64_t n, int k, const int32_t* idx, const float* dist, const float* kdist, float* lrd,
@@ -367,7 +441,36 @@ extern "C" int mdi_lof(int64_t n, int k, const int32_t* idx, const float* dist, 
   prof_mark("lof_lrd_kernel", st);
   lof_lrd_kernel<<<grid, kKnnThreads, 0, st>>>(n, k, idx, dist, kdist, lrd);
   prof_mark("lof_score_kernel", st);
-  lof_score_kernel<<<grid, kKnnThreads, 0, st>>>(n, k, idx, lrd, lof, outlier);
+  lof_score_kernel<<<grid, kKnnThreads, 0, st>>>(n, k, idx, lrd, lrd, lof, outlier);
   MDI_CHECK_LAUNCH("mdi_lof");
+  return MDI_OK;
+}
+
+// The two LOF passes separately, for a query split over ranks: rows are this rank's m
+// queries (compact rows of mdi_knn_queries), neighbours are addressed by original index into the
+// FULL per-point arrays that the caller gathers between the passes.
+extern "C" int mdi_lof_lrd(int64_t m, int k, const int32_t* idx, const float* dist, const float* kdist_full,
+                           float* lrd_rows, void* stream) {
+  using namespace mdi;
+  MDI_REQUIRE(m >= 0 && k >= 1 && k <= kKnnMaxK, "mdi_lof_lrd: bad size");
+  if (m == 0) return MDI_OK;
+  MDI_REQUIRE(idx && dist && kdist_full && lrd_rows, "mdi_lof_lrd: null pointer");
+  prof_mark("lof_lrd_kernel", (cudaStream_t)stream);
+  lof_lrd_kernel<<<(unsigned)((m + kKnnThreads - 1) / kKnnThreads), kKnnThreads, 0, (cudaStream_t)stream>>>(
+      m, k, idx, dist, kdist_full, lrd_rows);
+  MDI_CHECK_LAUNCH("mdi_lof_lrd");
+  return MDI_OK;
+}
+
+extern "C" int mdi_lof_score(int64_t m, int k, const int32_t* idx, const float* lrd_full, const float* lrd_rows,
+                             float* lof, uint8_t* outlier, void* stream) {
+  using namespace mdi;
+  MDI_REQUIRE(m >= 0 && k >= 1 && k <= kKnnMaxK, "mdi_lof_score: bad size");
+  if (m == 0) return MDI_OK;
+  MDI_REQUIRE(idx && lrd_full && lrd_rows && outlier, "mdi_lof_score: null pointer");
+  prof_mark("lof_score_kernel", (cudaStream_t)stream);
+  lof_score_kernel<<<(unsigned)((m + kKnnThreads - 1) / kKnnThreads), kKnnThreads, 0, (cudaStream_t)stream>>>(
+      m, k, idx, lrd_full, lrd_rows, lof, outlier);
+  MDI_CHECK_LAUNCH("mdi_lof_score");
   return MDI_OK;
 }

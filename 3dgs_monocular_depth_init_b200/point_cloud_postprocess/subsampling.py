@@ -22,8 +22,11 @@ def _stream() -> int:
 
 def subsample_pointcloud_device(points: torch.Tensor, rgbs: torch.Tensor, intrinsic_matrices: torch.Tensor,
                                 proj_matrices: torch.Tensor, image_sizes: torch.Tensor, params,
-                                max_levels: int = 0):
-    """Device tensors in, device tensors out: (pts[N',3], rgbs[N',3], extents[N])."""
+                                max_levels: int = 0, group=None):
+    """Device tensors in, device tensors out: (pts[N',3], rgbs[N',3], extents[N]).
+    `group` (torch.distributed group whose ranks all hold this same cloud): the O(N x cameras) extent
+    pass is split over the ranks; the k-d merge itself depends on the global order and runs on every
+    rank redundantly ("replicas only")."""
     lib = L.load()
     if points.ndim != 2 or points.shape[1] != 3:
         raise ValueError("Input points array must have shape (N, 3)")
@@ -46,9 +49,24 @@ def subsample_pointcloud_device(points: torch.Tensor, rgbs: torch.Tensor, intrin
     sizes = image_sizes.to(device=dev, dtype=torch.int32).contiguous()
     n = pts.shape[0]
     with torch.cuda.device(dev):
-        ext = torch.empty(n, dtype=torch.float32, device=dev)
-        L.check(lib.mdi_min_extents(L.ptr(pts), n, L.ptr(K), L.ptr(P), L.ptr(sizes), n_cams, L.ptr(ext), _stream()),
-                "mdi_min_extents")
+        if group is not None:
+            # a13 is independent per point: every rank computes the extents of its block of the
+            # (replicated) cloud and the 4-byte results are all-gathered
+            import torch.distributed as dist
+            world, rank = dist.get_world_size(group), dist.get_rank(group)
+            per = -(-n // world)
+            a, b = min(rank * per, n), min((rank + 1) * per, n)
+            part = torch.zeros(per, dtype=torch.float32, device=dev)
+            if b > a:
+                L.check(lib.mdi_min_extents(pts.data_ptr() + 12 * a, b - a, L.ptr(K), L.ptr(P), L.ptr(sizes), n_cams,
+                                            L.ptr(part), _stream()), "mdi_min_extents")
+            full = torch.empty(world * per, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(full, part, group=group)
+            ext = full[:n].contiguous()
+        else:
+            ext = torch.empty(n, dtype=torch.float32, device=dev)
+            L.check(lib.mdi_min_extents(L.ptr(pts), n, L.ptr(K), L.ptr(P), L.ptr(sizes), n_cams, L.ptr(ext), _stream()),
+                    "mdi_min_extents")
         ws = torch.empty(int(lib.mdi_merge_workspace_bytes(n)), dtype=torch.uint8, device=dev)
         out_p = torch.empty((n, 3), dtype=torch.float32, device=dev)
         out_c = torch.empty((n, 3), dtype=torch.float32, device=dev)

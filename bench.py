@@ -466,6 +466,163 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_postprocess(args):
+    """C5 post-processing leg (a12-a14): the hot path runs once per rank and the exchange leaves the
+    whole scene cloud on every GPU; then K timed steps of LOF outlier removal (kNN k = 40 + LOF, queries
+    split over the ranks) or of the native merge subsampling (extents split over the ranks, the k-d merge
+    on every rank).  value = points of the scene cloud per second."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dmod = mod("distributed")
+    dmod.bind_process_to_gpu_node(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L, mdi, knn = mod("_lib"), mod("monocular_depth_init"), mod("knn")
+    sub, pcfg = mod("point_cloud_postprocess.subsampling"), mod("point_cloud_postprocess.config")
+    V_total, H, W, n_sfm, aligner, subsample = WORKLOADS[args.workload]
+    V = args.views or max(1, V_total // 8)          # C5: 2000 views on 8 GPUs = 250 per GPU
+    cfg = make_config(aligner, subsample)
+    sc = mod("synthetic").make_scene(n_views=V, H=H, W=W, n_sfm=n_sfm, seed=20261104 + 7919 * rank, device=str(dev),
+                                     low_conf_every=50)
+    torch.manual_seed(1234)
+    exchange = dmod.CloudExchange(dev, capacity_rows=1 << 22) if world > 1 else None
+    res = mdi.points_from_views(cfg, sc.depth, sc.mask, sc.image, sc.K, sc.c2w, sc.names, sc.points, sc.point_indices,
+                                dev, L.IMAGE_U8, exchange=exchange)
+    pts, rgb = res.xyz.clone(), res.rgb.clone()
+    ok = (res.status == 0)
+    Kd, Pd = sc.K.to(dev)[ok], res.P[ok]
+    sizes = torch.tensor([[W, H]], dtype=torch.int32, device=dev).repeat(int(ok.sum()), 1)
+    if world > 1:   # cameras of all ranks (a13 needs every camera): padded all-gather, rank order = view order
+        def gather_cams(t):
+            n = torch.tensor([t.shape[0]], device=dev)
+            ns = [torch.zeros_like(n) for _ in range(world)]
+            dist.all_gather(ns, n)
+            m = int(max(x.item() for x in ns))
+            pad = torch.zeros((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+            pad[: t.shape[0]] = t
+            outs = [torch.empty_like(pad) for _ in range(world)]
+            dist.all_gather(outs, pad)
+            return torch.cat([o[: int(k.item())] for o, k in zip(outs, ns)])
+        Kd, Pd, sizes = gather_cams(Kd), gather_cams(Pd), gather_cams(sizes)
+    del sc, res, exchange
+    torch.cuda.empty_cache()
+    n = int(pts.shape[0])
+    group = dist.group.WORLD if world > 1 else None
+    params = pcfg.PointCloudSubsamplingParams()
+
+    def step():
+        if args.postprocess == "lof":
+            out, _ = (knn.local_outlier_factor_sharded(pts, 40, group) if group is not None
+                      else knn.local_outlier_factor(pts, 40))
+            keep = ~out
+            return pts[keep], rgb[keep]
+        p, c, _ = sub.subsample_pointcloud_device(pts, rgb, Kd, Pd, sizes, params, group=group)
+        return p, c
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n_warm = max(args.warmup, 1)
+    for _ in range(n_warm):
+        out = step()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    lib = L.load()
+    lib.mdi_profile_enable(1)
+    L.profile_collect()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        out = step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ktimes = L.profile_collect()
+    lib.mdi_profile_enable(0)
+    # every rank must end with the same cloud (bit-identity itself: tests/postprocess_check.py)
+    same = None
+    if world > 1:
+        flag = torch.tensor([int(out[0].shape[0])], device=dev)
+        lo, hi = flag.clone(), flag.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool(int(lo) == int(hi))
+    clk = clocks.stop() if rank == 0 else None
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_step = float(ms) / args.steps
+    # ---- CPU beside it: sklearn (LOF) / the reference's own compiled module (merge) on a bounded subset ----
+    pts_h, rgb_h = pts.cpu().numpy(), rgb.cpu().numpy()
+    if args.postprocess == "lof":
+        from sklearn.neighbors import LocalOutlierFactor
+        m = min(n, args.cpu_points)
+        t0 = time.perf_counter()
+        LocalOutlierFactor(n_neighbors=40, n_jobs=-1).fit_predict(pts_h[:m])
+        dt = time.perf_counter() - t0
+        cpu = {"value": m / dt / 1e6, "unit": "Mpts/s", "cores": os.cpu_count(), "kind": "reference",
+               "sample": f"sklearn LocalOutlierFactor(n_neighbors=40, n_jobs=-1) -- the reference's call, postprocess.py:20 -- "
+                         f"on the first {m} of {n} points"}
+    else:
+        sys.path.insert(0, str(ROOT / "oracle"))
+        m = min(n, args.cpu_points)
+        cams = min(int(Kd.shape[0]), 200)
+        Kh, Ph, sh = Kd[:cams].cpu().numpy(), Pd[:cams].cpu().numpy(), sizes[:cams].cpu().numpy()
+        kind = "port"
+        try:
+            import build_ref_native
+            ref = build_ref_native.load() if build_ref_native.built() else None
+        except Exception:  # noqa: BLE001
+            ref = None
+        t0 = time.perf_counter()
+        if ref is not None:
+            kind = "reference"
+            from types import SimpleNamespace
+            cwd = os.getcwd(); os.chdir("/tmp")
+            devnull = os.open(os.devnull, os.O_WRONLY); saved = os.dup(1); os.dup2(devnull, 1)
+            try:
+                ref.subsample_pointcloud(pts_h[:m], rgb_h[:m], list(Kh), list(Ph), sh,
+                                         SimpleNamespace(max_bbox_aspect_ratio=1.1, min_extent_multiplier=1.0))
+            finally:
+                os.dup2(saved, 1); os.close(devnull); os.close(saved); os.chdir(cwd)
+        else:
+            import native_oracle as NO
+            NO.subsample_pointcloud(pts_h[:m], rgb_h[:m], Kh, Ph, sh)
+        dt = time.perf_counter() - t0
+        cpu = {"value": m / dt / 1e6, "unit": "Mpts/s", "cores": 1, "kind": kind,
+               "sample": f"{'the reference module compiled into oracle/_ref' if kind == 'reference' else 'C restatement'} "
+                         f"(single-threaded like the original) on the first {m} of {n} points, {cams} of {int(Kd.shape[0])} cameras"}
+    print(json.dumps({
+        "metric": f"postprocess Mpts/sec ({args.postprocess}: " + ("kNN k=40 + LOF + filter" if args.postprocess == "lof" else "min extents + k-d merge") + ")",
+        "value": n / (ms_step * 1e-3) / 1e6, "unit": "Mpts/s", "n_gpus": world, "steps": args.steps, "warmup": n_warm,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": args.workload, "postprocess": args.postprocess, "views_per_gpu": V, "H": H, "W": W,
+                   "cloud_points": n, "cameras": int(Kd.shape[0]),
+                   "split": "kNN / LOF queries and extents split over the ranks, 4 + 4 + 8 B per point exchanged; "
+                            "k-d merge on every rank (replicas only)"},
+        "kept_points": int(out[0].shape[0]), "same_result_on_every_rank": same,
+        "kernels": {k: {"ms_per_call": round(v["ms"] / v["calls"], 4), "calls_per_step": v["calls"] / args.steps}
+                    for k, v in ktimes.items()},
+        "cpu_baseline": cpu, "clocks": clk,
+    }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -475,13 +632,20 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
     ap.add_argument("--cpu-views", type=int, default=12, help="views in the bounded CPU sample")
     ap.add_argument("--views", type=int, default=0, help="override views per GPU (profiling runs only)")
+    ap.add_argument("--postprocess", default=None, choices=["lof", "merge"],
+                    help="C5 post-processing leg instead of the hot path (default workload: c5_large_...)")
+    ap.add_argument("--cpu-points", type=int, default=1000000, help="points in the bounded CPU sample of --postprocess")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: every rank owns the workload's views; strong: the workload's views are sharded over the ranks")
     ap.add_argument("--profile-mode", action="store_true",
                     help="short run for ncu: warm-up as given, no e2e / CPU legs (not a bench value)")
     args = ap.parse_args()
+    if args.postprocess and args.workload == DEFAULT_WORKLOAD:
+        args.workload = "c5_large_2000x1600x1200_ransac_adaptive"
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.postprocess:
+        run_postprocess(args)
     else:
         run_ours(args)
 

@@ -414,6 +414,29 @@ int mdi_interp_scale_map(const double* transform, const int32_t* simplices, cons
                          const float* base, const float* scale_shift, void* workspace, float* out,
                          void* stream);
 
+/*
+ * Query split of a12 / a13 over ranks ("stages that do not shard by view"): every rank
+ * holds the whole cloud (after the exchange) and builds the same grid (mdi_knn_build), but answers
+ * only the queries at SORTED positions q_begin .. q_end - 1 (mdi_knn_query; Morton order of the grid,
+ * so a rank's queries are spatially coherent).  mdi_knn_split writes the rank boundaries bounds
+ * [world + 1] (device int64): cell-aligned cuts near r * ceil(n / world) -- whole cells, because the
+ * order of the points inside a cell differs between ranks.  With self_idx != NULL results go to
+ * compact rows 0 .. q_end - q_begin - 1 and self_idx int32 [rows] receives the original index of
+ * each row (NULL: rows are the original indices, as mdi_knn).  The caller gathers the 4-byte
+ * k-distances, then the 4-byte lrd, then the flags of all ranks (mdi_lof_lrd / mdi_lof_score take the
+ * gathered FULL arrays for the neighbours and the rank's own rows for the queries).  Every query's
+ * answer is independent of the split, so the result is bit-identical for any number of ranks.
+ * mdi_min_extents needs no variant: pass the rank's slice of pts.  mdi_knn = build + query(0, n).
+ */
+int mdi_knn_build(const float* pts, int64_t n, void* workspace, void* stream);
+int mdi_knn_split(void* workspace, int64_t n, int world, int64_t* bounds, void* stream);
+int mdi_knn_query(void* workspace, int64_t n, int k, int exclude_self, int64_t q_begin, int64_t q_end,
+                  int32_t* self_idx, int32_t* idx, float* dist, float* kdist, void* stream);
+int mdi_lof_lrd(int64_t m, int k, const int32_t* idx, const float* dist, const float* kdist_full,
+                float* lrd_rows, void* stream);
+int mdi_lof_score(int64_t m, int k, const int32_t* idx, const float* lrd_full, const float* lrd_rows,
+                  float* lof, uint8_t* outlier, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
