@@ -19,6 +19,7 @@ ABI_VERSION = 3
 TILE_PX = 4096
 TILE_WORDS = TILE_PX // 32
 PATCH_STRIDE = 2048
+INTERP_STATIC_MAX_PX = 2 * 1024 * 1024
 FACTOR_TABLE_STRIDE = 40
 STATUS_OK, STATUS_LOW_CONFIDENCE, STATUS_EMPTY_STATS, STATUS_STATS_RETRY = 0, 1, 2, 4
 STATS_EXACT, STATS_RETRY_FLAGGED = 64, 128
@@ -102,6 +103,7 @@ _SIGNATURES = {
     "mdi_lof_score": (_INT, [_I64, _INT, _P, _P, _P, _P, _P, _P]),
     "mdi_interp_workspace_bytes": (_I64, [_INT, _INT]),
     "mdi_interp_scale_map": (_INT, [_P, _P, _P, _P, _INT, C.c_double, _INT, _INT, _P, _P, _P, _P, _P]),
+    "mdi_interp_scale_map_static": (_INT, [_P, _P, _P, _P, _INT, C.c_double, _INT, _INT, _P, _P, _P, _P]),
     "mdi_merge_workspace_bytes": (_I64, [_I64]),
     "mdi_merge_subsample": (_INT, [_P, _P, _P, _I64, C.c_float, C.c_float, _INT, _P, _P, _P,
                                    C.POINTER(C.c_int64), C.POINTER(C.c_int32), _P]),

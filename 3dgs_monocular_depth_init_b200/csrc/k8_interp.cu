@@ -16,6 +16,8 @@
 // value up to float64 rounding -- far inside the 1e-5 bar after the cast to float32.
 #include <float.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace mdi {
@@ -122,4 +124,47 @@ extern "C" int mdi_interp_scale_map(const double* transform, const int32_t* simp
                                                                     owner, base, scale_shift, out);
   MDI_CHECK_LAUNCH("mdi_interp_scale_map");
   return MDI_OK;
+}
+
+// ---- allocation-free variant --------------------------------------------------------------------
+// No counterpart in the reference: added for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+// per-pixel owner map lives in a file-scope device array instead of a caller-provided workspace;
+// every GPU that loads the library holds its MDI_INTERP_STATIC_MAX_PX * 4 bytes until exit.
+// In host code `g_interp_owner_scratch` is only a stand-in for the symbol, never a device address:
+// the address is resolved once per device with cudaGetSymbolAddress and passed to the kernels.
+static __device__ __align__(256) int32_t g_interp_owner_scratch[MDI_INTERP_STATIC_MAX_PX];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+int32_t* g_scratch_addr[kMaxDevices] = {};
+}  // namespace
+
+extern "C" int mdi_interp_scale_map_static(const double* transform, const int32_t* simplices,
+                                           const double* points, const double* values, int n_tri,
+                                           double fill_value, int H, int W, const float* base,
+                                           const float* scale_shift, float* out, void* stream) {
+  MDI_REQUIRE(H > 0 && W > 0, "mdi_interp_scale_map_static: bad size");
+  MDI_REQUIRE((int64_t)H * W <= (int64_t)MDI_INTERP_STATIC_MAX_PX,
+              "mdi_interp_scale_map_static: %d x %d = %lld pixels exceed the static scratch of %d pixels; "
+              "use mdi_interp_scale_map with a caller-provided workspace", H, W, (long long)H * W,
+              MDI_INTERP_STATIC_MAX_PX);
+  int dev = -1;
+  MDI_CUDA(cudaGetDevice(&dev), "mdi_interp_scale_map_static");
+  MDI_REQUIRE(dev >= 0 && dev < kMaxDevices, "mdi_interp_scale_map_static: device ordinal %d out of range", dev);
+  int32_t* scratch;
+  {
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_addr[dev]) {   // once per device, with that device current
+      void* p = nullptr;
+      MDI_CUDA(cudaGetSymbolAddress(&p, g_interp_owner_scratch), "mdi_interp_scale_map_static symbol address");
+      g_scratch_addr[dev] = static_cast<int32_t*>(p);
+    }
+    scratch = g_scratch_addr[dev];
+  }
+  // the existing entry point with the static array as its workspace: it refills the owner map
+  // (memset + kernels, no allocation) on every call, so stale contents of earlier calls never leak
+  return mdi_interp_scale_map(transform, simplices, points, values, n_tri, fill_value, H, W, base, scale_shift,
+                              scratch, out, stream);
 }

@@ -415,6 +415,22 @@ int mdi_interp_scale_map(const double* transform, const int32_t* simplices, cons
                          void* stream);
 
 /*
+ * mdi_interp_scale_map without any allocation by caller or library.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * mdi_interp_scale_map minus `workspace`: the per-pixel owner map lives in a static device array of
+ * MDI_INTERP_STATIC_MAX_PX int32 (8 MiB, held by every GPU that loads the library until exit).
+ * H * W beyond that limit is rejected with MDI_EINVAL.  The call itself uses no cudaMalloc / cudaFree
+ * or allocating routine.  ALL calls on a device share the one array: it is refilled at the start of
+ * every call (nothing of an earlier call survives), and calls that overlap on the GPU (different
+ * streams, or threads) race on it -- serialise them or use mdi_interp_scale_map.
+ */
+#define MDI_INTERP_STATIC_MAX_PX (2 * 1024 * 1024)
+int mdi_interp_scale_map_static(const double* transform, const int32_t* simplices, const double* points,
+                                const double* values, int n_tri, double fill_value, int H, int W,
+                                const float* base, const float* scale_shift, float* out, void* stream);
+
+/*
  * Query split of a12 / a13 over ranks ("stages that do not shard by view"): every rank
  * holds the whole cloud (after the exchange) and builds the same grid (mdi_knn_build), but answers
  * only the queries at SORTED positions q_begin .. q_end - 1 (mdi_knn_query; Morton order of the grid,
