@@ -24,19 +24,34 @@
 namespace mdi {
 
 constexpr int kKnnThreads = 128;
-constexpr int kGridBits = 8;                       // 256 cells per axis
-constexpr int kCells = 1 << (3 * kGridBits);       // 16.7 M
+// Grid depth by point count: 256 cells per axis (16.7 M cells) up to kDenseGridPoints points, 512
+// (134 M cells) above -- a C5-sized cloud (5e7 points on surfaces) fills the cells of a 256^3 grid with
+// hundreds of points each, and every leaf is scanned whole.  MDI_KNN_BITS=8|9 overrides.
+constexpr int kMaxGridBits = 9;
+constexpr int64_t kDenseGridPoints = 8 * 1000 * 1000;
+static int grid_bits_for(int64_t n) {
+  static const int forced = [] {
+    const char* e = getenv("MDI_KNN_BITS");
+    const int b = e ? atoi(e) : 0;
+    return (b == 8 || b == 9) ? b : 0;
+  }();
+  return forced ? forced : (n > kDenseGridPoints ? 9 : 8);
+}
+static int64_t grid_cells_for(int64_t n) { return (int64_t)1 << (3 * grid_bits_for(n)); }
 constexpr int kLeafPoints = 24;                    // nodes this small are scanned, not split
 constexpr int kKnnMaxK = 64;
 
-struct KnnGrid { float lo[3]; float size; float inv_cell; float slack; };
+constexpr int kHistBins = 1024;
+struct KnnGrid { float lo[3]; float size; float inv_cell; float slack; int bits; int cells; };
 
 struct KnnWs {
   uint32_t* keys;      // [6] min/max keys of the coordinates
+  float* range;        // [3][6] per-axis (lo x3, hi x3): min/max, then two quantile refinements
+  uint32_t* hist;      // [2][3][kHistBins] coordinate histograms of the two refinements
   KnnGrid* grid;
-  int32_t* start;      // [kCells + 1] first sorted position of each Morton cell
-  int32_t* cursor;     // [kCells] scatter cursors
-  int32_t* blocksum;   // [kCells / 1024 + 1]
+  int32_t* start;      // [cells + 1] first sorted position of each Morton cell
+  int32_t* cursor;     // [cells] scatter cursors
+  int32_t* blocksum;   // [cells / 1024 + 1]
   uint32_t* cell_of;   // [n] Morton cell of every input point
   float4* sorted;      // [n] (x, y, z, original index bits) in Morton order
 };
@@ -48,27 +63,33 @@ static int64_t knn_carve(KnnWs* w, char* base, int64_t n) {
   auto take = [&](int64_t bytes) { char* p = base ? base + off : nullptr; off += knn_align(bytes); return p; };
   KnnWs t;
   t.keys = (uint32_t*)take(64);
+  t.range = (float*)take(3 * 6 * 4);
+  t.hist = (uint32_t*)take(2 * 3 * kHistBins * 4);
   t.grid = (KnnGrid*)take(sizeof(KnnGrid));
-  t.start = (int32_t*)take(((int64_t)kCells + 1) * 4);
-  t.cursor = (int32_t*)take((int64_t)kCells * 4);
-  t.blocksum = (int32_t*)take((kCells / 1024 + 1) * 4);
+  const int64_t cells = grid_cells_for(n);
+  t.start = (int32_t*)take((cells + 1) * 4);
+  t.cursor = (int32_t*)take(cells * 4);
+  t.blocksum = (int32_t*)take((cells / 1024 + 1) * 4);
   t.cell_of = (uint32_t*)take(n * 4);
   t.sorted = (float4*)take(n * 16);
   if (w) *w = t;
   return off;
 }
 
-__device__ __forceinline__ uint32_t spread3(uint32_t v) {  // 8 bits -> every third bit
-  v = (v | (v << 8)) & 0x0000F00Fu;
-  v = (v | (v << 4)) & 0x000C30C3u;
-  v = (v | (v << 2)) & 0x00249249u;
+__device__ __forceinline__ uint32_t spread3(uint32_t v) {  // 10 bits -> every third bit
+  v &= 0x000003FFu;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
   return v;
 }
 __device__ __forceinline__ uint32_t compact3(uint32_t v) {
-  v &= 0x00249249u;
-  v = (v | (v >> 2)) & 0x000C30C3u;
-  v = (v | (v >> 4)) & 0x0000F00Fu;
-  v = (v | (v >> 8)) & 0x000000FFu;
+  v &= 0x09249249u;
+  v = (v | (v >> 2)) & 0x030C30C3u;
+  v = (v | (v >> 4)) & 0x0300F00Fu;
+  v = (v | (v >> 8)) & 0x030000FFu;
+  v = (v | (v >> 16)) & 0x000003FFu;
   return v;
 }
 
@@ -91,22 +112,85 @@ __global__ void __launch_bounds__(256) knn_bbox_kernel(const float* __restrict__
     for (int a = 0; a < 3; ++a) { atomicMin(&keys[a], kmin[a]); atomicMax(&keys[3 + a], kmax[a]); }
 }
 
-__global__ void knn_grid_kernel(const uint32_t* keys, KnnGrid* g) {
+// The grid covers a ROBUST cube, not the bounding cube: a handful of far-away points (a view whose
+// alignment went wild) would otherwise stretch the cube and leave the real cloud in a few cells.
+// Per axis the 0.1 % .. 99.9 % coordinate range is located by two histogram refinements (1024 bins over
+// [min, max], then 1024 bins over the bins picked there); points outside are clamped into the border
+// cells, and the search treats border cells as open-ended, so it stays exact.
+__global__ void knn_range_init_kernel(const uint32_t* __restrict__ keys, float* __restrict__ range) {
+  const int a = threadIdx.x;
+  if (a >= 3) return;
+  float lo = keys[a] == 0xFFFFFFFFu ? 0.f : key_to_float(keys[a]);
+  float hi = keys[3 + a] == 0u ? 0.f : key_to_float(keys[3 + a]);
+  if (!(hi >= lo)) { lo = 0.f; hi = 0.f; }
+  range[a] = lo; range[3 + a] = hi;
+}
+
+__global__ void __launch_bounds__(256)
+knn_hist_kernel(const float* __restrict__ pts, int64_t n, const float* __restrict__ range, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t s_h[3 * kHistBins];
+  for (int i = threadIdx.x; i < 3 * kHistBins; i += blockDim.x) s_h[i] = 0u;
+  __syncthreads();
+  float lo[3], inv[3];
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = range[a];
+    const float w = range[3 + a] - lo[a];
+    inv[a] = (w > 0.f && w <= FLT_MAX) ? (float)kHistBins / w : 0.f;
+  }
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    for (int a = 0; a < 3; ++a) {
+      const float c = pts[3 * i + a];
+      if (c == c && fabsf(c) <= FLT_MAX) {
+        const int b = min(kHistBins - 1, max(0, (int)((c - lo[a]) * inv[a])));
+        atomicAdd(&s_h[a * kHistBins + b], 1u);
+      }
+    }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * kHistBins; i += blockDim.x)
+    if (s_h[i]) atomicAdd(&hist[i], s_h[i]);
+}
+
+// one warp per axis: bins holding the 0.1 % and 99.9 % ranks -> the next, narrower range
+__global__ void knn_hist_pick_kernel(const uint32_t* __restrict__ hist, const float* __restrict__ range,
+                                     float* __restrict__ next) {
+  const int a = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (a >= 3) return;
+  const uint32_t* h = hist + a * kHistBins;
+  uint32_t part = 0;
+  for (int b = lane; b < kHistBins; b += 32) part += h[b];
+  const uint32_t total = __reduce_add_sync(0xffffffffu, part);
+  if (lane != 0) return;
+  const float lo = range[a], hi = range[3 + a];
+  int b_lo = 0, b_hi = kHistBins - 1;
+  if (total > 0) {
+    const uint32_t cut = total / 1000u;   // points allowed outside on each side
+    uint32_t acc = 0;
+    for (b_lo = 0; b_lo < kHistBins - 1; ++b_lo) { acc += h[b_lo]; if (acc > cut) break; }
+    acc = 0;
+    for (b_hi = kHistBins - 1; b_hi > b_lo; --b_hi) { acc += h[b_hi]; if (acc > cut) break; }
+  }
+  const float w = (hi - lo) / (float)kHistBins;
+  const float nlo = lo + (float)b_lo * w, nhi = lo + (float)(b_hi + 1) * w;
+  next[a] = (w > 0.f && nlo >= lo) ? nlo : lo;
+  next[3 + a] = (w > 0.f && nhi <= hi) ? nhi : hi;
+}
+
+__global__ void knn_grid_kernel(const float* __restrict__ range, KnnGrid* g, int bits) {
   float size = 0.f;
   for (int a = 0; a < 3; ++a) {
-    const float lo = keys[a] == 0xFFFFFFFFu ? 0.f : key_to_float(keys[a]);
-    const float hi = keys[3 + a] == 0u ? 0.f : key_to_float(keys[3 + a]);
+    const float lo = range[a], hi = range[3 + a];
     g->lo[a] = lo;
     size = fmaxf(size, hi - lo);
   }
   if (!(size > 0.f) || !(size <= FLT_MAX)) size = 1.f;
   g->size = size;
-  g->inv_cell = (float)(1 << kGridBits) / size;
+  g->bits = bits; g->cells = 1 << (3 * bits);
+  g->inv_cell = (float)(1 << bits) / size;
   g->slack = size * 8e-6f;  // covers the rounding of the cell assignment below
 }
 
 __device__ __forceinline__ uint32_t cell_of_point(const KnnGrid& g, float x, float y, float z) {
-  const int top = (1 << kGridBits) - 1;
+  const int top = (1 << g.bits) - 1;
   const int cx = min(top, max(0, (int)((x - g.lo[0]) * g.inv_cell)));
   const int cy = min(top, max(0, (int)((y - g.lo[1]) * g.inv_cell)));
   const int cz = min(top, max(0, (int)((z - g.lo[2]) * g.inv_cell)));
@@ -133,7 +217,7 @@ __global__ void __launch_bounds__(1024) knn_scan_local_kernel(int32_t* start, in
   start[i] = ex;
   if (threadIdx.x == 0) blocksum[blockIdx.x] = total;
 }
-__global__ void __launch_bounds__(1024) knn_scan_top_kernel(int32_t* blocksum, int n_blocks, int32_t* start) {
+__global__ void __launch_bounds__(1024) knn_scan_top_kernel(int32_t* blocksum, int n_blocks, int32_t* start, int cells) {
   __shared__ int s_scan[33];
   int carry = 0;
   for (int base = 0; base < n_blocks; base += 1024) {
@@ -145,7 +229,7 @@ __global__ void __launch_bounds__(1024) knn_scan_top_kernel(int32_t* blocksum, i
     carry += total;
     __syncthreads();
   }
-  if (threadIdx.x == 0) start[kCells] = carry;
+  if (threadIdx.x == 0) start[cells] = carry;
 }
 __global__ void __launch_bounds__(1024)
 knn_scan_add_kernel(int32_t* start, const int32_t* __restrict__ blocksum, int32_t* cursor) {
@@ -217,26 +301,30 @@ knn_query_kernel(const float4* __restrict__ sorted, const int32_t* __restrict__ 
   if (out_self) out_self[row] = self;
   KnnHeap h;
   h.n = 0; h.k = k;
-  uint32_t stk[64];
+  uint32_t stk[7 * kMaxGridBits + 2];   // DFS: a popped node pushes at most 8 children
   int sp = 0;
   stk[sp++] = 0u;  // level 0, prefix 0
   while (sp > 0) {
     const uint32_t ent = stk[--sp];
     const int l = (int)(ent >> 28);
-    const uint32_t m = ent & 0x00FFFFFFu;
-    const int shift = 3 * (kGridBits - l);
+    const uint32_t m = ent & 0x0FFFFFFFu;
+    const int shift = 3 * (g.bits - l);
     const int s = start[m << shift], e = start[(m + 1u) << shift];
     const float cs = g.size / (float)(1 << l);
     const float bx = g.lo[0] + (float)compact3(m) * cs, by = g.lo[1] + (float)compact3(m >> 1) * cs,
                 bz = g.lo[2] + (float)compact3(m >> 2) * cs;
     if (h.n == k) {
-      const float tx = fmaxf(fmaxf(bx - q.x, q.x - (bx + cs)) - g.slack, 0.f);
-      const float ty = fmaxf(fmaxf(by - q.y, q.y - (by + cs)) - g.slack, 0.f);
-      const float tz = fmaxf(fmaxf(bz - q.z, q.z - (bz + cs)) - g.slack, 0.f);
+      // distance from the query to the node's box; a node on the border of the grid also holds the
+      // points clamped into it from outside the cube, so its box is open on that side
+      const uint32_t last = (1u << l) - 1u;
+      const uint32_t ux = compact3(m), uy = compact3(m >> 1), uz = compact3(m >> 2);
+      const float tx = fmaxf(fmaxf(ux == 0u ? -INFINITY : bx - q.x, ux == last ? -INFINITY : q.x - (bx + cs)) - g.slack, 0.f);
+      const float ty = fmaxf(fmaxf(uy == 0u ? -INFINITY : by - q.y, uy == last ? -INFINITY : q.y - (by + cs)) - g.slack, 0.f);
+      const float tz = fmaxf(fmaxf(uz == 0u ? -INFINITY : bz - q.z, uz == last ? -INFINITY : q.z - (bz + cs)) - g.slack, 0.f);
       const double d2 = (double)(tx * tx + ty * ty + tz * tz) * (1.0 - 1e-6);
       if (d2 > h.d[0]) continue;
     }
-    if (l == kGridBits || e - s <= kLeafPoints) {
+    if (l == g.bits || e - s <= kLeafPoints) {
       for (int j = s; j < e; ++j) {
         const float4 c = sorted[j];
         const int ci = __float_as_int(c.w);
@@ -332,14 +420,15 @@ namespace mdi {
 // rank boundaries of a query split: bounds[r] = first sorted position of the first cell that starts
 // at or after r * ceil(n / world).  Cell-aligned, because the order of the points INSIDE a cell comes
 // from atomics and differs from rank to rank: whole cells keep the ranks' query sets a partition.
-__global__ void knn_split_kernel(const int32_t* __restrict__ start, int64_t n, int world, int64_t* __restrict__ bounds) {
+__global__ void knn_split_kernel(const int32_t* __restrict__ start, int64_t n, int world, int64_t* __restrict__ bounds,
+                                 int cells) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r > world) return;
   if (r == 0) { bounds[0] = 0; return; }
   if (r == world) { bounds[world] = n; return; }
   const int64_t per = (n + world - 1) / world;
   const int64_t want = (int64_t)r * per;
-  int lo = 0, hi = kCells;   // smallest c with start[c] >= want (start[kCells] = n)
+  int lo = 0, hi = cells;    // smallest c with start[c] >= want (start[cells] = n)
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
     if ((int64_t)start[mid] >= want) hi = mid; else lo = mid + 1;
@@ -364,17 +453,25 @@ extern "C" int mdi_knn_build(const float* pts, int64_t n, void* workspace, void*
   KnnWs w;
   knn_carve(&w, (char*)workspace, n);
   const unsigned grid_n = (unsigned)((n + 255) / 256);
-  MDI_CUDA(cudaMemsetAsync(w.start, 0, ((size_t)kCells + 1) * 4, st), "mdi_knn_build");
+  const int bits = grid_bits_for(n);
+  const int cells = 1 << (3 * bits);
+  MDI_CUDA(cudaMemsetAsync(w.start, 0, ((size_t)cells + 1) * 4, st), "mdi_knn_build");
   prof_mark("knn_bbox_kernel", st);
   knn_bbox_init_kernel<<<1, 32, 0, st>>>(w.keys);
   knn_bbox_kernel<<<kSMs * 8, 256, 0, st>>>(pts, n, w.keys);
-  knn_grid_kernel<<<1, 1, 0, st>>>(w.keys, w.grid);
+  MDI_CUDA(cudaMemsetAsync(w.hist, 0, sizeof(uint32_t) * 2 * 3 * kHistBins, st), "mdi_knn_build");
+  knn_range_init_kernel<<<1, 32, 0, st>>>(w.keys, w.range);
+  for (int r = 0; r < 2; ++r) {
+    knn_hist_kernel<<<kSMs * 4, 256, 0, st>>>(pts, n, w.range + 6 * r, w.hist + r * 3 * kHistBins);
+    knn_hist_pick_kernel<<<1, 96, 0, st>>>(w.hist + r * 3 * kHistBins, w.range + 6 * r, w.range + 6 * (r + 1));
+  }
+  knn_grid_kernel<<<1, 1, 0, st>>>(w.range + 12, w.grid, bits);
   prof_mark("knn_count_kernel", st);
   knn_count_kernel<<<grid_n, 256, 0, st>>>(pts, n, w.grid, w.cell_of, w.start);
   prof_mark("knn_scan_kernels", st);
-  knn_scan_local_kernel<<<kCells / 1024, 1024, 0, st>>>(w.start, w.blocksum);
-  knn_scan_top_kernel<<<1, 1024, 0, st>>>(w.blocksum, kCells / 1024, w.start);
-  knn_scan_add_kernel<<<kCells / 1024, 1024, 0, st>>>(w.start, w.blocksum, w.cursor);
+  knn_scan_local_kernel<<<cells / 1024, 1024, 0, st>>>(w.start, w.blocksum);
+  knn_scan_top_kernel<<<1, 1024, 0, st>>>(w.blocksum, cells / 1024, w.start, cells);
+  knn_scan_add_kernel<<<cells / 1024, 1024, 0, st>>>(w.start, w.blocksum, w.cursor);
   prof_mark("knn_scatter_kernel", st);
   knn_scatter_kernel<<<grid_n, 256, 0, st>>>(pts, n, w.cell_of, w.cursor, w.sorted);
   MDI_CHECK_LAUNCH("mdi_knn_build");
@@ -392,7 +489,8 @@ extern "C" int mdi_knn_split(void* workspace, int64_t n, int world, int64_t* bou
   KnnWs w;
   knn_carve(&w, (char*)workspace, n);
   prof_mark("knn_split_kernel", (cudaStream_t)stream);
-  knn_split_kernel<<<(world + 1 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w.start, n, world, bounds);
+  knn_split_kernel<<<(world + 1 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w.start, n, world, bounds,
+                                                                              (int)grid_cells_for(n));
   MDI_CHECK_LAUNCH("mdi_knn_split");
   return MDI_OK;
 }

@@ -408,7 +408,9 @@ def run_ours(args):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     n_slots = sum(len(sc.point_indices[n]) for n in names)
     adaptive = subsample == "adaptive"
-    hbm_calls = {k: v for k, v in ktimes.items() if algorithmic_bytes(k, HW, V, n_kept, n_slots, adaptive) > 0}
+    # with the exchange fused in, the emit kernel is bound by NVLink, not HBM: it gets its own roofline below
+    hbm_calls = {k: v for k, v in ktimes.items() if algorithmic_bytes(k, HW, V, n_kept, n_slots, adaptive) > 0
+                 and not (world > 1 and k == "emit_points_kernel")}
     dom = max(hbm_calls, key=lambda k: hbm_calls[k]["ms"]) if hbm_calls else None
     traffic = None   # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu capture
     tpath = ROOT / "profiles" / "ncu_traffic.json"
@@ -427,6 +429,16 @@ def run_ours(args):
         roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": traffic, "peak_source": peak_src,
                 "note": "achieved = algorithmic bytes of one launch / its mean CUDA-event duration inside the (profiled) timed loop"}
+    # N > 1: every GPU receives the other ranks' rows (24 B each) through the emit kernels' peer stores
+    roof_exchange = None
+    if world > 1 and "emit_points_kernel" in ktimes and exchange is not None:
+        per = ktimes["emit_points_kernel"]["ms"] / ktimes["emit_points_kernel"]["calls"]
+        ingress = 24.0 * (n_kept_total - n_kept)
+        ach = ingress / (per * 1e-3) / 1e9
+        roof_exchange = {"bound": "nvlink", "kernel": "emit_points_kernel", "ms": round(per, 4),
+                         "ingress_bytes_per_gpu": int(ingress), "achieved": ach, "peak": 770.0, "unit": "GB/s",
+                         "frac": ach / 770.0,
+                         "peak_source": "measured peer copy per direction on this pool (B200_PROFILING.md; nominal 900)"}
     # the a7 statistics group as a whole: ONE algorithmic read of depth + mask over the sum of its kernels
     group = [k for k in ktimes if k.startswith("stats_")]
     roof_group = None
@@ -454,7 +466,7 @@ def run_ours(args):
         "mpts_per_s": (n_kept_total if world > 1 else n_kept) / (ms_step * 1e-3) / 1e6,
         "step_algorithmic_GBps": step_bytes / (ms_step * 1e-3) / 1e9,
         "step_frac_of_peak": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
-        "roofline": roof, "roofline_group": roof_group, "kernels": breakdown,
+        "roofline": roof, "roofline_group": roof_group, "roofline_exchange": roof_exchange, "kernels": breakdown,
         "cpu_baseline": {"value": nv / dt, "unit": "views/s", "cores": cores, "kind": "port",
                          "sample": f"{nv} of {V_total} views of the same workload, oracle port of the reference loop on the host"},
         "e2e": {"value": e2e_views_per_s, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -57,6 +57,31 @@ def test_knn_duplicates_far_points_and_errors():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("case", ["floaters_everywhere", "one_far_cluster", "flat_axis"])
+def test_knn_robust_grid_with_many_points_outside_the_cube(case):
+    """The grid covers the 0.1 % .. 99.9 % coordinate range only; everything outside is clamped into
+    the (open-ended) border cells.  The search must stay exact when far more than 0.1 % of the points
+    lie outside -- far floaters on all sides, a distant cluster on one side, a degenerate (flat) axis."""
+    from sklearn.neighbors import NearestNeighbors
+    K = mod("knn")
+    rng = np.random.default_rng(7)
+    pts = _cloud(30000, 5)
+    if case == "floaters_everywhere":
+        m = rng.random(len(pts)) < 0.02
+        pts[m] = (rng.normal(size=(int(m.sum()), 3)) * 300).astype(np.float32)
+    elif case == "one_far_cluster":
+        pts[:900] = (np.array([4000.0, -2500.0, 800.0]) + rng.normal(size=(900, 3)) * 0.05).astype(np.float32)
+    else:
+        pts[:, 2] = 1.25
+        pts[:60, 2] = rng.normal(size=60).astype(np.float32) * 50
+    for k in (4, 40):
+        want_d, want_i = NearestNeighbors(n_neighbors=k, metric="euclidean").fit(pts).kneighbors(pts)
+        idx, dist, _ = K.knn_search(torch.from_numpy(pts).cuda(), k, exclude_self=False)
+        np.testing.assert_allclose(dist.cpu().numpy(), want_d.astype(np.float32), rtol=1e-6, atol=1e-9)
+        assert (idx.cpu().numpy() == want_i).mean() > 0.999
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("n,k", [(3000, 40), (60000, 40), (60000, 10)])
 def test_lof_matches_sklearn(n, k):
     from sklearn.neighbors import LocalOutlierFactor
