@@ -15,7 +15,7 @@ PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libmdi_b200.so"
 
 # ---- constants mirrored from include/mdi_b200.h ------------------------------------------------
-ABI_VERSION = 3
+ABI_VERSION = 4
 TILE_PX = 4096
 TILE_WORDS = TILE_PX // 32
 PATCH_STRIDE = 2048
@@ -90,7 +90,8 @@ _SIGNATURES = {
     "mdi_emit_points_capped": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _P, _I64, _P]),
     "mdi_emit_points_multi": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _INT, _P, _P, _I64, _P]),
     "mdi_emit_points_multicast": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _P, _P, _I64, _P]),
-    "mdi_emit_points_exchange": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _INT, _P, _P, _P, _P, _P, _I64, _P]),
+    "mdi_emit_points_exchange": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _INT, _INT, _P, _P, _P, _P, _P, _I64, _P, _INT, _P]),
+    "mdi_expand_rgb8": (_INT, [_P, _P, _P, _INT, _I64, _P]),
     "mdi_exchange_counts": (_INT, [_P, _INT, _INT, C.c_uint32, _P, _P, _P]),
     "mdi_min_extents": (_INT, [_P, _I64, _P, _P, _P, _INT, _P, _P]),
     "mdi_knn_workspace_bytes": (_I64, [_I64]),

@@ -100,6 +100,11 @@ struct EmitDst {
   // exchange launch (mdi_emit_points_exchange): row_offset is read from the device ([0] of the record
   // written by mdi_exchange_counts; [1] = rows of all ranks, checked against capacity)
   const int64_t* exchange;
+  // byte-rgb exchange (uint8 images): peers receive the gathered rgb BYTES (3 B per point instead of
+  // 12) in rgb8[d] and expand them themselves (mdi_expand_rgb8: u8 / 255.0f, the same division);
+  // the float rgb is written to this GPU's own cloud (index self) only
+  uint8_t* rgb8[MDI_MAX_EMIT_DST];
+  int self;
 };
 
 __device__ __forceinline__ void multicast_store(float* addr, float v) {
@@ -125,8 +130,32 @@ static_assert(sizeof(EmitTile) == 128, "EmitTile is eight 16-byte rows");
 // One contiguous run of `n_words` floats from shared memory (`s`, word k of the run at s[shift + k]
 // with shift = word misalignment of the destination, so both sides of every 16-byte copy are
 // aligned) to every destination: scalar head (<= 3 words), 128-bit body, scalar tail.
+// one contiguous run of n_bytes bytes from shared memory (byte k at s[shift + k], shift = byte
+// misalignment of the destination) to every peer's byte cloud: scalar head / tail, 16-byte body
+__device__ __forceinline__ void store_run_bytes(const EmitDst& dst, const uint8_t* s, int shift, int64_t b0,
+                                                int n_bytes) {
+  const int head = min((16 - shift) & 15, n_bytes);
+  const int n_vec = (n_bytes - head) >> 4;
+  const int tail0 = head + 16 * n_vec;
+  const int tid = threadIdx.x;
+  if (tid < head) {
+    const uint8_t v = s[shift + tid];
+    for (int d = 0; d < dst.n; ++d) if (d != dst.self) dst.rgb8[d][b0 + tid] = v;
+  }
+  for (int i = tid; i < n_vec; i += kEmitThreads) {
+    const uint4 v = *reinterpret_cast<const uint4*>(s + shift + head + 16 * i);
+    for (int d = 0; d < dst.n; ++d)
+      if (d != dst.self) *reinterpret_cast<uint4*>(dst.rgb8[d] + b0 + head + 16 * i) = v;
+  }
+  if (tid < n_bytes - tail0) {
+    const uint8_t v = s[shift + tail0 + tid];
+    for (int d = 0; d < dst.n; ++d) if (d != dst.self) dst.rgb8[d][b0 + tail0 + tid] = v;
+  }
+}
+
 __device__ __forceinline__ void store_run(const EmitDst& dst, bool is_rgb, const float* s, int shift,
-                                          int64_t w0, int n_words) {
+                                          int64_t w0, int n_words, int d_begin = 0, int d_end = MDI_MAX_EMIT_DST) {
+  d_end = min(d_end, dst.n);
   const int head = min((4 - shift) & 3, n_words);
   const int n_vec = (n_words - head) >> 2;
   const int tail0 = head + 4 * n_vec;
@@ -141,16 +170,16 @@ __device__ __forceinline__ void store_run(const EmitDst& dst, bool is_rgb, const
   }
   if (tid < head) {
     const float v = s[shift + tid];
-    for (int d = 0; d < dst.n; ++d) (is_rgb ? dst.rgb[d] : dst.xyz[d])[w0 + tid] = v;
+    for (int d = d_begin; d < d_end; ++d) (is_rgb ? dst.rgb[d] : dst.xyz[d])[w0 + tid] = v;
   }
   for (int i = tid; i < n_vec; i += kEmitThreads) {
     const float4 v = *reinterpret_cast<const float4*>(s + shift + head + 4 * i);
-    for (int d = 0; d < dst.n; ++d)
+    for (int d = d_begin; d < d_end; ++d)
       *reinterpret_cast<float4*>((is_rgb ? dst.rgb[d] : dst.xyz[d]) + w0 + head + 4 * i) = v;
   }
   if (tid < n_words - tail0) {
     const float v = s[shift + tail0 + tid];
-    for (int d = 0; d < dst.n; ++d) (is_rgb ? dst.rgb[d] : dst.xyz[d])[w0 + tail0 + tid] = v;
+    for (int d = d_begin; d < d_end; ++d) (is_rgb ? dst.rgb[d] : dst.xyz[d])[w0 + tail0 + tid] = v;
   }
 }
 
@@ -176,10 +205,12 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
   __shared__ uint16_t s_list[kEmitList];
   __shared__ __align__(16) float s_xyz[3 * kEmitList + 4];
   __shared__ __align__(16) float s_rgb[3 * kEmitList + 4];
+  __shared__ __align__(16) uint8_t s_rgb8[IMAGE_KIND == MDI_IMAGE_U8 ? 3 * kEmitList + 16 : 16];
   __shared__ int s_scan[33];
   __shared__ long long s_out0;
   const bool want_xyz = dst.xyz[0] != nullptr || dst.mc_xyz != nullptr;
   const bool want_rgb = dst.rgb[0] != nullptr || dst.mc_rgb != nullptr;
+  const bool rgb_bytes = IMAGE_KIND == MDI_IMAGE_U8 && want_rgb && dst.n > 1 && dst.rgb8[0] != nullptr;
   const int tid = threadIdx.x;
   const int64_t tile0 = (int64_t)blockIdx.x * kEmitTiles;
   if (dst.total_rows && __ldg(dst.total_rows) > dst.capacity) return;
@@ -254,6 +285,7 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
     const float* any_r = dst.n ? dst.rgb[0] : dst.mc_rgb;
     const int sh_x = want_xyz ? (int)((reinterpret_cast<uintptr_t>(any_x + w0) >> 2) & 3) : 0;
     const int sh_r = want_rgb ? (int)((reinterpret_cast<uintptr_t>(any_r + w0) >> 2) & 3) : 0;
+    const int sh_b = rgb_bytes ? (int)(reinterpret_cast<uintptr_t>(dst.rgb8[0] + w0) & 15) : 0;   // byte w0 = 3 * row
     // (3) one point per thread
     for (int j = tid; j < n_here; j += kEmitThreads) {
       const uint32_t e = s_list[j];
@@ -270,6 +302,7 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
           const uint8_t* im = reinterpret_cast<const uint8_t*>(T.image) + 3 * p;
           const uint8_t a0 = im[0], a1 = im[1], a2 = im[2];
           r = fdiv((float)a0, 255.0f); g = fdiv((float)a1, 255.0f); bl = fdiv((float)a2, 255.0f);
+          if (rgb_bytes) { uint8_t* ob = s_rgb8 + sh_b + 3 * j; ob[0] = a0; ob[1] = a1; ob[2] = a2; }
         } else {
           const float* im = reinterpret_cast<const float*>(T.image) + 3 * p;
           r = im[0]; g = im[1]; bl = im[2];
@@ -297,8 +330,41 @@ emit_points_kernel(const MdiView* __restrict__ views, int n_views,
     __syncthreads();
     // (4) the pass is one contiguous run of 3 * n_here words in every destination cloud
     if (want_xyz) store_run(dst, false, s_xyz, sh_x, w0, 3 * n_here);
-    if (want_rgb) store_run(dst, true, s_rgb, sh_r, w0, 3 * n_here);
+    if (want_rgb && !rgb_bytes) store_run(dst, true, s_rgb, sh_r, w0, 3 * n_here);
+    if (rgb_bytes) {   // floats to the own cloud, bytes to the peers
+      store_run(dst, true, s_rgb, sh_r, w0, 3 * n_here, dst.self, dst.self + 1);
+      store_run_bytes(dst, s_rgb8, sh_b, w0, 3 * n_here);
+    }
     __syncthreads();
+  }
+}
+
+// Receiver side of the byte-rgb exchange: rows of OTHER ranks arrive as bytes; rgb = u8 / 255.0f, the
+// division the emit kernel applies to its own rows (bit-identical).  record: the mdi_exchange_counts
+// record of the step ([0] first row of this rank, [1] rows of all ranks, [3 + rank] rows of this rank).
+__global__ void __launch_bounds__(256)
+expand_rgb8_kernel(const uint8_t* __restrict__ rgb8, float* __restrict__ rgb, const int64_t* __restrict__ record,
+                   int rank, int64_t capacity) {
+  const int64_t total = record[1];
+  if (total > capacity) return;
+  const int64_t own0 = 3 * record[0], own1 = own0 + 3 * record[3 + rank], n = 3 * total;
+  const int64_t n4 = n >> 2;   // groups of four elements: one 32-bit load, one 128-bit store
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = 4 * g;
+    if (i >= own0 && i + 4 <= own1) continue;          // wholly inside this rank's own rows
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(rgb8 + i);
+    float4 v = make_float4(fdiv((float)(w & 255u), 255.0f), fdiv((float)((w >> 8) & 255u), 255.0f),
+                           fdiv((float)((w >> 16) & 255u), 255.0f), fdiv((float)(w >> 24), 255.0f));
+    if (i >= own1 || i + 4 <= own0) {
+      *reinterpret_cast<float4*>(rgb + i) = v;
+    } else {                                           // straddles the boundary of the own rows
+      const float e[4] = {v.x, v.y, v.z, v.w};
+      for (int k = 0; k < 4; ++k) if (i + k < own0 || i + k >= own1) rgb[i + k] = e[k];
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (int)(n & 3)) {
+    const int64_t i = 4 * n4 + threadIdx.x;
+    if (i < own0 || i >= own1) rgb[i] = fdiv((float)rgb8[i], 255.0f);
   }
 }
 
@@ -460,7 +526,8 @@ extern "C" int mdi_emit_points_exchange(const MdiView* views, int n_views, int64
                                         const int64_t* tile_offsets, const int64_t* view_offsets,
                                         int image_kind, int n_dst, float* const* xyz_dst,
                                         float* const* rgb_dst, float* xyz_mc, float* rgb_mc,
-                                        const int64_t* exchange_record, int64_t capacity_rows, void* stream) {
+                                        const int64_t* exchange_record, int64_t capacity_rows,
+                                        uint8_t* const* rgb8_dst, int self_rank, void* stream) {
   MDI_REQUIRE(n_dst >= 0 && n_dst <= MDI_MAX_EMIT_DST, "mdi_emit_points_exchange: n_dst %d not in 0..%d", n_dst,
               MDI_MAX_EMIT_DST);
   MDI_REQUIRE(exchange_record && capacity_rows >= 0, "mdi_emit_points_exchange: null record / negative capacity");
@@ -476,9 +543,30 @@ extern "C" int mdi_emit_points_exchange(const MdiView* views, int n_views, int64
       dst.rgb[d] = rgb_dst ? rgb_dst[d] : nullptr;
       MDI_REQUIRE((!xyz_dst || dst.xyz[d]) && (!rgb_dst || dst.rgb[d]), "mdi_emit_points_exchange: null destination %d", d);
     }
+    if (rgb8_dst && rgb_dst && image_kind == MDI_IMAGE_U8 && n_dst > 1) {
+      MDI_REQUIRE(self_rank >= 0 && self_rank < n_dst, "mdi_emit_points_exchange: self_rank %d outside 0..%d", self_rank, n_dst - 1);
+      for (int d = 0; d < n_dst; ++d) {
+        MDI_REQUIRE(rgb8_dst[d] && ((reinterpret_cast<uintptr_t>(rgb8_dst[d]) ^ reinterpret_cast<uintptr_t>(rgb8_dst[0])) & 15) == 0,
+                    "mdi_emit_points_exchange: byte clouds must be non-null and share their 16-byte alignment");
+        dst.rgb8[d] = rgb8_dst[d];
+      }
+      dst.self = self_rank;
+    }
   }
   return launch_emit(views, n_views, total_tiles, scale_shift, bits, tile_offsets, view_offsets, image_kind,
                      dst, stream, "mdi_emit_points_exchange");
+}
+
+extern "C" int mdi_expand_rgb8(const uint8_t* rgb8, float* rgb, const int64_t* exchange_record, int rank,
+                               int64_t capacity_rows, void* stream) {
+  MDI_REQUIRE(rgb8 && rgb && exchange_record && rank >= 0 && rank < MDI_MAX_EMIT_DST && capacity_rows >= 0,
+              "mdi_expand_rgb8: bad argument");
+  MDI_REQUIRE(((reinterpret_cast<uintptr_t>(rgb8) & 3) | (reinterpret_cast<uintptr_t>(rgb) & 15)) == 0,
+              "mdi_expand_rgb8: clouds must be 4- / 16-byte aligned");
+  mdi::prof_mark("expand_rgb8_kernel", (cudaStream_t)stream);
+  mdi::expand_rgb8_kernel<<<mdi::kSMs * 8, 256, 0, (cudaStream_t)stream>>>(rgb8, rgb, exchange_record, rank, capacity_rows);
+  MDI_CHECK_LAUNCH("mdi_expand_rgb8");
+  return MDI_OK;
 }
 
 extern "C" int mdi_exchange_counts(int64_t* const* hdr_ptrs, int rank, int world, uint32_t epoch,

@@ -67,7 +67,10 @@ class CloudExchange:
 
     MAX_RANKS = 16   # MDI_MAX_EMIT_DST
 
-    def __init__(self, device, group=None, capacity_rows: int = 1 << 20):
+    def __init__(self, device, group=None, capacity_rows: int = 1 << 20, byte_rgb: bool = False):
+        """byte_rgb (the same on every rank; uint8 images only): peers receive the gathered rgb as
+        3 bytes per point and expand them locally (u8 / 255, bit-identical) -- 15 instead of 24 bytes
+        of NVLink ingress per remote point."""
         import torch.distributed._symmetric_memory as symm_mem
         from . import _lib as L
         self._symm, self._L = symm_mem, L
@@ -78,6 +81,7 @@ class CloudExchange:
         if self.world > self.MAX_RANKS:
             raise ValueError("CloudExchange: at most 16 ranks (MDI_MAX_EMIT_DST)")
         self.capacity = 0
+        self.byte_rgb = bool(byte_rgb)
         self._alloc(int(capacity_rows))
         # count-exchange headers: 2 slot sets x world int64 per rank, zero before anybody publishes
         self._hdr = symm_mem.empty(2 * self.MAX_RANKS, dtype=torch.int64, device=self.device)
@@ -99,6 +103,11 @@ class CloudExchange:
         self._hr = self._symm.rendezvous(self.rgb, group=self.group)
         self.xyz_ptrs = [int(p) for p in self._hx.buffer_ptrs]
         self.rgb_ptrs = [int(p) for p in self._hr.buffer_ptrs]
+        self.rgb8_ptrs = None
+        if self.byte_rgb:
+            self.rgb8 = self._symm.empty(rows * 3 + 16, dtype=torch.uint8, device=self.device)
+            self._h8 = self._symm.rendezvous(self.rgb8, group=self.group)
+            self.rgb8_ptrs = [int(p) for p in self._h8.buffer_ptrs]
         # NVSwitch multicast addresses of the two clouds (0 when the fabric has no NVLS)
         self.xyz_mc = int(getattr(self._hx, "multicast_ptr", 0) or 0)
         self.rgb_mc = int(getattr(self._hr, "multicast_ptr", 0) or 0)
@@ -118,6 +127,13 @@ class CloudExchange:
         L.check(L.load().mdi_exchange_counts(hp, self.rank, self.world, self.epoch,
                                              local_ptr if local_ptr is not None else self._zero2.data_ptr(),
                                              self.record.data_ptr(), stream), "mdi_exchange_counts")
+
+    def expand_bytes(self, stream: int) -> None:
+        """After the step's barrier (byte_rgb): fill the other ranks' rows of this rank's float rgb
+        cloud from the bytes they sent.  Local, stream ordered."""
+        L = self._L
+        L.check(L.load().mdi_expand_rgb8(self.rgb8.data_ptr(), self.rgb.data_ptr(), self.record.data_ptr(), self.rank,
+                                         int(self.capacity), stream), "mdi_expand_rgb8")
 
     def barrier(self) -> None:
         """Collective, stream ordered: returns (on the stream) once every rank's emit kernel of this

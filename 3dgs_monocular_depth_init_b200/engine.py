@@ -149,7 +149,7 @@ KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_upload_table": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_capped": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
-    "mdi_emit_points_exchange": 1, "mdi_exchange_counts": 1,
+    "mdi_emit_points_exchange": 1, "mdi_exchange_counts": 1, "mdi_expand_rgb8": 1,
     "mdi_min_extents": 1,
 }
 
@@ -581,7 +581,10 @@ class Engine:
             def launch_emit():
                 ex = opt.exchange
                 xp = rp = None
-                n_dst = 0 if ex.use_multicast else ex.world
+                if ex.byte_rgb and want_rgb and int(vin.image_kind) != L.IMAGE_U8:
+                    raise L.MdiError("CloudExchange(byte_rgb=True) needs uint8 images on every rank")
+                n_dst = 0 if (ex.use_multicast and not ex.byte_rgb) else ex.world
+                r8 = (C.c_void_p * n_dst)(*ex.rgb8_ptrs) if (ex.byte_rgb and want_rgb and n_dst) else None
                 if n_dst:
                     xp = (C.c_void_p * n_dst)(*ex.xyz_ptrs) if want_xyz else None
                     rp = (C.c_void_p * n_dst)(*ex.rgb_ptrs) if want_rgb else None
@@ -589,7 +592,7 @@ class Engine:
                                                      res.view_offsets.data_ptr(), int(vin.image_kind), n_dst, xp, rp,
                                                      ex.xyz_mc if (not n_dst and want_xyz) else None,
                                                      ex.rgb_mc if (not n_dst and want_rgb) else None,
-                                                     ex.record.data_ptr(), int(ex.capacity), st),
+                                                     ex.record.data_ptr(), int(ex.capacity), r8, int(ex.rank), st),
                         "mdi_emit_points_exchange")
 
             def remask(mode):
@@ -651,6 +654,8 @@ class Engine:
             if launch_emit is not None:
                 launch_emit()
             ex.barrier()
+            if ex.byte_rgb:
+                ex.expand_bytes(st)
             row_offset, total_all, retry_any, counts, mine = ex.read_record(local)
             if retry_any:
                 # ranks whose own flag is clear keep their masks and simply emit again next round
@@ -662,6 +667,8 @@ class Engine:
                 if launch_emit is not None:
                     launch_emit()
                 ex.barrier()
+                if ex.byte_rgb:
+                    ex.expand_bytes(st)
                 torch.cuda.current_stream(self.device).synchronize()
             break
         res.total = counts[ex.rank]

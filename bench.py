@@ -261,9 +261,10 @@ def run_ours(args):
     gather = "none"
     if world > 1:
         try:
-            exchange = dmod.CloudExchange(dev, capacity_rows=1 << 22)
+            exchange = dmod.CloudExchange(dev, capacity_rows=1 << 22, byte_rgb=os.environ.get("MDI_BYTE_RGB", "1" if world > 2 else "0") == "1")
             gather = ("emit kernel writes every rank's cloud through NVSwitch multicast (multimem.st.v4)" if exchange.use_multicast
-                      else "emit kernel writes peer clouds over NVLink (16-byte stores, symmetric memory); counts exchanged on the device")
+                      else "emit kernel writes peer clouds over NVLink (16-byte stores, symmetric memory); counts exchanged on the device"
+                           + ("; rgb travels as 3 bytes per point and is expanded by the receiver" if exchange.byte_rgb else ""))
         except Exception as e:  # noqa: BLE001 - any failure to map peer memory selects the NCCL path
             gather = f"nccl all_gather ({type(e).__name__})"
 
@@ -433,7 +434,7 @@ def run_ours(args):
     roof_exchange = None
     if world > 1 and "emit_points_kernel" in ktimes and exchange is not None:
         per = ktimes["emit_points_kernel"]["ms"] / ktimes["emit_points_kernel"]["calls"]
-        ingress = 24.0 * (n_kept_total - n_kept)
+        ingress = (15.0 if exchange.byte_rgb else 24.0) * (n_kept_total - n_kept)
         ach = ingress / (per * 1e-3) / 1e9
         roof_exchange = {"bound": "nvlink", "kernel": "emit_points_kernel", "ms": round(per, 4),
                          "ingress_bytes_per_gpu": int(ingress), "achieved": ach, "peak": 770.0, "unit": "GB/s",

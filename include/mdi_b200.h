@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MDI_ABI_VERSION 3
+#define MDI_ABI_VERSION 4
 
 /* error codes */
 #define MDI_OK 0
@@ -347,7 +347,20 @@ int mdi_emit_points_exchange(const MdiView* views, int n_views, int64_t total_ti
                              const float* scale_shift, const uint32_t* bits, const int64_t* tile_offsets,
                              const int64_t* view_offsets, int image_kind, int n_dst,
                              float* const* xyz_dst, float* const* rgb_dst, float* xyz_mc, float* rgb_mc,
-                             const int64_t* exchange_record, int64_t capacity_rows, void* stream);
+                             const int64_t* exchange_record, int64_t capacity_rows,
+                             uint8_t* const* rgb8_dst, int self_rank, void* stream);
+
+/*
+ * Byte-rgb exchange (uint8 images, n_dst > 1, rgb8_dst != NULL): the rgb a peer needs is the three
+ * gathered BYTES of a point -- the float rgb is u8 / 255.0f, which the receiver computes itself with
+ * the same division.  Peers then receive 12 + 3 instead of 12 + 12 bytes per point over NVLink:
+ * mdi_emit_points_exchange writes float rgb into rgb_dst[self_rank] only and the bytes into every
+ * other rank's rgb8_dst[d] (uint8 [capacity_rows * 3], peer-mapped, 16-byte aligned), and after the
+ * step's barrier every rank calls mdi_expand_rgb8 on its own byte cloud to fill the other ranks' rows
+ * of its float rgb cloud.  Bit-identical to exchanging the floats.
+ */
+int mdi_expand_rgb8(const uint8_t* rgb8, float* rgb, const int64_t* exchange_record, int rank,
+                    int64_t capacity_rows, void* stream);
 
 /*
  * a13: minimal Gaussian extent per point over all cameras that see it (else -1).

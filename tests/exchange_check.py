@@ -32,8 +32,10 @@ def main():
     names = [sc.names[i] for i in mine]
     args = (sel(sc.depth), sel(sc.mask), sel(sc.image), sel(sc.K), sel(sc.c2w), names, sc.points, sc.point_indices, dev,
             L.IMAGE_U8)
-    ex = dmod.CloudExchange(dev, capacity_rows=1024)  # small on purpose: exercises the collective growth
-    for rep in range(3):  # the buffers are reused across scenes
+    exchanges = [dmod.CloudExchange(dev, capacity_rows=1024),                   # small on purpose: collective growth
+                 dmod.CloudExchange(dev, capacity_rows=1024, byte_rgb=True)]    # rgb travels as 3 bytes per point
+    for rep in range(4):  # the buffers are reused across scenes
+        ex = exchanges[rep % 2]
         res = mdi.points_from_views(cfg, *args, exchange=ex)
         got_xyz, got_rgb = res.xyz.clone(), res.rgb.clone()
         loc = mdi.points_from_views(cfg, *args)
