@@ -47,7 +47,7 @@ class RansacConfigC(C.Structure):
     _fields_ = [
         ("inlier_threshold", C.c_float), ("max_iters", C.c_int32), ("confidence", C.c_double),
         ("sample_size", C.c_int32), ("min_iters", C.c_int32), ("loss_kind", C.c_int32),
-        ("_pad", C.c_int32), ("seed", C.c_uint64),
+        ("view_base", C.c_int32), ("seed", C.c_uint64),
     ]
 
 

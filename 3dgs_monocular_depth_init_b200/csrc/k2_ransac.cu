@@ -146,7 +146,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
           uint64_t ctr = 0;
           bool dup;
           do {
-            const uint64_t r = splitmix64(cfg.seed ^ splitmix64(((uint64_t)v << 40) ^ ((uint64_t)it << 8) ^ (uint64_t)k ^ (ctr << 56)));
+            const uint64_t r = splitmix64(cfg.seed ^ splitmix64(((uint64_t)(uint32_t)(v + cfg.view_base) << 40) ^ ((uint64_t)it << 8) ^ (uint64_t)k ^ (ctr << 56)));
             idx = (int)(r % (uint64_t)n);
             dup = false;
             for (int j = 0; j < k; ++j) dup |= (chosen[j] == idx);
@@ -341,6 +341,7 @@ extern "C" int mdi_ransac(const MdiView* views, int n_views, const float* d, con
   MDI_REQUIRE(cfg->sample_size >= 1 && cfg->sample_size <= kMaxSample,
               "mdi_ransac: sample_size %d not in 1..%d", cfg->sample_size, kMaxSample);
   MDI_REQUIRE(cfg->max_iters >= 0 && max_points >= 0, "mdi_ransac: negative max_iters/max_points");
+  MDI_REQUIRE(cfg->view_base >= 0, "mdi_ransac: negative view_base");
   MDI_REQUIRE(cfg->loss_kind == MDI_LOSS_RANSAC || cfg->loss_kind == MDI_LOSS_MSAC,
               "mdi_ransac: unknown loss kind %d", cfg->loss_kind);
   cudaStream_t st = (cudaStream_t)stream;

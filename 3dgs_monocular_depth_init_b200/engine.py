@@ -9,6 +9,7 @@ monocular_depth_init.py:120-184 (scene loop), batched over views.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 from typing import Optional, Sequence, Union
 
@@ -18,6 +19,10 @@ import torch
 from . import _lib as L
 
 TensorOrList = Union[torch.Tensor, Sequence[torch.Tensor]]
+
+# view ranges of one run queued on separate CUDA streams (RunOptions.streams overrides)
+DEFAULT_STREAMS = max(1, int(os.environ.get("MDI_STREAMS", "1") or 1))
+MIN_VIEWS_PER_RANGE = 16
 
 
 def patch_geometry(H: int, W: int, n_small: int):
@@ -83,6 +88,7 @@ class RunOptions:
     exchange: object = None                      # distributed.CloudExchange: emit into every rank's cloud
     speculative_emit: bool = True                # launch a10/a11 before the output size reaches the host
     defer_emit: bool = False                     # stop after the mask; Engine.emit_deferred() writes the cloud later
+    streams: Optional[int] = None                # view ranges queued on separate streams (None: MDI_STREAMS, default 1)
 
 
 @dataclass
@@ -224,6 +230,31 @@ class Engine:
             t = torch.empty(max(int(n * 1.25), 16), dtype=dtype, device=self.device)
             self._ws[name] = t
         return t[:n]
+
+    # ---- view ranges on part streams ---------------------------------------------------------------
+    def _part_stream(self, i: int) -> "torch.cuda.Stream":
+        ps = self.__dict__.setdefault("_part_streams", [])
+        while len(ps) <= i:
+            ps.append(torch.cuda.Stream(self.device))
+        return ps[i]
+
+    @staticmethod
+    def _view_ranges(vin: ViewInputs, opt: RunOptions, V: int, desc, adaptive: bool, have_proj: bool):
+        """Contiguous view ranges of a run: one (the whole batch) unless RunOptions.streams / MDI_STREAMS
+        asks for more and the run is the plain full pipeline (every kernel of it indexes its per-view
+        arguments by the view's position in the range, so a range is the same call with offset
+        pointers; the per-pixel mask kernel is the exception and keeps such runs in one range)."""
+        n = opt.streams if opt.streams is not None else DEFAULT_STREAMS
+        lattice = bool(opt.flags & L.KEEP_SUBSAMPLE) and (
+            (adaptive and opt.factor_min >= 1 and opt.factor_max >= opt.factor_min and opt.factor_max - opt.factor_min < 4096)
+            or (not adaptive and opt.subsample not in (0, -2**31)))
+        if (n <= 1 or V < MIN_VIEWS_PER_RANGE * 2 or not have_proj or opt.stop_after not in (None, "mask")
+                or opt.aligner not in ("lstsqrs", "ransac", "msac") or opt.grad_thresh is not None or opt.defer_emit
+                or opt.stats_exact or not lattice or int(desc["H"].max()) >= 65536 or int(desc["W"].max()) >= 65536):
+            return [(0, V)]
+        n = min(n, V // MIN_VIEWS_PER_RANGE)
+        cuts = [(V * i) // n for i in range(n + 1)]
+        return [(cuts[i], cuts[i + 1]) for i in range(n)]
 
     # ---- descriptor table ---------------------------------------------------------------------
     def build_views(self, vin: ViewInputs, opt: RunOptions):
@@ -374,10 +405,10 @@ class Engine:
             # torch.linalg.inv); anything else: batched LU inverse on the host like the reference
             if vin.P_override is not None:  # stage-wise parity / project_and_filter_sfm_pts: P as given
                 desc["P"] = vin.P_override.reshape(V, 12).numpy()
-            parts = [desc.view(np.uint8).reshape(-1), kn, c2wn]
+            blob_parts = [desc.view(np.uint8).reshape(-1), kn, c2wn]
             if not pinhole:
-                parts.append(torch.linalg.inv(torch.from_numpy(kn)).numpy())
-            blob = self._upload("views", parts, owned=opt.defer_emit)
+                blob_parts.append(torch.linalg.inv(torch.from_numpy(kn)).numpy())
+            blob = self._upload("views", blob_parts, owned=opt.defer_emit)
             if key is not None:
                 self._plan = (key, (desc, px_begin.copy(), tile_begin, sfm_begin.copy(), blob, pinhole))
         vp = blob.data_ptr()
@@ -390,40 +421,42 @@ class Engine:
 
         i32, f32 = torch.int32, torch.float32
         res.status = torch.zeros(V, dtype=i32, device=self.device)
-        # a2: projection + filtering (or externally supplied coords)
+        VS = desc.itemsize
+        adaptive = opt.subsample == "adaptive"
+        if not adaptive and not isinstance(opt.subsample, int) and opt.stop_after not in ("project", "fit"):
+            raise ValueError(f"Unsupported subsampling factor: {opt.subsample}")
+        have_proj = vin.uv is None and vin.sfm_xyz is not None
+        ranges = self._view_ranges(vin, opt, V, desc, adaptive, have_proj)
+        parts = len(ranges)
+
+        def at(t, a, per_view=1):
+            """address of view a's row in a per-view array (None stays NULL)"""
+            return None if t is None else t.data_ptr() + a * per_view * t.element_size()
+
+        # ---- a2-a4 outputs: everything is allocated on the calling stream before the first launch, so
+        # that view ranges can be queued on part streams without the allocator seeing those streams
         if vin.uv is not None:
             res.uv, res.z, res.n_valid = vin.uv, vin.z, vin.n_valid
             assert res.uv.shape[1] >= slots - 4 and res.uv.dtype == i32
             slots = int(res.uv.shape[1])
-        elif vin.sfm_xyz is not None:
+        elif have_proj:
             res.uv = torch.empty((2, slots), dtype=i32, device=self.device)
             res.z = torch.empty(slots, dtype=f32, device=self.device)
             res.n_inbounds = torch.empty(V, dtype=i32, device=self.device)
             res.n_valid = torch.empty(V, dtype=i32, device=self.device)
-            L.check(lib.mdi_project_filter(vp, V, vin.sfm_xyz.data_ptr(), L.ptr(vin.sfm_index), slots,
-                                           res.uv.data_ptr(), res.z.data_ptr(), res.n_inbounds.data_ptr(),
-                                           res.n_valid.data_ptr(), res.status.data_ptr(), st),
-                    "mdi_project_filter")
-        if opt.stop_after == "project":
-            return res
-
-        # a3 + a8: gather, normal equations, patch histogram
         have_pts = res.uv is not None
         use_patch = bool(opt.use_patch_mask and have_pts)
-        if have_pts:
+        want_fit = opt.stop_after != "project"
+        write_fit = opt.aligner == "lstsqrs"
+        cfg = None
+        if have_pts and want_fit:
             res.d = torch.zeros(slots, dtype=f32, device=self.device)
             res.sums = torch.empty((V, 5), dtype=torch.float64, device=self.device)
-            write_fit = opt.aligner == "lstsqrs"
             if write_fit:
                 res.scale_shift = torch.empty((V, 2), dtype=f32, device=self.device)
             if use_patch:
                 res.patch_blocked = torch.empty((V, L.PATCH_STRIDE), dtype=torch.uint8, device=self.device)
-            L.check(lib.mdi_gather_fit(vp, V, slots, res.uv.data_ptr(), res.z.data_ptr(), res.n_valid.data_ptr(),
-                                       res.d.data_ptr(), res.sums.data_ptr(), L.ptr(res.scale_shift),
-                                       1 if write_fit else 0, int(opt.patch_threshold),
-                                       L.ptr(res.patch_blocked), st), "mdi_gather_fit")
-        # a4: RANSAC / MSAC
-        if opt.aligner in ("ransac", "msac"):
+        if opt.aligner in ("ransac", "msac") and want_fit:
             assert have_pts, "RANSAC needs SfM points"
             cfg = L.RansacConfigC(float(opt.ransac_threshold), int(opt.ransac_max_iters),
                                   float(opt.ransac_confidence), int(opt.ransac_sample_size),
@@ -439,25 +472,46 @@ class Engine:
                 assert opt.sample_idx.dtype == i32 and opt.sample_idx.is_cuda and opt.sample_idx.is_contiguous()
                 assert tuple(opt.sample_idx.shape) == (V, opt.ransac_max_iters, opt.ransac_sample_size)
             max_pts = int(desc["sfm_count"].max())
-            L.check(lib.mdi_ransac(vp, V, res.d.data_ptr(), res.z.data_ptr(), res.n_valid.data_ptr(),
-                                   res.status.data_ptr(), L.ptr(opt.sample_idx), C.byref(cfg), max_pts,
-                                   res.scale_shift.data_ptr(), L.ptr(res.inlier_mask),
-                                   res.ransac_iters.data_ptr(), res.ransac_inliers.data_ptr(), st),
-                    "mdi_ransac")
         elif opt.aligner is None:
             res.scale_shift = opt.scale_shift
             if res.scale_shift is not None:
                 assert res.scale_shift.dtype == f32 and tuple(res.scale_shift.shape) == (V, 2)
-        elif opt.aligner != "lstsqrs":
+        elif opt.aligner not in ("lstsqrs", "ransac", "msac"):
             raise NotImplementedError(f"aligner {opt.aligner!r} is not on the B200 path")
-        if opt.stop_after == "fit":
-            return res
+
+        def launch_project(a: int, b: int, s: int):
+            """a2 of views a..b-1: projection + filtering"""
+            L.check(lib.mdi_project_filter(vp + a * VS, b - a, vin.sfm_xyz.data_ptr(), L.ptr(vin.sfm_index), slots,
+                                           res.uv.data_ptr(), res.z.data_ptr(), at(res.n_inbounds, a),
+                                           at(res.n_valid, a), at(res.status, a), s),
+                    "mdi_project_filter")
+
+        def launch_fit(a: int, b: int, s: int):
+            """a3 + a8 (gather, normal equations, patch histogram) and a4 (RANSAC / MSAC) of views a..b-1"""
+            if have_pts:
+                L.check(lib.mdi_gather_fit(vp + a * VS, b - a, slots, res.uv.data_ptr(), res.z.data_ptr(), at(res.n_valid, a),
+                                           res.d.data_ptr(), at(res.sums, a, 5), at(res.scale_shift, a, 2) if write_fit else None,
+                                           1 if write_fit else 0, int(opt.patch_threshold),
+                                           at(res.patch_blocked, a, L.PATCH_STRIDE), s), "mdi_gather_fit")
+            if cfg is not None:
+                cfg.view_base = a   # the device sampler draws per batch view, whatever the launch ranges are
+                L.check(lib.mdi_ransac(vp + a * VS, b - a, res.d.data_ptr(), res.z.data_ptr(), at(res.n_valid, a),
+                                       at(res.status, a), at(opt.sample_idx, a, opt.ransac_max_iters * opt.ransac_sample_size),
+                                       C.byref(cfg), max_pts, at(res.scale_shift, a, 2), L.ptr(res.inlier_mask),
+                                       at(res.ransac_iters, a), at(res.ransac_inliers, a), s),
+                        "mdi_ransac")
+
+        if parts == 1:
+            if have_proj:
+                launch_project(0, V, st)
+            if opt.stop_after == "project":
+                return res
+            launch_fit(0, V, st)
+            if opt.stop_after == "fit":
+                return res
 
         # a7 / a9: per-view statistics
         ftab = None
-        adaptive = opt.subsample == "adaptive"
-        if not adaptive and not isinstance(opt.subsample, int):
-            raise ValueError(f"Unsupported subsampling factor: {opt.subsample}")
         flags = opt.flags
         if use_patch:
             flags |= L.KEEP_PATCH
@@ -466,8 +520,15 @@ class Engine:
         meta = torch.zeros(2 * V + 2, dtype=torch.int64, device=self.device)
         res.view_counts, res.view_offsets = meta[:V], meta[V:2 * V]
         use_stats = bool(adaptive and (flags & L.KEEP_SUBSAMPLE))
+        ws_part = [0] * parts
         if use_stats:
             wsb = int(lib.mdi_depth_range_workspace_bytes(V, max_tiles))
+            if parts > 1:   # one workspace per view range, 256-byte aligned; the whole-batch retry reuses the buffer
+                o = 0
+                for i, (a, b) in enumerate(ranges):
+                    ws_part[i] = o
+                    o += (int(lib.mdi_depth_range_workspace_bytes(b - a, max_tiles)) + 255) & ~255
+                wsb = max(wsb, o)
             ws = self._buf("stats_ws", wsb, torch.uint8)
             res.lo_hi = torch.empty((V, 2), dtype=f32, device=self.device)
             res.quantiles = torch.empty((V, 4), dtype=f32, device=self.device)
@@ -516,29 +577,65 @@ class Engine:
         hint = getattr(self, "_emit_hint", 0)
         may_speculate = bool(opt.speculative_emit and opt.exchange is None and opt.stop_after != "mask"
                              and not opt.defer_emit and (want_xyz or want_rgb) and hint > 0)
+        Hmax, Wmax = int(desc["H"].max()), int(desc["W"].max())
 
-        def launch_mask(stats_mode: int):
-            """a7 statistics -> a5-a10 keep mask -> compaction offsets (launches only)."""
+        def launch_mask_range(a: int, b: int, stats_mode: int, s: int, ws_ptr: int, zeroed: bool):
+            """a7 statistics -> a5-a10 keep mask of views a..b-1 (launches only)"""
             if use_stats:
-                L.check(lib.mdi_depth_range(vp, V, max_tiles, ssp, res.status.data_ptr(),
+                L.check(lib.mdi_depth_range(vp + a * VS, b - a, max_tiles, at(res.scale_shift, a, 2), at(res.status, a),
                                             (flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)) | stats_mode,
-                                            ws.data_ptr(), res.lo_hi.data_ptr(), res.quantiles.data_ptr(),
-                                            meta[2 * V + 1:].data_ptr(), st), "mdi_depth_range")
-                L.check(lib.mdi_factor_table(V, res.lo_hi.data_ptr(), int(opt.factor_min), int(opt.factor_max),
-                                             ftab.data_ptr(), st), "mdi_factor_table")
-            if prezeroed[0]:
-                main.wait_event(zero_done)
-                scfg.flags = int(flags) | L.KEEP_PREZEROED
-                prezeroed[0] = False
-            else:  # the exact-statistics retry fills again, in stream order
-                scfg.flags = int(flags)
-            L.check(lib.mdi_keep_mask(vp, V, total_tiles, int(px_begin[-1]), int(desc["H"].max()), int(desc["W"].max()), ssp,
-                                      res.status.data_ptr(), L.ptr(res.lo_hi), L.ptr(res.grad_range),
-                                      L.ptr(res.patch_blocked), L.ptr(ftab), C.byref(scfg), L.ptr(res.keep),
-                                      bits.data_ptr(), tile_counts.data_ptr(), st), "mdi_keep_mask")
+                                            ws_ptr, at(res.lo_hi, a, 2), at(res.quantiles, a, 4),
+                                            meta[2 * V + 1:].data_ptr(), s), "mdi_depth_range")
+                L.check(lib.mdi_factor_table(b - a, at(res.lo_hi, a, 2), int(opt.factor_min), int(opt.factor_max),
+                                             at(ftab, a, L.FACTOR_TABLE_STRIDE), s), "mdi_factor_table")
+            scfg.flags = int(flags) | (L.KEEP_PREZEROED if zeroed else 0)
+            L.check(lib.mdi_keep_mask(vp + a * VS, b - a, total_tiles, int(px_begin[-1]), Hmax, Wmax, at(res.scale_shift, a, 2),
+                                      at(res.status, a), at(res.lo_hi, a, 2), at(res.grad_range, a, 2),
+                                      at(res.patch_blocked, a, L.PATCH_STRIDE), at(ftab, a, L.FACTOR_TABLE_STRIDE),
+                                      C.byref(scfg), L.ptr(res.keep), bits.data_ptr(), tile_counts.data_ptr(), s),
+                    "mdi_keep_mask")
+
+        def launch_scan():
             L.check(lib.mdi_scan_tiles(vp, V, total_tiles, tile_counts.data_ptr(), tile_offsets.data_ptr(),
                                        res.view_counts.data_ptr(), res.view_offsets.data_ptr(),
                                        meta[2 * V:].data_ptr(), st), "mdi_scan_tiles")
+
+        def launch_mask(stats_mode: int):
+            """a7 statistics -> a5-a10 keep mask -> compaction offsets (launches only).  The first call of a
+            run with several view ranges also carries their alignment stages: range i goes to part stream
+            i (range 0 stays on the calling stream), so that the latency-bound kernels of one range
+            (projection, fit, RANSAC, brackets, in-bin select) share the SMs with the HBM-bound ones of
+            another; the ranges meet again in front of the scan."""
+            if prezeroed[0] and parts > 1:
+                prezeroed[0] = False
+                forked = torch.cuda.Event()
+                forked.record(main)
+                joined = []
+                for i, (a, b) in enumerate(ranges):
+                    ps = main if i == 0 else self._part_stream(i - 1)
+                    if i:
+                        ps.wait_event(forked)
+                    with torch.cuda.stream(ps):
+                        s = _stream()
+                        launch_project(a, b, s)
+                        launch_fit(a, b, s)
+                        ps.wait_event(zero_done)
+                        launch_mask_range(a, b, stats_mode, s, ws.data_ptr() + ws_part[i] if use_stats else 0, True)
+                        if i:
+                            e = torch.cuda.Event()
+                            e.record(ps)
+                            joined.append(e)
+                for e in joined:
+                    main.wait_event(e)
+                launch_scan()
+                return
+            zeroed = prezeroed[0]
+            if zeroed:
+                main.wait_event(zero_done)
+                prezeroed[0] = False
+            # (not zeroed: the exact-statistics retry fills again, in stream order)
+            launch_mask_range(0, V, stats_mode, st, ws.data_ptr() if use_stats else 0, zeroed)
+            launch_scan()
 
         def mask_stage(stats_mode: int, speculate: bool = False):
             """launch_mask + the read-back of (total, retry); returns (total, retry, spec)."""

@@ -125,12 +125,15 @@ class SfmTable:
 @torch.no_grad()
 def points_from_views(config, depths, masks, images, K, c2w, names, points: np.ndarray, point_indices: dict,
                       device, image_kind: int = L.IMAGE_F32_255, sample_idx: Optional[torch.Tensor] = None,
-                      sfm: Optional[SfmTable] = None, exchange=None, defer_emit: bool = False):
+                      sfm: Optional[SfmTable] = None, exchange=None, defer_emit: bool = False,
+                      streams: Optional[int] = None):
     """The batched hot path.  depths / masks / images: stacked tensors or per-view lists; images
     are [H,W,3] float32 0..255 or uint8, on the device or in pinned host memory.  `sfm` is an
     already uploaded SfmTable of (points, point_indices, names); built here when omitted.
     `exchange` (distributed.CloudExchange, one per rank): this rank's views are emitted into every
     rank's cloud, and xyz / rgb of the result are the whole scene (see distributed.py).
+    `streams`: number of contiguous view ranges queued on separate CUDA streams (engine.py; None = the
+    MDI_STREAMS default); the result does not depend on it.
     Returns the engine RunResult (xyz / rgb on the device)."""
     eng = get_engine(device)
     dev = eng.device
@@ -144,6 +147,7 @@ def points_from_views(config, depths, masks, images, K, c2w, names, points: np.n
             opt.ransac_seed = ransac_seed()
     opt.exchange = exchange
     opt.defer_emit = bool(defer_emit)
+    opt.streams = streams
     vin = ViewInputs(depth=depths, mask=masks, image=images, image_kind=image_kind, K=K, c2w=c2w,
                      sfm_xyz=sfm.xyz, sfm_index=sfm.index, sfm_counts=sfm.counts)
     if config.mdi.alignment.segmenter is not None:   # region-wise alignment: aligned map materialised per view

@@ -122,7 +122,9 @@ typedef struct MdiRansacConfig {
   int32_t sample_size;    /* must be 4 when sample_idx is generated on device; <= 8 otherwise */
   int32_t min_iters;
   int32_t loss_kind;      /* MDI_LOSS_*                                        */
-  int32_t _pad;
+  int32_t view_base;      /* index of views[0] in the caller's batch: the device sampler draws for
+                             view view_base + v, so a batch launched as several view ranges (one per
+                             stream) draws the samples of one launch over all views; 0 otherwise */
   uint64_t seed;          /* device sampler seed when sample_idx == NULL       */
 } MdiRansacConfig;
 
