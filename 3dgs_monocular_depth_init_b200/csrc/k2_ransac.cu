@@ -1,15 +1,24 @@
 // k2_ransac.cu -- LO-RANSAC / MSAC scale-shift fit (a4).  Reference: ransacs.py:100-189.
 //
-// Every per-hypothesis quantity of the reference loop (sample fit, loss, inlier set, local
-// optimisation refit, its loss and inlier count) depends only on the hypothesis' sample
-// indices, never on loop state; the loop state is a scalar scan on top.  So: one CTA per
-// view, the (d, g) pairs of the view staged once into shared memory with a 1-D bulk (TMA)
-// copy completing on an mbarrier, one warp per hypothesis scoring all points from shared
-// memory, and after each round of kWarps hypotheses one thread replays the reference's state
-// machine (first-wins `<` comparisons, adaptive stopping rule) in iteration order.
-// The local-optimisation pass is only run for hypotheses whose sample loss beats the best
-// sample loss at the start of the round (a superset of those the sequential loop refits,
-// because that bound only decreases).  Issue-bound, not HBM-bound.
+// The reference loop is sequential: draw 4 points, fit, score ALL points; only when the sample
+// loss beats the best sample loss so far, refit on the sample model's inliers (local optimisation),
+// score again, maybe accept; then test the stopping rule.  The sample fit and its loss depend only
+// on the hypothesis' sample indices, never on loop state, so a round scores 16 / 32 / 64 hypotheses
+// at once: one CTA per view (two CTAs per SM: a 200-view batch is resident at once), the (d, g)
+// pairs of the view staged once into shared memory with a 1-D bulk (TMA) copy completing on an
+// mbarrier, one warp per 1, 2 or 4 hypotheses, four points per lane and step (128-bit
+// shared-memory loads).  The reference's state machine is then replayed over the round in
+// iteration order -- by EVERY thread, redundantly, on registers (warp ballots over the round's
+// sample losses find the next hypothesis the reference would refit, the stopping iteration follows
+// from the bound in closed form), so the control flow stays uniform across the CTA and nothing is
+// broadcast.  Whenever the replay reaches a hypothesis the reference would refit -- sample loss <
+// best sample loss AT THAT ITERATION, exactly the reference's test -- the whole CTA does that refit
+// together, along with up to three likely followers (later hypotheses of the round on the falling
+// chain of sample losses: the ones the loop refits next if this one is accepted): 512 threads
+// accumulate the inlier normal equations in fp64 over ~10 points each, a block reduction, one
+// solve per candidate (one warp each, with the stopping bound of its inlier count), a second short
+// pass for the refit's loss and inlier count.  A view needs ~5 refits in all, so the scoring
+// passes are what remains.  Issue-bound, not HBM-bound.
 #include <type_traits>
 
 #include "common.cuh"
@@ -39,8 +48,10 @@ __device__ __forceinline__ void solve(const Sums& s, float* h0, float* h1) {
   solve_normal_eq(s.dd, s.d, s.n, s.dg, s.g, h0, h1);
 }
 
+constexpr int kLoBatch = 4;                           // refits the CTA does together
+
 template <bool USE_SMEM>
-__global__ void __launch_bounds__(kRansacThreads)
+__global__ void __launch_bounds__(kRansacThreads, 2)
 ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all,
               const float* __restrict__ g_all, const int32_t* __restrict__ n_valid,
               const int32_t* __restrict__ status, const int32_t* __restrict__ sample_idx,
@@ -49,18 +60,18 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
               int32_t* __restrict__ n_inliers) {
   extern __shared__ __align__(16) float s_pts[];  // d[smem_points] then g[smem_points]
   __shared__ __align__(8) unsigned long long s_bar;
-  __shared__ double s_loss_sample[kRound], s_loss_lo[kRound];
+  __shared__ double s_loss_sample[kRound];        // sample loss of the round's hypotheses
+  __shared__ float s_hs[kRound][2];               // their sample fits
+  __shared__ double s_loss_lo[kRound], s_req_lo[kRound];   // refit loss / stopping bound, where refitted
   __shared__ float s_hlo[kRound][2];
   __shared__ int s_ninl_lo[kRound];
-  __shared__ double s_best_sample, s_best_lo;
-  __shared__ float s_hbest[2];
-  __shared__ int s_have, s_done, s_last_it, s_ninl;
-  __shared__ double s_req;  // iteration at which the stopping rule fires if the best model stays
+  __shared__ double s_red[kLoBatch][kRansacWarps][6];   // per-warp partial sums of a refit batch
+  __shared__ int s_redi[kLoBatch][kRansacWarps][2];
 
   const int v = blockIdx.x;
   const int n = n_valid[v];
   const int64_t base = views[v].sfm_begin;
-  const int lane = lane_id(), warp = warp_id();
+  const int tid = threadIdx.x, lane = lane_id(), warp = warp_id();
   const bool skip = status && status[v] != MDI_STATUS_OK;
   const float thr = cfg.inlier_threshold;
   const int ss = cfg.sample_size;
@@ -68,13 +79,8 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
   const float* dg = d_all + base;
   const float* gg = g_all + base;
 
-  if (threadIdx.x == 0) {
-    s_best_sample = INFINITY; s_best_lo = INFINITY;
-    s_hbest[0] = NAN; s_hbest[1] = NAN;
-    s_have = 0; s_done = 0; s_last_it = cfg.max_iters - 1; s_ninl = 0; s_req = INFINITY;
-  }
   if (skip) {
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       scale_shift[2 * v] = NAN; scale_shift[2 * v + 1] = NAN;
       n_iter[v] = 0; n_inliers[v] = 0;
     }
@@ -90,12 +96,12 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
     const bool tma_ok = bytes > 0 && ((reinterpret_cast<uintptr_t>(dg) & 15) == 0) &&
                         ((reinterpret_cast<uintptr_t>(gg) & 15) == 0);
     if (tma_ok) {
-      if (threadIdx.x == 0) {
+      if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       }
       __syncthreads();
-      if (threadIdx.x == 0) {
+      if (tid == 0) {
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                      ::"r"(smem_u32(&s_bar)), "r"(2 * bytes) : "memory");
         asm volatile(
@@ -115,23 +121,25 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
             : "=r"(ok) : "r"(smem_u32(&s_bar)), "r"(0u) : "memory");
       }
     } else {
-      for (int i = threadIdx.x; i < n; i += blockDim.x) { sd[i] = dg[i]; sg[i] = gg[i]; }
+      for (int i = tid; i < n; i += blockDim.x) { sd[i] = dg[i]; sg[i] = gg[i]; }
     }
     dp = sd; gp = sg;
   }
   __syncthreads();
+  // four points per lane and step where both arrays can be read as 16-byte vectors (always in
+  // shared memory; the global-memory fallback of very large views only if the slots happen to be aligned)
+  const bool vec = ((reinterpret_cast<uintptr_t>(dp) | reinterpret_cast<uintptr_t>(gp)) & 15) == 0;
 
   const int n_samp = ss < n ? ss : n;
-  // One round = KH hypotheses per warp.  The first round takes one per warp (16 hypotheses): with a
-  // healthy inlier ratio the stopping rule fires after a handful of iterations, and a 64-wide
-  // round would score 50+ hypotheses nobody asks for; later rounds take 1, 2 or kHyp per warp,
-  // whatever covers the iterations the stopping rule still requires.
-  auto round = [&](auto kh_c, const int round0) {
+  // ---- scoring pass of one round: KH hypotheses per warp --------------------------------------
+  // The first round takes one per warp (16 hypotheses): with a healthy inlier ratio the stopping
+  // rule fires after a handful of iterations, and a 64-wide round would score 50+ hypotheses
+  // nobody asks for; later rounds take 1, 2 or kHyp per warp, whatever covers the iterations the
+  // stopping rule still requires.
+  auto score_round = [&](auto kh_c, const int round0) {
     constexpr int KH = decltype(kh_c)::value;
-    constexpr int HR = kRansacWarps * KH;
     const int it0 = round0 + warp * KH;   // this warp's hypotheses: it0 .. it0 + KH - 1
-    const double cutoff = s_best_sample;
-    // ---- sample fits: lane k < KH fits hypothesis it0 + k, then broadcasts it --------------
+    // sample fits: lane k < KH fits hypothesis it0 + k, then broadcasts it
     float hs0 = 0.f, hs1 = 0.f;
     if (lane < KH && it0 + lane < cfg.max_iters) {
       const int it = it0 + lane;
@@ -160,6 +168,7 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
         }
       }
       solve(sm, &hs0, &hs1);
+      s_hs[warp * KH + lane][0] = hs0; s_hs[warp * KH + lane][1] = hs1;
     }
     float h0[KH], h1[KH];
     bool act[KH];
@@ -169,161 +178,214 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
       h1[k] = __shfl_sync(0xffffffffu, hs1, k);
       act[k] = it0 + k < cfg.max_iters;
     }
-    // ---- phase A: sample loss of the KH hypotheses; inlier normal equations of the candidates ---
-    // Only a hypothesis whose sample loss beats the best one so far is ever refitted, and after
-    // the first round that is a few per round: the 5 double-precision sums per (point, hypothesis)
-    // are left to a second pass over the candidates alone.  While there is nothing to beat yet
-    // (first round) every hypothesis is a candidate and one fused pass does both.
-    const bool fused = !(cutoff < (double)INFINITY);
-    Sums in[KH];
     int n_out[KH];
     double msac[KH];
 #pragma unroll
-    for (int k = 0; k < KH; ++k) { in[k] = {0, 0, 0, 0, 0}; n_out[k] = 0; msac[k] = 0.0; }
+    for (int k = 0; k < KH; ++k) { n_out[k] = 0; msac[k] = 0.0; }
+    auto score_point = [&](const float dv, const float gv) {
+#pragma unroll
+      for (int k = 0; k < KH; ++k) {
+        const float r = residual_sq(h0[k], h1[k], dv, gv);
+        if (r >= thr) ++n_out[k];
+        if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
+      }
+    };
     if (act[0]) {
-      if (fused) {
-        for (int i = lane; i < n; i += 32) {
-          const float dv = dp[i], gv = gp[i];
-          const double dd = (double)dv, gd = (double)gv;
-          const double ddd = dd * dd, ddg = dd * gd;
-#pragma unroll
-          for (int k = 0; k < KH; ++k) {
-            const float r = residual_sq(h0[k], h1[k], dv, gv);
-            if (r < thr) { in[k].dd += ddd; in[k].d += dd; in[k].n += 1.0; in[k].dg += ddg; in[k].g += gd; }
-            if (r >= thr) ++n_out[k];
-            if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
-          }
+      if (vec) {
+        const int n4 = n & ~3;
+        for (int i0 = 4 * lane; i0 < n4; i0 += 128) {
+          const float4 d4 = *reinterpret_cast<const float4*>(dp + i0);
+          const float4 g4 = *reinterpret_cast<const float4*>(gp + i0);
+          score_point(d4.x, g4.x); score_point(d4.y, g4.y); score_point(d4.z, g4.z); score_point(d4.w, g4.w);
         }
+        if (n4 + lane < n) score_point(dp[n4 + lane], gp[n4 + lane]);   // last n % 4 points
       } else {
-        for (int i = lane; i < n; i += 32) {
-          const float dv = dp[i], gv = gp[i];
-#pragma unroll
-          for (int k = 0; k < KH; ++k) {
-            const float r = residual_sq(h0[k], h1[k], dv, gv);
-            if (r >= thr) ++n_out[k];
-            if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
-          }
-        }
+        for (int i = lane; i < n; i += 32) score_point(dp[i], gp[i]);
       }
     }
-    bool candk[KH];
-    bool any_cand = false;
-    double loss_s_mine = INFINITY;
 #pragma unroll
     for (int k = 0; k < KH; ++k) {
       double ls;
       if (msac_loss) ls = (double)(float)warp_sum_f64(msac[k]);
       else ls = (double)warp_sum_i32(n_out[k]);
-      candk[k] = act[k] && ls < cutoff;   // warp-uniform
-      any_cand = any_cand || candk[k];
-      if (lane == k) loss_s_mine = act[k] ? ls : INFINITY;
+      if (lane == 0) s_loss_sample[warp * KH + k] = act[k] ? ls : (double)INFINITY;
     }
-    if (!fused && any_cand) {
-      for (int i = lane; i < n; i += 32) {
+  };
+
+  // ---- local optimisation of hypotheses b[0..nb) of the round, by the whole CTA (ransacs.py:142-146):
+  // least squares over the inliers of the sample model, then loss / inlier count of the refit.
+  // b / nb are the same in every thread; four barriers, all in uniform control flow ------------
+  auto refit_batch = [&](const int (&bt)[kLoBatch], const int nb) {
+#pragma unroll 1
+    for (int c = 0; c < nb; ++c) {
+      const int w = bt[c];
+      const float a0 = s_hs[w][0], a1 = s_hs[w][1];
+      Sums in = {0, 0, 0, 0, 0};
+      for (int i = tid; i < n; i += kRansacThreads) {
         const float dv = dp[i], gv = gp[i];
-        const double dd = (double)dv, gd = (double)gv;
-        const double ddd = dd * dd, ddg = dd * gd;
-#pragma unroll
-        for (int k = 0; k < KH; ++k) {
-          if (!candk[k]) continue;
-          const float r = residual_sq(h0[k], h1[k], dv, gv);
-          if (r < thr) { in[k].dd += ddd; in[k].d += dd; in[k].n += 1.0; in[k].dg += ddg; in[k].g += gd; }
+        if (residual_sq(a0, a1, dv, gv) < thr) {
+          const double dd = (double)dv, gd = (double)gv;
+          in.dd += dd * dd; in.d += dd; in.n += 1.0; in.dg += dd * gd; in.g += gd;
         }
       }
-    }
-    float hl0 = 0.f, hl1 = 0.f;   // lane k keeps the local-optimisation fit of hypothesis k
-#pragma unroll
-    for (int k = 0; k < KH; ++k) {
-      if (!candk[k]) continue;
-      Sums t;
-      t.dd = warp_sum_f64(in[k].dd); t.d = warp_sum_f64(in[k].d); t.n = warp_sum_f64(in[k].n);
-      t.dg = warp_sum_f64(in[k].dg); t.g = warp_sum_f64(in[k].g);
-      if (lane == k) solve(t, &hl0, &hl1);
-    }
-    if (lane < KH && it0 + lane < cfg.max_iters) {
-      s_loss_sample[warp * KH + lane] = loss_s_mine;
-      s_hlo[warp * KH + lane][0] = hl0; s_hlo[warp * KH + lane][1] = hl1;
-    }
-    // ---- phase B: local-optimisation loss of the candidates --------------------------------------
-#pragma unroll
-    for (int k = 0; k < KH; ++k) {
-      h0[k] = __shfl_sync(0xffffffffu, hl0, k);
-      h1[k] = __shfl_sync(0xffffffffu, hl1, k);
-      n_out[k] = 0; msac[k] = 0.0;
-    }
-    int n_in[KH];
-#pragma unroll
-    for (int k = 0; k < KH; ++k) n_in[k] = 0;
-    if (any_cand) {
-      for (int i = lane; i < n; i += 32) {
-        const float dv = dp[i], gv = gp[i];
-#pragma unroll
-        for (int k = 0; k < KH; ++k) {
-          if (!candk[k]) continue;  // warp-uniform
-          const float r = residual_sq(h0[k], h1[k], dv, gv);
-          if (r < thr) ++n_in[k];
-          if (r >= thr) ++n_out[k];
-          if (msac_loss) msac[k] += (r != r) ? (double)NAN : (double)fminf(r, thr);
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < KH; ++k) {
-        if (!candk[k]) continue;
-        const int ni = warp_sum_i32(n_in[k]);
-        double loss_lo;
-        if (msac_loss) loss_lo = (double)(float)warp_sum_f64(msac[k]);
-        else loss_lo = (double)warp_sum_i32(n_out[k]);
-        if (lane == 0) { s_loss_lo[warp * KH + k] = loss_lo; s_ninl_lo[warp * KH + k] = ni; }
+      in.dd = warp_sum_f64(in.dd); in.d = warp_sum_f64(in.d); in.n = warp_sum_f64(in.n);
+      in.dg = warp_sum_f64(in.dg); in.g = warp_sum_f64(in.g);
+      if (lane == 0) {
+        double* o = s_red[c][warp];
+        o[0] = in.dd; o[1] = in.d; o[2] = in.n; o[3] = in.dg; o[4] = in.g;
       }
     }
     __syncthreads();
-    // ---- replay of the sequential state machine (ransacs.py:141-162) --------------------------
-    if (threadIdx.x == 0) {
-      // the stopping bound only changes when the best model does
-      double req = s_have ? required_samples((int64_t)s_ninl, (int64_t)n, ss, cfg.confidence) : 0.0;
-      for (int w = 0; w < HR; ++w) {
-        const int itw = round0 + w;
-        if (itw >= cfg.max_iters) break;
-        if (s_loss_sample[w] < s_best_sample) {
-          if (s_loss_lo[w] < s_best_lo) {
-            s_hbest[0] = s_hlo[w][0]; s_hbest[1] = s_hlo[w][1];
-            s_best_lo = s_loss_lo[w];
-            s_best_sample = s_loss_sample[w];
-            s_ninl = s_ninl_lo[w];
-            s_have = 1;
-            req = required_samples((int64_t)s_ninl, (int64_t)n, ss, cfg.confidence);
-          }
-        }
-        if (s_have && itw >= cfg.min_iters && req <= (double)itw) {
-          s_done = 1; s_last_it = itw;
-          break;
-        }
+    if (warp < nb) {   // warp c adds up candidate c's partial sums (fixed order) and solves, all lanes alike
+      const bool has = lane < kRansacWarps;
+      Sums t;
+      t.dd = warp_sum_f64(has ? s_red[warp][lane][0] : 0.0);
+      t.d = warp_sum_f64(has ? s_red[warp][lane][1] : 0.0);
+      t.n = warp_sum_f64(has ? s_red[warp][lane][2] : 0.0);
+      t.dg = warp_sum_f64(has ? s_red[warp][lane][3] : 0.0);
+      t.g = warp_sum_f64(has ? s_red[warp][lane][4] : 0.0);
+      float b0, b1;
+      solve(t, &b0, &b1);
+      if (lane == 0) { s_hlo[bt[warp]][0] = b0; s_hlo[bt[warp]][1] = b1; }
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int c = 0; c < nb; ++c) {
+      const int w = bt[c];
+      const float b0 = s_hlo[w][0], b1 = s_hlo[w][1];
+      int n_in = 0, n_out = 0;
+      double ms = 0.0;
+      for (int i = tid; i < n; i += kRansacThreads) {
+        const float r = residual_sq(b0, b1, dp[i], gp[i]);
+        if (r < thr) ++n_in;
+        if (r >= thr) ++n_out;
+        if (msac_loss) ms += (r != r) ? (double)NAN : (double)fminf(r, thr);
       }
-      s_req = s_have ? fmax(req, (double)cfg.min_iters) : INFINITY;
+      n_in = warp_sum_i32(n_in); n_out = warp_sum_i32(n_out);
+      if (msac_loss) ms = warp_sum_f64(ms);
+      if (lane == 0) { s_redi[c][warp][0] = n_in; s_redi[c][warp][1] = n_out; s_red[c][warp][5] = ms; }
+    }
+    __syncthreads();
+    if (warp < nb) {
+      const bool has = lane < kRansacWarps;
+      const int ni = warp_sum_i32(has ? s_redi[warp][lane][0] : 0);
+      const int no = warp_sum_i32(has ? s_redi[warp][lane][1] : 0);
+      double ms = 0.0;
+      if (msac_loss) ms = warp_sum_f64(has ? s_red[warp][lane][5] : 0.0);
+      const double rq = required_samples((int64_t)ni, (int64_t)n, ss, cfg.confidence);
+      if (lane == 0) {
+        const int w = bt[warp];
+        s_loss_lo[w] = msac_loss ? (double)(float)ms : (double)no;
+        s_ninl_lo[w] = ni;
+        s_req_lo[w] = rq;
+      }
     }
     __syncthreads();
   };
+
+  // ---- state of the reference's loop (ransacs.py:120-162), the same in every thread ------------
+  double best_sample = INFINITY, best_lo = INFINITY;
+  double req = 0.0;             // required_samples() of the current best model
+  float hb0 = NAN, hb1 = NAN;
+  int have = 0, ninl = 0, last_it = cfg.max_iters - 1;
+  bool done = false;
+
   int round0 = 0;
-  if (cfg.max_iters > 0) { round(std::integral_constant<int, 1>{}, 0); round0 = kRansacWarps; }
-  while (!s_done && round0 < cfg.max_iters) {
-    // size the round to what the stopping rule still asks for with the current best model
-    const double need = s_req - (double)round0 + 1.0;
+  bool first = true;
+  while (!done && round0 < cfg.max_iters) {
+    // size the round to what the stopping rule still asks for with the current best model (the
+    // first round: one hypothesis per warp)
+    const double stop_at = have ? fmax(req, (double)cfg.min_iters) : (double)INFINITY;
+    const double need = first ? 0.0 : stop_at - (double)round0 + 1.0;
+    first = false;
+    int hr;
     if (need <= (double)kRansacWarps) {
-      round(std::integral_constant<int, 1>{}, round0); round0 += kRansacWarps;
+      score_round(std::integral_constant<int, 1>{}, round0); hr = kRansacWarps;
     } else if (need <= (double)(2 * kRansacWarps)) {
-      round(std::integral_constant<int, 2>{}, round0); round0 += 2 * kRansacWarps;
+      score_round(std::integral_constant<int, 2>{}, round0); hr = 2 * kRansacWarps;
     } else {
-      round(std::integral_constant<int, kHyp>{}, round0); round0 += kRound;
+      score_round(std::integral_constant<int, kHyp>{}, round0); hr = kRound;
     }
+    __syncthreads();
+    // ---- replay of the sequential loop over the round's hr hypotheses (ransacs.py:141-162) ----
+    // lane l holds the sample losses of hypotheses l and l + 32 (+inf beyond the round / max_iters)
+    const double ls_a = lane < hr ? s_loss_sample[lane] : (double)INFINITY;
+    const double ls_b = lane + 32 < hr ? s_loss_sample[lane + 32] : (double)INFINITY;
+    auto loss_of = [&](const int w) {   // sample loss of hypothesis w of the round, w uniform
+      const double x = (w & 32) ? ls_b : ls_a;
+      return __hiloint2double(__shfl_sync(0xffffffffu, __double2hiint(x), w & 31),
+                              __shfl_sync(0xffffffffu, __double2loint(x), w & 31));
+    };
+    auto below = [&](const double bound, const int from) {   // hypotheses >= from with sample loss < bound
+      const uint64_t m = ((uint64_t)__ballot_sync(0xffffffffu, ls_b < bound) << 32) | __ballot_sync(0xffffffffu, ls_a < bound);
+      return from >= 64 ? 0ull : (m & (~0ull << from));
+    };
+    uint64_t lo_mask = 0;   // hypotheses of this round whose refit is in s_*_lo
+    int pos = 0;
+#pragma unroll 1
+    for (;;) {
+      // next hypothesis the reference refits, and the first iteration at which its stopping rule
+      // fires while the best model stays what it is: `req <= it` is monotone in it
+      const uint64_t cand = below(best_sample, pos);
+      const int w_c = cand ? __ffsll((long long)cand) - 1 : hr;
+      int w_s = hr;
+      if (have && req == req) {
+        const double t = fmax(fmax(ceil(req), (double)cfg.min_iters) - (double)round0, (double)pos);
+        if (t < (double)hr) w_s = (int)t;
+      }
+      if (w_s < w_c) {   // the loop stops before it refits again (iterations past max_iters do not exist)
+        if (round0 + w_s < cfg.max_iters) { done = true; last_it = round0 + w_s; }
+        break;
+      }
+      if (w_c >= hr) break;
+      if (!((lo_mask >> w_c) & 1ull)) {
+        // the whole CTA refits it, with the later hypotheses of the round that the loop refits too if
+        // this one is accepted (falling chain of sample losses)
+        int bt[kLoBatch];
+        int nb = 1;
+        bt[0] = w_c;
+#pragma unroll
+        for (int c = 1; c < kLoBatch; ++c) bt[c] = 0;
+        double m = loss_of(w_c);
+        int last = w_c;
+#pragma unroll 1
+        for (int tries = 0; tries < 8 && nb < kLoBatch; ++tries) {
+          const uint64_t f = below(m, last + 1);
+          if (!f) break;
+          last = __ffsll((long long)f) - 1;
+          m = loss_of(last);
+          if (!((lo_mask >> last) & 1ull)) {
+#pragma unroll
+            for (int c = 1; c < kLoBatch; ++c) if (c == nb) bt[c] = last;
+            ++nb;
+          }
+        }
+        refit_batch(bt, nb);
+#pragma unroll
+        for (int c = 0; c < kLoBatch; ++c) if (c < nb) lo_mask |= 1ull << bt[c];
+      }
+      const int itw = round0 + w_c;
+      if (s_loss_lo[w_c] < best_lo) {
+        hb0 = s_hlo[w_c][0]; hb1 = s_hlo[w_c][1];
+        best_lo = s_loss_lo[w_c];
+        best_sample = loss_of(w_c);
+        ninl = s_ninl_lo[w_c];
+        have = 1;
+        req = s_req_lo[w_c];
+      }
+      if (have && itw >= cfg.min_iters && req <= (double)itw) { done = true; last_it = itw; break; }
+      pos = w_c + 1;
+    }
+    round0 += hr;
+    __syncthreads();   // the next round rewrites s_loss_sample / s_hs
   }
 
-  const float h0 = s_hbest[0], h1 = s_hbest[1];
   if (inliers)
-    for (int i = threadIdx.x; i < n; i += blockDim.x)
-      inliers[base + i] = residual_sq(h0, h1, dp[i], gp[i]) < thr ? 1 : 0;
-  if (threadIdx.x == 0) {
-    scale_shift[2 * v] = h0; scale_shift[2 * v + 1] = h1;
-    n_iter[v] = s_last_it; n_inliers[v] = s_ninl;
+    for (int i = tid; i < n; i += blockDim.x)
+      inliers[base + i] = residual_sq(hb0, hb1, dp[i], gp[i]) < thr ? 1 : 0;
+  if (tid == 0) {
+    scale_shift[2 * v] = hb0; scale_shift[2 * v + 1] = hb1;
+    n_iter[v] = last_it; n_inliers[v] = ninl;
   }
 }
 
