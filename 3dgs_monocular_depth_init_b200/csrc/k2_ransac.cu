@@ -144,27 +144,54 @@ ransac_kernel(const MdiView* __restrict__ views, const float* __restrict__ d_all
     if (lane < KH && it0 + lane < cfg.max_iters) {
       const int it = it0 + lane;
       Sums sm = {0, 0, 0, 0, 0};
-      int chosen[kMaxSample];
-      for (int k = 0; k < n_samp; ++k) {
-        int idx;
-        if (sample_idx) {
-          idx = sample_idx[((int64_t)v * cfg.max_iters + it) * ss + k];
-        } else {
-          // k-th of n_samp distinct uniform indices (randperm(n)[:ss] in distribution)
-          uint64_t ctr = 0;
-          bool dup;
-          do {
-            const uint64_t r = splitmix64(cfg.seed ^ splitmix64(((uint64_t)(uint32_t)(v + cfg.view_base) << 40) ^ ((uint64_t)it << 8) ^ (uint64_t)k ^ (ctr << 56)));
-            idx = (int)(r % (uint64_t)n);
-            dup = false;
-            for (int j = 0; j < k; ++j) dup |= (chosen[j] == idx);
-            ++ctr;
-          } while (dup);
-        }
-        chosen[k] = idx;
+      // k-th of n_samp distinct uniform indices (randperm(n)[:ss] in distribution): draw number
+      // `ctr` for slot k of hypothesis `it` of batch view v; a draw that repeats an earlier slot
+      // is redrawn with the next ctr
+      auto draw = [&](const int k, const uint64_t ctr) {
+        const uint64_t r = splitmix64(cfg.seed ^ splitmix64(((uint64_t)(uint32_t)(v + cfg.view_base) << 40) ^ ((uint64_t)it << 8) ^ (uint64_t)k ^ (ctr << 56)));
+        return (int)(((r >> 32) * (uint64_t)(uint32_t)n) >> 32);   // uniform in 0 .. n-1 (multiply-high)
+      };
+      auto add_point = [&](const int idx) {
         if (idx >= 0 && idx < n) {
           const double dd = (double)dp[idx], gd = (double)gp[idx];
           sm.dd += dd * dd; sm.d += dd; sm.n += 1.0; sm.dg += dd * gd; sm.g += gd;
+        }
+      };
+      bool drawn = false;
+      if (!sample_idx && n_samp == 4) {
+        // the usual case: four independent hash chains, and almost never a repeated index
+        const int i0 = draw(0, 0), i1 = draw(1, 0), i2 = draw(2, 0), i3 = draw(3, 0);
+        if (i0 != i1 && i0 != i2 && i0 != i3 && i1 != i2 && i1 != i3 && i2 != i3) {
+          const float d0 = dp[i0], d1 = dp[i1], d2 = dp[i2], d3 = dp[i3];
+          const float g0 = gp[i0], g1 = gp[i1], g2 = gp[i2], g3 = gp[i3];
+          const double e0 = d0, e1 = d1, e2 = d2, e3 = d3, f0 = g0, f1 = g1, f2 = g2, f3 = g3;
+          // same order of additions as the general loop below
+          sm.dd = ((e0 * e0 + e1 * e1) + e2 * e2) + e3 * e3;
+          sm.d = ((e0 + e1) + e2) + e3;
+          sm.n = 4.0;
+          sm.dg = ((e0 * f0 + e1 * f1) + e2 * f2) + e3 * f3;
+          sm.g = ((f0 + f1) + f2) + f3;
+          drawn = true;
+        }
+      }
+      if (!drawn) {
+        int chosen[kMaxSample];
+        for (int k = 0; k < n_samp; ++k) {
+          int idx;
+          if (sample_idx) {
+            idx = sample_idx[((int64_t)v * cfg.max_iters + it) * ss + k];
+          } else {
+            uint64_t ctr = 0;
+            bool dup;
+            do {
+              idx = draw(k, ctr);
+              dup = false;
+              for (int j = 0; j < k; ++j) dup |= (chosen[j] == idx);
+              ++ctr;
+            } while (dup);
+          }
+          chosen[k] = idx;
+          add_point(idx);
         }
       }
       solve(sm, &hs0, &hs1);
