@@ -357,15 +357,20 @@ stats_bracket_kernel(const float* __restrict__ scale_shift, const int32_t* __res
       const uint32_t i = base + u * kBracketThreads + tid;
       kk[u] = i < ns ? keys[i] : 0xFFFFFFFFu;
     }
+    // Only the robust range is binned finely: the bracket ranks (q -/+ delta) sit well inside it.
+    // Keys below it are counted into bin 102 (which then holds everything <= sort[102]), keys
+    // above it need no count at all (bin 1024, "above the last edge", is what a rank falls into
+    // when no bin claims it); a 7-step search for either would make the whole warp wait.
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      if (base + u * kBracketThreads + tid >= ns) continue;
+      const bool in = base + u * kBracketThreads + tid < ns;
       const uint32_t key = kk[u];
-      int lo, hi;
-      if (key < Rlo) { lo = 0; hi = 102; }
-      else if (key > Rhi) { lo = 921; hi = 1024; }
-      else { const uint32_t g = (key - Rlo) >> gs; lo = s_guide[g]; hi = s_guide[g + 1]; }
-      atomicAdd(&s_hist[lower_bound(key, lo, hi)], 1u);
+      const unsigned below = __ballot_sync(0xffffffffu, in && key < Rlo);
+      if (below && lane_id() == 0) atomicAdd(&s_hist[102], (uint32_t)__popc(below));
+      if (in && !(key < Rlo) && !(key > Rhi)) {
+        const uint32_t g = (key - Rlo) >> gs;
+        atomicAdd(&s_hist[lower_bound(key, s_guide[g], s_guide[g + 1])], 1u);
+      }
     }
   }
   // half-width of the rank bracket: the sample is ns / 8 sectors of 8 adjacent (correlated) pixels,
@@ -399,8 +404,10 @@ stats_bracket_kernel(const float* __restrict__ scale_shift, const int32_t* __res
     for (int g = 0; g < 2; ++g) {
       const uint32_t bl = s_bin[2 * g], bh = s_bin[2 * g + 1];
       // keys of bin b satisfy sort[b-1] < key <= sort[b]
-      uint32_t L = bl == 0 ? 0u : s_sort[bl - 1] + (s_sort[bl - 1] == 0xFFFFFFFFu ? 0u : 1u);
-      uint32_t U = bh >= 1024u ? 0xFFFFFFFFu : s_sort[bh];
+      // (merged ends: bin 102 reaches down to the smallest key, bin 1024 down to sort[921])
+      const uint32_t below_bl = bl >= 1024u ? s_sort[921] : (bl <= 102u ? 0xFFFFFFFFu : s_sort[bl - 1]);
+      uint32_t L = bl <= 102u ? 0u : below_bl + (below_bl == 0xFFFFFFFFu ? 0u : 1u);
+      uint32_t U = bh >= 1024u ? 0xFFFFFFFFu : s_sort[bh < 102u ? 102u : bh];
       if (L < kKeyNegInf) L = kKeyNegInf;
       if (U > kKeyPosInf) U = kKeyPosInf;
       s_LU[2 * g] = L; s_LU[2 * g + 1] = U >= L ? U : L;
