@@ -15,14 +15,14 @@ PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libmdi_b200.so"
 
 # ---- constants mirrored from include/mdi_b200.h ------------------------------------------------
-ABI_VERSION = 4
+ABI_VERSION = 5
 TILE_PX = 4096
 TILE_WORDS = TILE_PX // 32
 PATCH_STRIDE = 2048
 INTERP_STATIC_MAX_PX = 2 * 1024 * 1024
 FACTOR_TABLE_STRIDE = 40
 STATUS_OK, STATUS_LOW_CONFIDENCE, STATUS_EMPTY_STATS, STATUS_STATS_RETRY = 0, 1, 2, 4
-STATS_EXACT, STATS_RETRY_FLAGGED = 64, 128
+STATS_EXACT, STATS_RETRY_FLAGGED, STATS_RAW = 64, 128, 512
 IMAGE_F32_UNIT, IMAGE_F32_255, IMAGE_U8 = 0, 1, 2
 SUBSAMPLE_STATIC, SUBSAMPLE_ADAPTIVE = 0, 1
 KEEP_PRED_MASK, KEEP_SENTINEL, KEEP_NONNEG, KEEP_PATCH, KEEP_GRAD, KEEP_SUBSAMPLE = 1, 2, 4, 8, 16, 32
@@ -81,6 +81,7 @@ _SIGNATURES = {
     "mdi_apply_region_scale_shift": (_INT, [_P, _P, _I64, _P, _P, _INT, _P, _P]),
     "mdi_depth_range_workspace_bytes": (_I64, [_INT, _I64]),
     "mdi_depth_range": (_INT, [_P, _INT, _I64, _P, _P, _INT, _P, _P, _P, _P, _P]),
+    "mdi_depth_range_map": (_INT, [_INT, _I64, _P, _P, _INT, _P, _P, _P, _P, _P]),
     "mdi_grad_range": (_INT, [_P, _INT, _I64, _P, _P, _P, _P]),
     "mdi_factor_table": (_INT, [_INT, _P, _INT, _INT, _P, _P]),
     "mdi_keep_mask": (_INT, [_P, _INT, _I64, _I64, _INT, _INT, _P, _P, _P, _P, _P, _P, C.POINTER(SubsampleConfigC), _P, _P, _P, _P]),

@@ -24,39 +24,70 @@ project_filter_kernel(const MdiView* __restrict__ views, const float* __restrict
   if (threadIdx.x == 0) s_inb = 0;
   __syncthreads();
 
+  // Four consecutive points per thread and step: the index, coordinate and mask loads of a step are
+  // dependent gathers (index -> xyz -> pixel of the mask), so the four chains of a thread and the
+  // 2048 of the CTA are in flight together and a 6000-point view takes three round trips per stage
+  // instead of twelve.  The ordered compaction ranks a thread's points behind the block scan of the
+  // per-thread counts.
+  constexpr int kPer = 4;
+  const bool idx_vec = sfm_index && ((reinterpret_cast<uintptr_t>(sfm_index + base) & 15) == 0);
   int out_base = 0, inb_local = 0;
-  for (int start = 0; start < M; start += blockDim.x) {
-    const int i = start + threadIdx.x;
-    bool ok = false;
-    int iu = 0, iv = 0;
-    float zc = 0.f;
-    if (i < M) {
-      const int64_t src = sfm_index ? (int64_t)sfm_index[base + i] : (base + i);
-      const float X = sfm_xyz[3 * src + 0], Y = sfm_xyz[3 * src + 1], Z = sfm_xyz[3 * src + 2];
+  for (int start = 0; start < M; start += kPer * (int)blockDim.x) {
+    const int i0 = start + kPer * (int)threadIdx.x;
+    int64_t src[kPer];
+    if (idx_vec && i0 + kPer <= M) {
+      const int4 q = *reinterpret_cast<const int4*>(sfm_index + base + i0);
+      src[0] = q.x; src[1] = q.y; src[2] = q.z; src[3] = q.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < kPer; ++k)
+        src[k] = i0 + k < M ? (sfm_index ? (int64_t)sfm_index[base + i0 + k] : (base + i0 + k)) : 0;
+    }
+    float X[kPer], Y[kPer], Z[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const bool in = i0 + k < M;
+      X[k] = in ? sfm_xyz[3 * src[k] + 0] : 0.f;
+      Y[k] = in ? sfm_xyz[3 * src[k] + 1] : 0.f;
+      Z[k] = in ? sfm_xyz[3 * src[k] + 2] : 0.f;
+    }
+    bool ok[kPer];
+    int iu[kPer], iv[kPer];
+    float zc[kPer];
+    uint8_t mb[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
       // P @ [X;1] as the sgemm of the reference evaluates it: one FMA chain over k = 0..3
       const float* P = vw.P;
-      float cx = dot4_fma(P[0], P[1], P[2], P[3], X, Y, Z);
-      float cy = dot4_fma(P[4], P[5], P[6], P[7], X, Y, Z);
-      zc = dot4_fma(P[8], P[9], P[10], P[11], X, Y, Z);
-      float fu = rintf(fdiv(cx, zc));  // torch.round = half to even
-      float fv = rintf(fdiv(cy, zc));
+      const float cx = dot4_fma(P[0], P[1], P[2], P[3], X[k], Y[k], Z[k]);
+      const float cy = dot4_fma(P[4], P[5], P[6], P[7], X[k], Y[k], Z[k]);
+      zc[k] = dot4_fma(P[8], P[9], P[10], P[11], X[k], Y[k], Z[k]);
+      const float fu = rintf(fdiv(cx, zc[k]));  // torch.round = half to even
+      const float fv = rintf(fdiv(cy, zc[k]));
       // 0 <= u < W, 0 <= v < H, z >= 0 ; NaN / inf / out-of-int64 all fail the comparisons
-      bool inb = (fu >= 0.f) && (fu < (float)vw.W) && (fv >= 0.f) && (fv < (float)vw.H) &&
-                 (zc >= 0.f);
-      if (inb) {
-        iu = (int)fu;
-        iv = (int)fv;
-        ++inb_local;
-        ok = vw.mask ? (vw.mask[(int64_t)iv * vw.W + iu] != 0) : true;
-      }
+      const bool inb = (i0 + k < M) && (fu >= 0.f) && (fu < (float)vw.W) && (fv >= 0.f) && (fv < (float)vw.H) &&
+                       (zc[k] >= 0.f);
+      iu[k] = inb ? (int)fu : 0;
+      iv[k] = inb ? (int)fv : 0;
+      ok[k] = inb;
+      if (inb) ++inb_local;
     }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) mb[k] = (ok[k] && vw.mask) ? vw.mask[(int64_t)iv[k] * vw.W + iu[k]] : 1;
+    int mine = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) { ok[k] = ok[k] && mb[k] != 0; mine += ok[k] ? 1 : 0; }
     int total;
-    int pos = block_excl_scan(ok ? 1 : 0, scan_smem, &total);
-    if (ok) {
-      const int64_t o = base + out_base + pos;
-      uv[o] = iu;
-      uv[slots + o] = iv;
-      z_out[o] = zc;
+    int pos = block_excl_scan(mine, scan_smem, &total);
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      if (ok[k]) {
+        const int64_t o = base + out_base + pos;
+        uv[o] = iu[k];
+        uv[slots + o] = iv[k];
+        z_out[o] = zc[k];
+        ++pos;
+      }
     }
     out_base += total;
   }
@@ -91,16 +122,42 @@ gather_fit_kernel(const MdiView* __restrict__ views, int64_t slots,
   __syncthreads();
 
   double sdd = 0, sd = 0, sdg = 0, sg = 0;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const int iu = uv[base + i], iv = uv[slots + base + i];
-    const float g = z[base + i];
-    const float dv = vw.depth[(int64_t)iv * vw.W + iu];
-    d_out[base + i] = dv;
-    const double dd = (double)dv, gd = (double)g;
-    sdd += dd * dd; sd += dd; sdg += dd * gd; sg += gd;
-    if (patch_blocked) {
-      const int pr = iv / vw.patch_h, pc = iu / vw.patch_w;
-      if (pr < vw.grid_h && pc < vw.grid_w) atomicAdd(&s_hist[pr * vw.grid_w + pc], 1);
+  // r / patch_h as a multiply-high: exact because r, patch_h < 2^16 (x * d < 2^32 with M = floor(2^32 / d) + 1)
+  const bool small = vw.H < 65536 && vw.W < 65536;
+  const uint32_t mh = 0xFFFFFFFFu / (uint32_t)max(vw.patch_h, 1) + 1u, mw = 0xFFFFFFFFu / (uint32_t)max(vw.patch_w, 1) + 1u;
+  // four depth gathers of a thread in flight together (the loop is a chain of DRAM round trips otherwise);
+  // the sums keep the order i = threadIdx.x, + blockDim.x, ... of the plain loop
+  constexpr int kPer = 4;
+  for (int i0 = threadIdx.x; i0 < n; i0 += kPer * (int)blockDim.x) {
+    int iu[kPer], iv[kPer];
+    float g[kPer], dv[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = i0 + k * (int)blockDim.x;
+      const bool in = i < n;
+      iu[k] = in ? uv[base + i] : 0; iv[k] = in ? uv[slots + base + i] : 0;
+      g[k] = in ? z[base + i] : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k)
+      dv[k] = (i0 + k * (int)blockDim.x < n) ? vw.depth[(int64_t)iv[k] * vw.W + iu[k]] : 0.f;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = i0 + k * (int)blockDim.x;
+      if (i >= n) break;
+      d_out[base + i] = dv[k];
+      const double dd = (double)dv[k], gd = (double)g[k];
+      sdd += dd * dd; sd += dd; sdg += dd * gd; sg += gd;
+      if (patch_blocked) {
+        int pr, pc;
+        if (small) {
+          pr = vw.patch_h <= 1 ? iv[k] : (int)__umulhi((uint32_t)iv[k], mh);
+          pc = vw.patch_w <= 1 ? iu[k] : (int)__umulhi((uint32_t)iu[k], mw);
+        } else {
+          pr = iv[k] / vw.patch_h; pc = iu[k] / vw.patch_w;
+        }
+        if (pr < vw.grid_h && pc < vw.grid_w) atomicAdd(&s_hist[pr * vw.grid_w + pc], 1);
+      }
     }
   }
   sdd = warp_sum_f64(sdd); sd = warp_sum_f64(sd); sdg = warp_sum_f64(sdg); sg = warp_sum_f64(sg);

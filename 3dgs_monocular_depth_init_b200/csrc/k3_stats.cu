@@ -61,7 +61,11 @@ struct StatsHdr {
   uint32_t force_retry; // set by the depth-domain loop: NaN / inf in the population or a pixel that may hit the sentinel
   float d_lo[2], d_hi[2];
   float ds_lo, ds_hi;   // depths whose aligned value is exactly -42.0 (empty when ds_lo > ds_hi)
+  // MDI_STATS_RAW: what stats_finish_kernel found on the raw depth, for stats_map_kernel
+  uint32_t raw_state;   // kRaw*
+  float raw_val[kTargets], raw_min, raw_max;
 };
+constexpr uint32_t kRawNone = 0, kRawOk = 1, kRawEmpty = 2, kRawFail = 3, kRawNan = 4;
 
 struct StatsWs {
   StatsHdr* hdr;       // [V]
@@ -926,7 +930,7 @@ __device__ __forceinline__ void write_range(int v, const float val[kTargets], fl
 
 __global__ void __launch_bounds__(kSelThreads, 2)
 stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict__ lo_hi,
-                    float* __restrict__ quantiles, int64_t* __restrict__ retry_flag) {
+                    float* __restrict__ quantiles, int64_t* __restrict__ retry_flag, int raw) {
   // the in-bin lists and the radix-select fallback share one buffer
   __shared__ __align__(16) unsigned char s_raw[sizeof(SelShared) > sizeof(uint32_t) * kTargets * kListCap
                                                    ? sizeof(SelShared) : sizeof(uint32_t) * kTargets * kListCap];
@@ -939,6 +943,10 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
   StatsHdr* h = ws.hdr + v;
   const bool low_conf = status && (status[v] & MDI_STATUS_LOW_CONFIDENCE);
   const uint32_t n = h->count;
+  if (raw && n == 0) {   // MDI_STATS_RAW: the verdict is stats_map_kernel's
+    if (tid == 0) h->raw_state = kRawEmpty;
+    return;
+  }
   if (low_conf || n == 0) {
     if (tid == 0) {
       if (lo_hi) { lo_hi[2 * v] = 0.f; lo_hi[2 * v + 1] = 0.f; }
@@ -1044,7 +1052,16 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
       __syncthreads();
     }
   }
-  if (tid == 0) {
+  if (tid == 0 && raw) {
+    h->fail_code = s_fail;
+    if (s_fail) {
+      h->raw_state = kRawFail;
+    } else {
+      for (int j = 0; j < kTargets; ++j) h->raw_val[j] = key_to_float(s_out[j]);
+      h->raw_min = key_to_float(h->min_key); h->raw_max = key_to_float(h->max_key);
+      h->raw_state = has_nan ? kRawNan : kRawOk;
+    }
+  } else if (tid == 0) {
     h->fail_code = s_fail;
     if (s_fail) {
       if (lo_hi) { lo_hi[2 * v] = NAN; lo_hi[2 * v + 1] = NAN; }
@@ -1056,6 +1073,75 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
       write_range(v, val, r1.w, r3.w, h->min_key, has_nan ? 0xFFFFFFFFu : h->max_key, lo_hi, quantiles);
     }
   }
+}
+
+// MDI_STATS_RAW, second half.  Order statistics commute with a monotone map: with a finite scale > 0
+// and a finite shift, F(d) = fl(fl(d * s) + t) is non-decreasing in d, so the k-th smallest ALIGNED
+// value of a view is F(k-th smallest raw depth), whatever the fit turns out to be -- the whole
+// statistics pass can run on the raw depth, beside the alignment kernels, and this kernel (one
+// thread per view, after both) maps its six numbers through the fit and finishes like
+// stats_finish_kernel: torch.quantile's lerp, the IQR clamp, MDI_STATUS_EMPTY_STATS.  What the raw
+// pass cannot know is handed to the exact path (MDI_STATUS_STATS_RETRY, *retry_flag): a fit that is
+// not increasing, and a view in which some depth of the population's range aligns to exactly -42.0,
+// the sentinel the population excludes (sentinel != 0).
+__global__ void stats_map_kernel(int n_views, const float* __restrict__ scale_shift, int32_t* __restrict__ status,
+                                 int sentinel, StatsWs ws, float* __restrict__ lo_hi,
+                                 float* __restrict__ quantiles, int64_t* __restrict__ retry_flag) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_views) return;
+  StatsHdr* h = ws.hdr + v;
+  const bool low_conf = status && (status[v] & MDI_STATUS_LOW_CONFIDENCE);
+  const uint32_t state = h->raw_state;
+  auto put = [&](float lo, float hi, float q1, float q3, float mn, float mx) {
+    if (lo_hi) { lo_hi[2 * v] = lo; lo_hi[2 * v + 1] = hi; }
+    if (quantiles) { quantiles[4 * v] = q1; quantiles[4 * v + 1] = q3; quantiles[4 * v + 2] = mn; quantiles[4 * v + 3] = mx; }
+  };
+  if (low_conf || state == kRawEmpty) {
+    put(0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
+    if (!low_conf && status) status[v] |= MDI_STATUS_EMPTY_STATS;
+    return;
+  }
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  bool retry = state != kRawOk && state != kRawNan;
+  if (!(s > 0.f && s < INFINITY && fabsf(t) < INFINITY)) retry = true;
+  auto F = [&](uint32_t kd) { return fast_key(align_depth(key_to_float(kd), s, t)); };
+  if (!retry && sentinel && state == kRawOk) {
+    // [d_a, d_b] = the depths that align to exactly -42.0: smallest kd with F(kd) >= key(-42), largest
+    // with F(kd) <= key(-42); both exist for an increasing F.  A 33-float window around (-42 - t) / s first.
+    const uint32_t bound = fast_key(-42.0f);
+    const float guess = fdiv(fsub(-42.0f, t), s);
+    uint32_t wlo = kKeyNegInf, whi = kKeyPosInf;
+    if (guess == guess) {
+      const uint32_t kg = fast_key(guess);
+      if (kg > kKeyNegInf + 16u && kg < kKeyPosInf - 16u) { wlo = kg - 16u; whi = kg + 16u; }
+    }
+    uint32_t lo = kKeyNegInf, hi = kKeyPosInf;
+    if (wlo != kKeyNegInf && F(whi) >= bound && F(wlo) < bound) { lo = wlo + 1u; hi = whi; }
+    while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if (F(mid) >= bound) hi = mid; else lo = mid + 1; }
+    const uint32_t ka = lo;
+    lo = kKeyNegInf; hi = kKeyPosInf;
+    if (wlo != kKeyNegInf && F(wlo) <= bound && F(whi) > bound) { lo = wlo; hi = whi - 1u; }
+    while (lo < hi) { const uint32_t mid = lo + ((hi - lo + 1) >> 1); if (F(mid) <= bound) lo = mid; else hi = mid - 1; }
+    const uint32_t kb = lo;
+    // compared as floats (the raw pass does not tell -0 from +0)
+    const float da = key_to_float(ka), db = key_to_float(kb);
+    if (da <= db && h->raw_min <= db && h->raw_max >= da) retry = true;
+  }
+  if (retry) {
+    put(NAN, NAN, NAN, NAN, NAN, NAN);
+    if (status) status[v] |= MDI_STATUS_STATS_RETRY;
+    if (retry_flag) *retry_flag = 1;
+    return;
+  }
+  const uint32_t n = h->count;
+  const QuantileRank r1 = quantile_rank(0.25f, (int64_t)n);
+  const QuantileRank r3 = quantile_rank(0.75f, (int64_t)n);
+  float val[kTargets];
+  for (int j = 0; j < kTargets; ++j) val[j] = align_depth(h->raw_val[j], s, t);
+  // monotone alignment: the extreme aligned values are those of the extreme depths
+  const uint32_t kmn = fast_key(align_depth(h->raw_min, s, t)), kmx = fast_key(align_depth(h->raw_max, s, t));
+  write_range(v, val, r1.w, r3.w, kmn, state == kRawNan ? 0xFFFFFFFFu : kmx, lo_hi, quantiles);
 }
 
 // ---- exact path: radix select over all pixels ------------------------------------------------------
@@ -1296,13 +1382,16 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
   using namespace mdi;
   MDI_REQUIRE(n_views >= 0 && max_tiles_per_view >= 0, "mdi_depth_range: negative size");
   if (n_views == 0) return MDI_OK;
-  MDI_REQUIRE(views && workspace && (lo_hi || quantiles), "mdi_depth_range: null pointer");
+  MDI_REQUIRE(views && workspace && (lo_hi || quantiles || (flags & MDI_STATS_RAW)), "mdi_depth_range: null pointer");
   MDI_REQUIRE(n_views <= 65535, "mdi_depth_range: more than 65535 views per call");
   if (max_tiles_per_view < 1) max_tiles_per_view = 1;
   cudaStream_t st = (cudaStream_t)stream;
   const StatsWs ws = carve(workspace, n_views, max_tiles_per_view);
   const int mode = (flags & MDI_STATS_EXACT) ? 1 : ((flags & MDI_STATS_RETRY_FLAGGED) ? 2 : 0);
-  const int pop = flags & (MDI_KEEP_PRED_MASK | MDI_KEEP_SENTINEL);
+  const bool raw = (flags & MDI_STATS_RAW) != 0;
+  MDI_REQUIRE(!raw || mode == 0, "mdi_depth_range: MDI_STATS_RAW goes with the one-pass algorithm only");
+  if (raw) { scale_shift = nullptr; status = nullptr; }   // raw depth, every view: the fit and the status may not exist yet
+  const int pop = flags & (MDI_KEEP_PRED_MASK | (raw ? 0 : MDI_KEEP_SENTINEL));
   MDI_CUDA(cudaMemsetAsync(ws.hdr, 0, sizeof(StatsHdr) * (size_t)n_views, st), "mdi_depth_range");
   mdi::prof_mark("stats_init_kernel", st);
   stats_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(ws.hdr, n_views, status, mode);
@@ -1347,7 +1436,7 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     else if (se) stats_main_kernel<false, true><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws, prefetch_ahead);
     else stats_main_kernel<false, false><<<grid, kStatsThreads, 0, st>>>(views, scale_shift, status, ws, prefetch_ahead);
     mdi::prof_mark("stats_finish_kernel", st);
-    stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag);
+    stats_finish_kernel<<<n_views, kSelThreads, 0, st>>>(status, ws, lo_hi, quantiles, retry_flag, raw ? 1 : 0);
   } else {
     // per device (context) attribute: set on every call (microseconds), never cached process-wide
     MDI_CUDA(cudaFuncSetAttribute(stats_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1366,6 +1455,23 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
     stats_select_kernel<2><<<n_views, kStatsThreads, 0, st>>>(status, ws, lo_hi, quantiles);
   }
   MDI_CHECK_LAUNCH("mdi_depth_range");
+  return MDI_OK;
+}
+
+extern "C" int mdi_depth_range_map(int n_views, int64_t max_tiles_per_view, const float* scale_shift,
+                                   int32_t* status, int flags, void* workspace, float* lo_hi,
+                                   float* quantiles, int64_t* retry_flag, void* stream) {
+  using namespace mdi;
+  MDI_REQUIRE(n_views >= 0 && max_tiles_per_view >= 0, "mdi_depth_range_map: negative size");
+  if (n_views == 0) return MDI_OK;
+  MDI_REQUIRE(workspace && (lo_hi || quantiles), "mdi_depth_range_map: null pointer");
+  if (max_tiles_per_view < 1) max_tiles_per_view = 1;
+  const StatsWs ws = carve(workspace, n_views, max_tiles_per_view);
+  cudaStream_t st = (cudaStream_t)stream;
+  mdi::prof_mark("stats_map_kernel", st);
+  stats_map_kernel<<<(n_views + 63) / 64, 64, 0, st>>>(n_views, scale_shift, status, (flags & MDI_KEEP_SENTINEL) ? 1 : 0,
+                                                       ws, lo_hi, quantiles, retry_flag);
+  MDI_CHECK_LAUNCH("mdi_depth_range_map");
   return MDI_OK;
 }
 

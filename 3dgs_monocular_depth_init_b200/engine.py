@@ -23,6 +23,13 @@ TensorOrList = Union[torch.Tensor, Sequence[torch.Tensor]]
 # view ranges of one run queued on separate CUDA streams (RunOptions.streams overrides)
 DEFAULT_STREAMS = max(1, int(os.environ.get("MDI_STREAMS", "1") or 1))
 MIN_VIEWS_PER_RANGE = 16
+# a7 statistics on the raw depth beside the alignment kernels, which then run on a high-priority side
+# stream (mdi_depth_range with MDI_STATS_RAW + mdi_depth_range_map).  Bit-identical, but off by default
+# (MDI_RAW_STATS=1 turns it on): on C2 the two chains share the SMs poorly (1.10 instead of 1.14 ms per
+# step when no view needs the fallback), and a view whose fit is not increasing or reaches the sentinel
+# -- the garbage fits the reference's iteration-0 exit leaves in 1-3 % of the views -- sends the batch
+# through the exact-path retry (1.75 ms)
+OVERLAP_STATS = os.environ.get("MDI_RAW_STATS", "0") == "1"
 
 
 def patch_geometry(H: int, W: int, n_small: int):
@@ -89,6 +96,7 @@ class RunOptions:
     speculative_emit: bool = True                # launch a10/a11 before the output size reaches the host
     defer_emit: bool = False                     # stop after the mask; Engine.emit_deferred() writes the cloud later
     streams: Optional[int] = None                # view ranges queued on separate streams (None: MDI_STREAMS, default 1)
+    raw_stats: Optional[bool] = None             # a7 on the raw depth beside the alignment (None: MDI_RAW_STATS, default off)
 
 
 @dataclass
@@ -153,7 +161,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 # kernels launched by each C-ABI entry point (for the bench's `gpu_launches` claim)
 KERNELS_PER_CALL = {
     "mdi_setup_cameras": 1, "mdi_upload_table": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
-    "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
+    "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_depth_range_map": 1, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_capped": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
     "mdi_emit_points_exchange": 1, "mdi_exchange_counts": 1, "mdi_expand_rgb8": 1,
     "mdi_min_extents": 1,
@@ -433,6 +441,33 @@ class Engine:
             """address of view a's row in a per-view array (None stays NULL)"""
             return None if t is None else t.data_ptr() + a * per_view * t.element_size()
 
+        # ---- a7 workspaces first: with an increasing fit the order statistics of the aligned depth are the
+        # aligned order statistics of the RAW depth, so the one pass over the pixels does not have to wait
+        # for the fit -- it is queued on a side stream here and runs beside projection / fit / RANSAC
+        use_stats = bool(adaptive and (opt.flags & L.KEEP_SUBSAMPLE) and opt.stop_after not in ("project", "fit"))
+        # views under 64K pixels give the one-pass path too small a sample to bracket: exact select
+        first_mode = L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0
+        pop_flags = opt.flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)
+        # [view counts V][view offsets V][total][stats retry flag]
+        meta = torch.zeros(2 * V + 2, dtype=torch.int64, device=self.device)
+        ws_part = [0] * parts
+        ws = None
+        if use_stats:
+            wsb = int(lib.mdi_depth_range_workspace_bytes(V, max_tiles))
+            if parts > 1:   # one workspace per view range, 256-byte aligned; the whole-batch retry reuses the buffer
+                o = 0
+                for i, (a, b) in enumerate(ranges):
+                    ws_part[i] = o
+                    o += (int(lib.mdi_depth_range_workspace_bytes(b - a, max_tiles)) + 255) & ~255
+                wsb = max(wsb, o)
+            ws = self._buf("stats_ws", wsb, torch.uint8)
+            res.lo_hi = torch.empty((V, 2), dtype=f32, device=self.device)
+            res.quantiles = torch.empty((V, 4), dtype=f32, device=self.device)
+        want_raw = opt.raw_stats if opt.raw_stats is not None else (
+            OVERLAP_STATS and have_proj and opt.aligner in ("lstsqrs", "ransac", "msac"))
+        raw_stats = bool(use_stats and want_raw and first_mode == 0 and parts == 1 and not opt.defer_emit
+                         and opt.stop_after in (None, "mask"))
+
         # ---- a2-a4 outputs: everything is allocated on the calling stream before the first launch, so
         # that view ranges can be queued on part streams without the allocator seeing those streams
         if vin.uv is not None:
@@ -501,7 +536,28 @@ class Engine:
                                        at(res.ransac_iters, a), at(res.ransac_inliers, a), s),
                         "mdi_ransac")
 
-        if parts == 1:
+        fit_done = None
+        if parts == 1 and raw_stats:
+            # the alignment kernels (one CTA per view, latency-bound) go to a HIGH-priority side stream and
+            # the statistics pass over the raw depth stays here: the SMs take the alignment CTAs as soon as
+            # they are ready and fill up with the streaming pass in between
+            if not hasattr(self, "_align_stream"):
+                hi_prio = torch.cuda.Stream.priority_range()[1] if hasattr(torch.cuda.Stream, "priority_range") else -1
+                self._align_stream = torch.cuda.Stream(self.device, priority=hi_prio)
+            sa = self._align_stream
+            cams = torch.cuda.Event()
+            cams.record()
+            sa.wait_event(cams)
+            with torch.cuda.stream(sa):
+                s_a = _stream()
+                if have_proj:
+                    launch_project(0, V, s_a)
+                launch_fit(0, V, s_a)
+                fit_done = torch.cuda.Event()
+                fit_done.record(sa)
+            L.check(lib.mdi_depth_range(vp, V, max_tiles, None, None, pop_flags | L.STATS_RAW, ws.data_ptr(),
+                                        None, None, None, st), "mdi_depth_range")
+        elif parts == 1:
             if have_proj:
                 launch_project(0, V, st)
             if opt.stop_after == "project":
@@ -516,22 +572,8 @@ class Engine:
         if use_patch:
             flags |= L.KEEP_PATCH
         ssp = L.ptr(res.scale_shift)
-        # [view counts V][view offsets V][total][stats retry flag]
-        meta = torch.zeros(2 * V + 2, dtype=torch.int64, device=self.device)
         res.view_counts, res.view_offsets = meta[:V], meta[V:2 * V]
-        use_stats = bool(adaptive and (flags & L.KEEP_SUBSAMPLE))
-        ws_part = [0] * parts
         if use_stats:
-            wsb = int(lib.mdi_depth_range_workspace_bytes(V, max_tiles))
-            if parts > 1:   # one workspace per view range, 256-byte aligned; the whole-batch retry reuses the buffer
-                o = 0
-                for i, (a, b) in enumerate(ranges):
-                    ws_part[i] = o
-                    o += (int(lib.mdi_depth_range_workspace_bytes(b - a, max_tiles)) + 255) & ~255
-                wsb = max(wsb, o)
-            ws = self._buf("stats_ws", wsb, torch.uint8)
-            res.lo_hi = torch.empty((V, 2), dtype=f32, device=self.device)
-            res.quantiles = torch.empty((V, 4), dtype=f32, device=self.device)
             ftab = self._buf("factor_table", V * L.FACTOR_TABLE_STRIDE, f32)
         if opt.grad_thresh is not None:
             flags |= L.KEEP_GRAD
@@ -567,6 +609,7 @@ class Engine:
             zero_done = torch.cuda.Event()
             zero_done.record(zs)
         prezeroed = [True]
+        raw_pending = [fit_done]
 
         want_xyz = bool(opt.want_xyz)
         want_rgb = bool(opt.want_rgb and vin.image is not None)
@@ -581,11 +624,19 @@ class Engine:
 
         def launch_mask_range(a: int, b: int, stats_mode: int, s: int, ws_ptr: int, zeroed: bool):
             """a7 statistics -> a5-a10 keep mask of views a..b-1 (launches only)"""
-            if use_stats:
+            if use_stats and raw_pending[0] is not None and stats_mode == 0:
+                # the pass over the pixels ran on the raw depth beside the alignment: map it through the fit
+                main.wait_event(raw_pending[0])
+                raw_pending[0] = None
+                L.check(lib.mdi_depth_range_map(V, max_tiles, ssp, res.status.data_ptr(), pop_flags, ws_ptr,
+                                                res.lo_hi.data_ptr(), res.quantiles.data_ptr(),
+                                                meta[2 * V + 1:].data_ptr(), s), "mdi_depth_range_map")
+            elif use_stats:
                 L.check(lib.mdi_depth_range(vp + a * VS, b - a, max_tiles, at(res.scale_shift, a, 2), at(res.status, a),
-                                            (flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)) | stats_mode,
+                                            pop_flags | stats_mode,
                                             ws_ptr, at(res.lo_hi, a, 2), at(res.quantiles, a, 4),
                                             meta[2 * V + 1:].data_ptr(), s), "mdi_depth_range")
+            if use_stats:
                 L.check(lib.mdi_factor_table(b - a, at(res.lo_hi, a, 2), int(opt.factor_min), int(opt.factor_max),
                                              at(ftab, a, L.FACTOR_TABLE_STRIDE), s), "mdi_factor_table")
             scfg.flags = int(flags) | (L.KEEP_PREZEROED if zeroed else 0)
@@ -669,8 +720,6 @@ class Engine:
             copied.synchronize()
             return int(self._tail_pin[0]), bool(self._tail_pin[1]), (cap, xyz, rgb)
 
-        # views under 64K pixels give the one-pass path too small a sample to bracket: exact select
-        first_mode = L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0
         if (opt.exchange is not None and opt.stop_after is None and not opt.defer_emit
                 and (opt.want_xyz or opt.want_rgb)):
             # multi-GPU: counts travel on the device, the emit kernel writes this rank's points into every

@@ -329,6 +329,8 @@ def run_ours(args):
     # (one view range on one stream here, so that every kernel is timed alone)
     streams = emod.DEFAULT_STREAMS
     emod.DEFAULT_STREAMS = 1
+    overlap = emod.OVERLAP_STATS
+    emod.OVERLAP_STATS = False
     lib.mdi_profile_enable(1)
     L.profile_collect()
     ms_prof, res = timed_loop(args.steps)
@@ -337,6 +339,7 @@ def run_ours(args):
     # batch queued as `streams` contiguous view ranges on separate CUDA streams (Engine.run)
     lib.mdi_profile_enable(0)
     emod.DEFAULT_STREAMS = streams
+    emod.OVERLAP_STATS = overlap
     for _ in range(2):
         step()
     ms_total, res = timed_loop(args.steps)
@@ -348,7 +351,7 @@ def run_ours(args):
     if args.profile_mode:
         if rank == 0:
             clocks.stop()
-            print(json.dumps({"profile_mode": True, "streams": streams, "ms_per_step": ms_total / args.steps,
+            print(json.dumps({"profile_mode": True, "streams": streams, "raw_stats_overlap": bool(overlap), "ms_per_step": ms_total / args.steps,
                               "ms_per_step_profiled": ms_prof / args.steps, "kernels": ktimes,
                               "kept": n_kept, "views": V}))
         if world > 1:
@@ -467,9 +470,10 @@ def run_ours(args):
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.workload, args.scaling, world),
         "run": {"views_ok_rank0": n_ok, "kept_points_rank0": n_kept, "cloud_rows": n_kept_total, "exchange": gather,
-                "numa": numa, "streams": streams,
-                "streams_note": "view ranges of a step queued on separate CUDA streams in the headline loop; "
-                                "the profiled loop (per-kernel times, roofline) runs them as one range on one stream"},
+                "numa": numa, "streams": streams, "raw_stats_overlap": bool(overlap),
+                "streams_note": "headline loop: the a7 statistics pass runs on the raw depth on a side stream beside "
+                                "projection / fit / RANSAC (raw_stats_overlap) and the batch is queued as `streams` view "
+                                "ranges; the profiled loop (per-kernel times, roofline) runs every kernel alone on one stream"},
         "ms_per_step_profiled": ms_prof / args.steps,
         "cold_call_ms": float(cold_ms),
         "cold_call_note": "one call on a fresh Engine (no cached descriptor table, no output-size hint, no workspaces), "

@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MDI_ABI_VERSION 4
+#define MDI_ABI_VERSION 5
 
 /* error codes */
 #define MDI_OK 0
@@ -88,6 +88,8 @@ extern "C" {
 /* mdi_depth_range algorithm selection (OR-ed into its flags) */
 #define MDI_STATS_EXACT 64          /* three-pass radix select over all pixels, every view      */
 #define MDI_STATS_RETRY_FLAGGED 128 /* the same, only for views flagged MDI_STATUS_STATS_RETRY  */
+#define MDI_STATS_RAW 512           /* one-pass statistics of the RAW depth of every view; completed by
+                                       mdi_depth_range_map once the fit exists                    */
 
 /* RANSAC loss kinds */
 #define MDI_LOSS_RANSAC 0 /* outlier count       (ransacs.py:60) */
@@ -238,6 +240,24 @@ int mdi_depth_range(const MdiView* views, int n_views, int64_t max_tiles_per_vie
                     const float* scale_shift, int32_t* status, int flags, void* workspace,
                     float* lo_hi, float* quantiles /* [V,4] q1,q3,min,max or NULL */,
                     int64_t* retry_flag, void* stream);
+
+/*
+ * a7 (statistics) split in two so that the pass over the pixels does not wait for the fit
+ * (adaptive_subsampling.py:82-95 evaluated as F(order statistics of the raw depth), F = the
+ * alignment, monotone for a finite scale > 0 and a finite shift).  mdi_depth_range with
+ * MDI_STATS_RAW ignores scale_shift / status / lo_hi / quantiles / retry_flag (they may be NULL) and
+ * leaves, per view, the four order statistics, min, max and count of the raw depth over the pixels
+ * the predicted mask admits in `workspace`; it may run on another stream, beside mdi_project_filter /
+ * mdi_gather_fit / mdi_ransac.  mdi_depth_range_map (same n_views, max_tiles_per_view, workspace;
+ * after both) maps them through the fit and writes lo_hi / quantiles / status bits exactly like
+ * mdi_depth_range.  Views it cannot finish this way -- a scale that is not finite and positive, a
+ * depth in the view's range that aligns to exactly -42.0 (MDI_KEEP_SENTINEL in flags), brackets the
+ * raw pass could not certify -- get MDI_STATUS_STATS_RETRY and *retry_flag = 1, for a
+ * mdi_depth_range call with MDI_STATS_RETRY_FLAGGED.
+ */
+int mdi_depth_range_map(int n_views, int64_t max_tiles_per_view, const float* scale_shift,
+                        int32_t* status, int flags, void* workspace, float* lo_hi,
+                        float* quantiles, int64_t* retry_flag, void* stream);
 
 /* a9 (statistics): min and max of |dx|+|dy| of the aligned depth per view -> grad_range [V,2] */
 int mdi_grad_range(const MdiView* views, int n_views, int64_t max_tiles_per_view,
