@@ -75,6 +75,7 @@ _SIGNATURES = {
     "mdi_profile_collect": (_INT, [_P, _INT, _P, _P, _INT]),
     "mdi_setup_cameras": (_INT, [_P, _INT, _P, _P, _P, _P, _INT, _P]),
     "mdi_project_filter": (_INT, [_P, _INT, _P, _P, _I64, _P, _P, _P, _P, _P, _P]),
+    "mdi_setup_project_filter": (_INT, [_P, _INT, _P, _P, _P, _P, _INT, _P, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "mdi_gather_fit": (_INT, [_P, _INT, _I64, _P, _P, _P, _P, _P, _P, _INT, _INT, _P, _P]),
     "mdi_ransac": (_INT, [_P, _INT, _P, _P, _P, _P, _P, C.POINTER(RansacConfigC), _INT, _P, _P, _P, _P, _P]),
     "mdi_apply_scale_shift": (_INT, [_P, _I64, _P, _P, _P]),

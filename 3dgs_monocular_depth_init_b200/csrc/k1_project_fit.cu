@@ -7,17 +7,67 @@ namespace mdi {
 
 constexpr int kK1Threads = 512;
 
+// a1.  P = (K @ R^T... precisely the reference's `K @ R @ hstack([eye(3), -C[:, None]])` with
+// R = c2w[:3,:3].T, C = c2w[:3,3] (points_from_depth.py:231-233): the first product (right
+// operand a transposed view) as separately rounded products, the second as an FMA chain over k,
+// which is how the CPU sgemm evaluates them (bit-identical on every golden view).  Also copies Kinv and the top 3 rows of c2w into the
+// descriptors.  One thread per view.
+__device__ __forceinline__ void setup_camera(MdiView* views, int v, const float* K, const float* c2w,
+                                             const float* Kinv, float* P_out, int keep_P) {
+  const float* k = K + 9 * (int64_t)v;
+  const float* m = c2w + 16 * (int64_t)v;
+  float P[12];
+  if (keep_P) {  // the caller filled the descriptors' P already
+    for (int q = 0; q < 12; ++q) P[q] = views[v].P[q];
+  } else {
+    projection_matrix(k, m, P);
+  }
+  for (int q = 0; q < 12; ++q) {
+    views[v].P[q] = P[q];
+    views[v].c2w[q] = m[q];
+    if (P_out) P_out[12 * (int64_t)v + q] = P[q];
+  }
+  if (Kinv) {
+    for (int q = 0; q < 9; ++q) views[v].Kinv[q] = Kinv[9 * (int64_t)v + q];
+  } else {
+    // zero-skew pinhole K: torch.linalg.inv (LU + back substitution) is exactly
+    // [[1/fx, 0, -cx/fx], [0, 1/fy, -cy/fy], [0, 0, 1]] with true divisions (pinned on the CPU
+    // against torch for 5000 random intrinsics, tests/test_host_math.py)
+    float ki[9];
+    pinhole_inverse(k, ki);
+    for (int q = 0; q < 9; ++q) views[v].Kinv[q] = ki[q];
+  }
+}
+
+__global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
+                                     const float* __restrict__ K, const float* __restrict__ c2w,
+                                     const float* __restrict__ Kinv, float* __restrict__ P_out,
+                                     int keep_P) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_views) return;
+  setup_camera(views, v, K, c2w, Kinv, P_out, keep_P);
+}
+
 // a2.  Reference: points_from_depth.py:145-162 (project, round half-even, cast) and :111-142
 // (bounds / z >= 0 validity, the "< 1/4 in bounds" rule, mask lookup, ordered filter).
+// kSetup: the CTA first fills its own view's camera fields (a1, mdi_setup_project_filter) -- one launch
+// less in front of a kernel that is a chain of dependent round trips anyway.
+template <bool kSetup>
 __global__ void __launch_bounds__(kK1Threads)
-project_filter_kernel(const MdiView* __restrict__ views, const float* __restrict__ sfm_xyz,
+project_filter_kernel(MdiView* views, const float* __restrict__ sfm_xyz,
                       const int32_t* __restrict__ sfm_index, int64_t slots,
                       int32_t* __restrict__ uv, float* __restrict__ z_out,
                       int32_t* __restrict__ n_inbounds, int32_t* __restrict__ n_valid,
-                      int32_t* __restrict__ status) {
+                      int32_t* __restrict__ status, const float* __restrict__ K,
+                      const float* __restrict__ c2w, const float* __restrict__ Kinv,
+                      float* __restrict__ P_out, int keep_P) {
   __shared__ int scan_smem[33];
   __shared__ int s_inb;
   const int v = blockIdx.x;
+  if (kSetup) {
+    if (threadIdx.x == 0) setup_camera(views, v, K, c2w, Kinv, P_out, keep_P);
+    __syncthreads();
+  }
   const MdiView vw = views[v];
   const int M = vw.sfm_count;
   const int64_t base = vw.sfm_begin;
@@ -187,42 +237,6 @@ gather_fit_kernel(const MdiView* __restrict__ views, int64_t slots,
   }
 }
 
-// a1.  P = (K @ R^T... precisely the reference's `K @ R @ hstack([eye(3), -C[:, None]])` with
-// R = c2w[:3,:3].T, C = c2w[:3,3] (points_from_depth.py:231-233): the first product (right
-// operand a transposed view) as separately rounded products, the second as an FMA chain over k,
-// which is how the CPU sgemm evaluates them (bit-identical on every golden view).  Also copies Kinv and the top 3 rows of c2w into the
-// descriptors.  One thread per view.
-__global__ void setup_cameras_kernel(MdiView* __restrict__ views, int n_views,
-                                     const float* __restrict__ K, const float* __restrict__ c2w,
-                                     const float* __restrict__ Kinv, float* __restrict__ P_out,
-                                     int keep_P) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v >= n_views) return;
-  const float* k = K + 9 * (int64_t)v;
-  const float* m = c2w + 16 * (int64_t)v;
-  float P[12];
-  if (keep_P) {  // the caller filled the descriptors' P already
-    for (int q = 0; q < 12; ++q) P[q] = views[v].P[q];
-  } else {
-    projection_matrix(k, m, P);
-  }
-  for (int q = 0; q < 12; ++q) {
-    views[v].P[q] = P[q];
-    views[v].c2w[q] = m[q];
-    if (P_out) P_out[12 * (int64_t)v + q] = P[q];
-  }
-  if (Kinv) {
-    for (int q = 0; q < 9; ++q) views[v].Kinv[q] = Kinv[9 * (int64_t)v + q];
-  } else {
-    // zero-skew pinhole K: torch.linalg.inv (LU + back substitution) is exactly
-    // [[1/fx, 0, -cx/fx], [0, 1/fy, -cy/fy], [0, 0, 1]] with true divisions (pinned on the CPU
-    // against torch for 5000 random intrinsics, tests/test_host_math.py)
-    float ki[9];
-    pinhole_inverse(k, ki);
-    for (int q = 0; q < 9; ++q) views[v].Kinv[q] = ki[q];
-  }
-}
-
 __global__ void apply_scale_shift_kernel(const float* __restrict__ depth, int64_t n,
                                          const float* __restrict__ scale_shift,
                                          float* __restrict__ out) {
@@ -291,9 +305,26 @@ extern "C" int mdi_project_filter(const MdiView* views, int n_views, const float
   MDI_REQUIRE(views && sfm_xyz && uv && z && n_inbounds && n_valid && status,
               "mdi_project_filter: null pointer");
   mdi::prof_mark("project_filter_kernel", (cudaStream_t)stream);
-  mdi::project_filter_kernel<<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
-      views, sfm_xyz, sfm_index, slots, uv, z, n_inbounds, n_valid, status);
+  mdi::project_filter_kernel<false><<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
+      const_cast<MdiView*>(views), sfm_xyz, sfm_index, slots, uv, z, n_inbounds, n_valid, status, nullptr, nullptr,
+      nullptr, nullptr, 0);
   MDI_CHECK_LAUNCH("mdi_project_filter");
+  return MDI_OK;
+}
+
+extern "C" int mdi_setup_project_filter(MdiView* views, int n_views, const float* K, const float* c2w,
+                                        const float* Kinv, float* P_out, int keep_P, const float* sfm_xyz,
+                                        const int32_t* sfm_index, int64_t slots, int32_t* uv, float* z,
+                                        int32_t* n_inbounds, int32_t* n_valid, int32_t* status,
+                                        void* stream) {
+  MDI_REQUIRE(n_views >= 0 && slots >= 0, "mdi_setup_project_filter: negative size");
+  if (n_views == 0) return MDI_OK;
+  MDI_REQUIRE(views && K && c2w && sfm_xyz && uv && z && n_inbounds && n_valid && status,
+              "mdi_setup_project_filter: null pointer");
+  mdi::prof_mark("project_filter_kernel", (cudaStream_t)stream);
+  mdi::project_filter_kernel<true><<<n_views, mdi::kK1Threads, 0, (cudaStream_t)stream>>>(
+      views, sfm_xyz, sfm_index, slots, uv, z, n_inbounds, n_valid, status, K, c2w, Kinv, P_out, keep_P);
+  MDI_CHECK_LAUNCH("mdi_setup_project_filter");
   return MDI_OK;
 }
 

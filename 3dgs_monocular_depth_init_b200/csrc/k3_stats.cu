@@ -41,7 +41,7 @@ constexpr int kSelBins = 2048;
 struct StatsHdr {
   // sample-select path
   uint32_t n_sample, n_cand;
-  uint32_t min_key, max_key, count;
+  uint32_t nmin_key, max_key, count;   // nmin_key = ~(smallest key): a zero-filled header needs no init kernel
   uint32_t below[2];
   uint32_t br_lo[2], br_hi[2], br_shift[2];
   uint32_t run_exact;  // this view goes through the exact path in this call
@@ -50,7 +50,7 @@ struct StatsHdr {
   uint32_t slot_prefix[kTargets];  // prefix each histogram slot selects on
   uint32_t tgt_prefix[kTargets];
   uint32_t tgt_slot[kTargets];
-  uint32_t smp_min, smp_max, fail_code;  // fail_code: why the one-pass path asked for a retry
+  uint32_t smp_nmin, smp_max, fail_code;  // smp_nmin = ~(smallest sample key); fail_code: why the one-pass path asked for a retry
   long long tgt_rank[kTargets];
   float w[2];
   uint32_t gmin_key, gmax_key;
@@ -207,7 +207,7 @@ __device__ uint32_t block_select(const uint32_t* __restrict__ keys, uint32_t n,
 __global__ void stats_init_kernel(StatsHdr* hdr, int n_views, const int32_t* status, int mode) {
   int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n_views) return;
-  hdr[v].min_key = 0xFFFFFFFFu; hdr[v].x_min_key = 0xFFFFFFFFu; hdr[v].smp_min = 0xFFFFFFFFu;
+  hdr[v].x_min_key = 0xFFFFFFFFu;
   // mode 0: sample-select for everybody; 1: exact for everybody; 2: exact for views flagged RETRY
   const bool retry = status && (status[v] & MDI_STATUS_STATS_RETRY);
   hdr[v].run_exact = mode == 1 ? 1u : (mode == 2 ? (retry ? 1u : 0u) : 0u);
@@ -282,7 +282,7 @@ stats_sample_kernel(const MdiView* __restrict__ views, const float* __restrict__
     uint32_t base = 0;
     if (lane_id() == 31) {
       base = atomicAdd(&ws.hdr[v].n_sample, (uint32_t)tot);
-      atomicMin(&ws.hdr[v].smp_min, kmin);
+      atomicMax(&ws.hdr[v].smp_nmin, ~kmin);
       atomicMax(&ws.hdr[v].smp_max, kmax);
     }
     base = __shfl_sync(0xffffffffu, base, 31);
@@ -475,7 +475,7 @@ stats_bracket_kernel(const float* __restrict__ scale_shift, const int32_t* __res
     // 1: no pixel of the SAMPLE comes near the sentinel -- the loop only certifies that none does
     //    (thread-level range check, else force_retry); 2: the loop tests every pixel against ds_*
     const uint32_t kSent = fast_key(-42.0f);
-    const bool far = !sentinel || kSent < h->smp_min || kSent > h->smp_max;
+    const bool far = !sentinel || kSent < ~h->smp_nmin || kSent > h->smp_max;
     h->fast = (mono && s_fast) ? (far ? 1u : 2u) : 0u;
   }
 }
@@ -714,7 +714,7 @@ stats_main_kernel(const MdiView* __restrict__ views, const float* __restrict__ s
   }
   __syncthreads();
   if (threadIdx.x == 0 && s_cnt) {
-    atomicMin(&h->min_key, s_min); atomicMax(&h->max_key, s_max); atomicAdd(&h->count, s_cnt);
+    atomicMax(&h->nmin_key, ~s_min); atomicMax(&h->max_key, s_max); atomicAdd(&h->count, s_cnt);
     atomicAdd(&h->below[0], s_below[0]); atomicAdd(&h->below[1], s_below[1]);
   }
   uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;  // [2][kBrBins] of it
@@ -903,7 +903,7 @@ stats_main_tma_kernel(const MdiView* __restrict__ views, const float* __restrict
   }
   __syncthreads();
   if (tid == 0 && s_cnt) {
-    atomicMin(&h->min_key, s_min); atomicMax(&h->max_key, s_max); atomicAdd(&h->count, s_cnt);
+    atomicMax(&h->nmin_key, ~s_min); atomicMax(&h->max_key, s_max); atomicAdd(&h->count, s_cnt);
     atomicAdd(&h->below[0], s_below[0]); atomicAdd(&h->below[1], s_below[1]);
   }
   uint32_t* ghist = ws.hist + (int64_t)v * kTargets * kBins;  // [2][kBrBins] of it
@@ -958,7 +958,8 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
   const QuantileRank r1 = quantile_rank(0.25f, (int64_t)n);
   const QuantileRank r3 = quantile_rank(0.75f, (int64_t)n);
   const uint32_t n_cand = h->n_cand;
-  const bool has_nan = h->max_key > kKeyPosInf || h->min_key < kKeyNegInf;
+  const uint32_t min_key = ~h->nmin_key;
+  const bool has_nan = h->max_key > kKeyPosInf || min_key < kKeyNegInf;
   const uint32_t L[2] = {h->br_lo[0], h->br_lo[1]};
   const uint32_t Wd[2] = {h->br_hi[0] - L[0], h->br_hi[1] - L[1]};
   const uint32_t sft[2] = {h->br_shift[0], h->br_shift[1]};
@@ -1058,7 +1059,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
       h->raw_state = kRawFail;
     } else {
       for (int j = 0; j < kTargets; ++j) h->raw_val[j] = key_to_float(s_out[j]);
-      h->raw_min = key_to_float(h->min_key); h->raw_max = key_to_float(h->max_key);
+      h->raw_min = key_to_float(min_key); h->raw_max = key_to_float(h->max_key);
       h->raw_state = has_nan ? kRawNan : kRawOk;
     }
   } else if (tid == 0) {
@@ -1070,7 +1071,7 @@ stats_finish_kernel(int32_t* __restrict__ status, StatsWs ws, float* __restrict_
     } else {
       float val[kTargets];
       for (int j = 0; j < kTargets; ++j) val[j] = key_to_float(s_out[j]);
-      write_range(v, val, r1.w, r3.w, h->min_key, has_nan ? 0xFFFFFFFFu : h->max_key, lo_hi, quantiles);
+      write_range(v, val, r1.w, r3.w, min_key, has_nan ? 0xFFFFFFFFu : h->max_key, lo_hi, quantiles);
     }
   }
 }
@@ -1393,8 +1394,10 @@ extern "C" int mdi_depth_range(const MdiView* views, int n_views, int64_t max_ti
   if (raw) { scale_shift = nullptr; status = nullptr; }   // raw depth, every view: the fit and the status may not exist yet
   const int pop = flags & (MDI_KEEP_PRED_MASK | (raw ? 0 : MDI_KEEP_SENTINEL));
   MDI_CUDA(cudaMemsetAsync(ws.hdr, 0, sizeof(StatsHdr) * (size_t)n_views, st), "mdi_depth_range");
-  mdi::prof_mark("stats_init_kernel", st);
-  stats_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(ws.hdr, n_views, status, mode);
+  if (mode != 0) {   // the one-pass path starts from the zero-filled headers
+    mdi::prof_mark("stats_init_kernel", st);
+    stats_init_kernel<<<(n_views + 255) / 256, 256, 0, st>>>(ws.hdr, n_views, status, mode);
+  }
   dim3 grid(max_chunks(max_tiles_per_view), (unsigned)n_views);
   MDI_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(uint32_t) * kTargets * kBins * (size_t)n_views, st),
            "mdi_depth_range");

@@ -160,7 +160,7 @@ def _ptrs(x: Optional[TensorOrList], V: int, esize_check: Optional[int] = None):
 
 # kernels launched by each C-ABI entry point (for the bench's `gpu_launches` claim)
 KERNELS_PER_CALL = {
-    "mdi_setup_cameras": 1, "mdi_upload_table": 1, "mdi_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
+    "mdi_setup_cameras": 1, "mdi_upload_table": 1, "mdi_project_filter": 1, "mdi_setup_project_filter": 1, "mdi_gather_fit": 1, "mdi_ransac": 1,
     "mdi_apply_scale_shift": 1, "mdi_depth_range": 5, "mdi_depth_range_map": 1, "mdi_grad_range": 3, "mdi_factor_table": 1, "mdi_keep_mask": 4,
     "mdi_scan_tiles": 2, "mdi_emit_points": 1, "mdi_emit_points_capped": 1, "mdi_emit_points_multi": 1, "mdi_emit_points_multicast": 1,
     "mdi_emit_points_exchange": 1, "mdi_exchange_counts": 1, "mdi_expand_rgb8": 1,
@@ -424,9 +424,6 @@ class Engine:
         c2wp = kp + 4 * 9 * V
         kinvp = None if pinhole else c2wp + 4 * 16 * V
         res.P = torch.empty((V, 3, 4), dtype=torch.float32, device=self.device)
-        L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(),
-                                      0 if vin.P_override is None else 1, st), "mdi_setup_cameras")
-
         i32, f32 = torch.int32, torch.float32
         res.status = torch.zeros(V, dtype=i32, device=self.device)
         VS = desc.itemsize
@@ -436,18 +433,61 @@ class Engine:
         have_proj = vin.uv is None and vin.sfm_xyz is not None
         ranges = self._view_ranges(vin, opt, V, desc, adaptive, have_proj)
         parts = len(ranges)
+        keep_P = 0 if vin.P_override is None else 1
+        # a1 rides in the projection launch when the whole batch is projected by one (mdi_setup_project_filter)
+        fuse_cam = have_proj and parts == 1
+        if not fuse_cam:
+            L.check(lib.mdi_setup_cameras(vp, V, kp, c2wp, kinvp, res.P.data_ptr(), keep_P, st), "mdi_setup_cameras")
 
         def at(t, a, per_view=1):
             """address of view a's row in a per-view array (None stays NULL)"""
             return None if t is None else t.data_ptr() + a * per_view * t.element_size()
 
-        # ---- a7 workspaces first: with an increasing fit the order statistics of the aligned depth are the
-        # aligned order statistics of the RAW depth, so the one pass over the pixels does not have to wait
-        # for the fit -- it is queued on a side stream here and runs beside projection / fit / RANSAC
         use_stats = bool(adaptive and (opt.flags & L.KEEP_SUBSAMPLE) and opt.stop_after not in ("project", "fit"))
         # views under 64K pixels give the one-pass path too small a sample to bracket: exact select
         first_mode = L.STATS_EXACT if (opt.stats_exact or max_tiles <= 16) else 0
         pop_flags = opt.flags & (L.KEEP_PRED_MASK | L.KEEP_SENTINEL)
+        want_raw = opt.raw_stats if opt.raw_stats is not None else (
+            OVERLAP_STATS and have_proj and opt.aligner in ("lstsqrs", "ransac", "msac"))
+        raw_stats = bool(use_stats and want_raw and first_mode == 0 and parts == 1 and not opt.defer_emit
+                         and opt.stop_after in (None, "mask"))
+
+        # ---- a2: outputs and, when the batch is one range on this stream, the launch itself -- the device
+        # gets its first kernel before the host allocates everything else
+        if vin.uv is not None:
+            res.uv, res.z, res.n_valid = vin.uv, vin.z, vin.n_valid
+            assert res.uv.shape[1] >= slots - 4 and res.uv.dtype == i32
+            slots = int(res.uv.shape[1])
+        elif have_proj:
+            res.uv = torch.empty((2, slots), dtype=i32, device=self.device)
+            res.z = torch.empty(slots, dtype=f32, device=self.device)
+            res.n_inbounds = torch.empty(V, dtype=i32, device=self.device)
+            res.n_valid = torch.empty(V, dtype=i32, device=self.device)
+
+        def launch_project(a: int, b: int, s: int):
+            """a2 of views a..b-1: projection + filtering"""
+            if fuse_cam:
+                L.check(lib.mdi_setup_project_filter(vp, V, kp, c2wp, kinvp, res.P.data_ptr(), keep_P,
+                                                     vin.sfm_xyz.data_ptr(), L.ptr(vin.sfm_index), slots,
+                                                     res.uv.data_ptr(), res.z.data_ptr(), res.n_inbounds.data_ptr(),
+                                                     res.n_valid.data_ptr(), res.status.data_ptr(), s),
+                        "mdi_setup_project_filter")
+                return
+            L.check(lib.mdi_project_filter(vp + a * VS, b - a, vin.sfm_xyz.data_ptr(), L.ptr(vin.sfm_index), slots,
+                                           res.uv.data_ptr(), res.z.data_ptr(), at(res.n_inbounds, a),
+                                           at(res.n_valid, a), at(res.status, a), s),
+                    "mdi_project_filter")
+
+        projected = False
+        if parts == 1 and have_proj and not raw_stats:
+            launch_project(0, V, st)
+            projected = True
+        if opt.stop_after == "project" and parts == 1 and not raw_stats:
+            return res
+
+        # ---- a7 workspaces: with an increasing fit the order statistics of the aligned depth are the
+        # aligned order statistics of the RAW depth, so the one pass over the pixels does not have to wait
+        # for the fit (raw_stats: queued beside projection / fit / RANSAC)
         # [view counts V][view offsets V][total][stats retry flag]
         meta = torch.zeros(2 * V + 2, dtype=torch.int64, device=self.device)
         ws_part = [0] * parts
@@ -463,22 +503,9 @@ class Engine:
             ws = self._buf("stats_ws", wsb, torch.uint8)
             res.lo_hi = torch.empty((V, 2), dtype=f32, device=self.device)
             res.quantiles = torch.empty((V, 4), dtype=f32, device=self.device)
-        want_raw = opt.raw_stats if opt.raw_stats is not None else (
-            OVERLAP_STATS and have_proj and opt.aligner in ("lstsqrs", "ransac", "msac"))
-        raw_stats = bool(use_stats and want_raw and first_mode == 0 and parts == 1 and not opt.defer_emit
-                         and opt.stop_after in (None, "mask"))
 
-        # ---- a2-a4 outputs: everything is allocated on the calling stream before the first launch, so
-        # that view ranges can be queued on part streams without the allocator seeing those streams
-        if vin.uv is not None:
-            res.uv, res.z, res.n_valid = vin.uv, vin.z, vin.n_valid
-            assert res.uv.shape[1] >= slots - 4 and res.uv.dtype == i32
-            slots = int(res.uv.shape[1])
-        elif have_proj:
-            res.uv = torch.empty((2, slots), dtype=i32, device=self.device)
-            res.z = torch.empty(slots, dtype=f32, device=self.device)
-            res.n_inbounds = torch.empty(V, dtype=i32, device=self.device)
-            res.n_valid = torch.empty(V, dtype=i32, device=self.device)
+        # ---- a3 / a4 outputs (all allocated on the calling stream before anything is queued on a part
+        # stream, so that the allocator never sees those streams)
         have_pts = res.uv is not None
         use_patch = bool(opt.use_patch_mask and have_pts)
         want_fit = opt.stop_after != "project"
@@ -513,13 +540,6 @@ class Engine:
                 assert res.scale_shift.dtype == f32 and tuple(res.scale_shift.shape) == (V, 2)
         elif opt.aligner not in ("lstsqrs", "ransac", "msac"):
             raise NotImplementedError(f"aligner {opt.aligner!r} is not on the B200 path")
-
-        def launch_project(a: int, b: int, s: int):
-            """a2 of views a..b-1: projection + filtering"""
-            L.check(lib.mdi_project_filter(vp + a * VS, b - a, vin.sfm_xyz.data_ptr(), L.ptr(vin.sfm_index), slots,
-                                           res.uv.data_ptr(), res.z.data_ptr(), at(res.n_inbounds, a),
-                                           at(res.n_valid, a), at(res.status, a), s),
-                    "mdi_project_filter")
 
         def launch_fit(a: int, b: int, s: int):
             """a3 + a8 (gather, normal equations, patch histogram) and a4 (RANSAC / MSAC) of views a..b-1"""
@@ -558,7 +578,7 @@ class Engine:
             L.check(lib.mdi_depth_range(vp, V, max_tiles, None, None, pop_flags | L.STATS_RAW, ws.data_ptr(),
                                         None, None, None, st), "mdi_depth_range")
         elif parts == 1:
-            if have_proj:
+            if have_proj and not projected:
                 launch_project(0, V, st)
             if opt.stop_after == "project":
                 return res

@@ -184,6 +184,16 @@ int mdi_project_filter(const MdiView* views, int n_views, const float* sfm_xyz,
                        int32_t* n_inbounds, int32_t* n_valid, int32_t* status, void* stream);
 
 /*
+ * mdi_setup_cameras + mdi_project_filter in one launch (a1 + a2: points_from_depth.py:231-233 and
+ * :111-162): the CTA of a view fills the view's camera fields before it projects.  Same arguments
+ * and results as the two calls.
+ */
+int mdi_setup_project_filter(MdiView* views, int n_views, const float* K, const float* c2w,
+                             const float* Kinv, float* P_out, int keep_P, const float* sfm_xyz,
+                             const int32_t* sfm_index, int64_t slots, int32_t* uv, float* z,
+                             int32_t* n_inbounds, int32_t* n_valid, int32_t* status, void* stream);
+
+/*
  * a3 + a8: gather d_i = depth[v_i,u_i], accumulate the normal equations in fp64, solve with
  * torch.linalg.pinv semantics, count points per patch.
  *   sums      float64 [V,5] = (sum d*d, sum d, n, sum d*g, sum g)
