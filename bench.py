@@ -471,9 +471,9 @@ def run_ours(args):
         "config": workload_config(args.workload, args.scaling, world),
         "run": {"views_ok_rank0": n_ok, "kept_points_rank0": n_kept, "cloud_rows": n_kept_total, "exchange": gather,
                 "numa": numa, "streams": streams, "raw_stats_overlap": bool(overlap),
-                "streams_note": "headline loop: the a7 statistics pass runs on the raw depth on a side stream beside "
-                                "projection / fit / RANSAC (raw_stats_overlap) and the batch is queued as `streams` view "
-                                "ranges; the profiled loop (per-kernel times, roofline) runs every kernel alone on one stream"},
+                "streams_note": "what the headline loop used: `streams` view ranges on separate CUDA streams, and "
+                                "(raw_stats_overlap) the a7 statistics pass on the raw depth beside the alignment kernels; "
+                                "the profiled loop (per-kernel times, roofline) runs every kernel alone on one stream"},
         "ms_per_step_profiled": ms_prof / args.steps,
         "cold_call_ms": float(cold_ms),
         "cold_call_note": "one call on a fresh Engine (no cached descriptor table, no output-size hint, no workspaces), "
