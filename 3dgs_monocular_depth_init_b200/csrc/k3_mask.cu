@@ -15,6 +15,9 @@
 // the lattice points instead.  Kept pixels set their keep byte, their bit in the tile bit words
 // and bump the tile count that the order-preserving compaction consumes (mdi_scan_tiles /
 // mdi_emit_points).  Configurations without a stride test run the per-pixel kernel.
+#include <stdlib.h>
+#include <string.h>
+
 #include "common.cuh"
 
 namespace mdi {
@@ -250,6 +253,231 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
   }
 }
 
+// ---- the lattice walk with the rows staged by bulk copies (adaptive strides, the default) ---------
+// keep_lattice_kernel gathers one 32-byte sector per lattice point, and 32-byte sectors fetched one
+// by one get about 0.42 of the copy bandwidth out of the 64-byte DRAM bursts (the same ceiling the
+// other gather kernels sit at).  But the lattices of the strides fmin..fmax touch EVERY sector of the
+// rows they visit (a stride is at most 15 floats), and those rows are known up front: row r is
+// visited by every stride that divides it (63 % of the rows for 5..15).  So a warp takes eight
+// consecutive rows, and for each of them that some stride divides it streams the whole depth row and
+// the whole predicted-mask row into shared memory with two 1-D bulk copies (TMA) on an mbarrier,
+// two rows in flight per warp; the lattice points of all strides dividing the row are then read from
+// shared memory.  DRAM sees long sequential reads, the per-point work has no global load left except
+// the SfM-density patch row (one per ~40 image rows, fetched a row ahead), and the warps need no
+// CTA-wide barrier.  The per-point decisions are those of keep_lattice_kernel, operation for operation.
+constexpr int kRowWarps = 4;
+constexpr int kRowsPerWarp = 8;
+constexpr int kRowPatchBytes = 128;   // SfM-density patch row cached per warp (grid_w beyond: global loads)
+constexpr int kRowMaxFloats = 2048;   // widest row staged in one piece; wider views keep the gather kernel
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(kRowWarps * 32)
+keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ scale_shift,
+                 const int32_t* __restrict__ status, const float* __restrict__ lo_hi,
+                 const uint8_t* __restrict__ patch_blocked, const float* __restrict__ factor_table,
+                 MaskParams prm, int slot_bytes, int depth_bytes, uint8_t* __restrict__ keep,
+                 uint32_t* __restrict__ bits, int32_t* __restrict__ tile_counts) {
+  extern __shared__ __align__(16) unsigned char s_dyn[];   // [warp][slot]{depth row, mask row}, then [warp] patch row
+  __shared__ __align__(8) unsigned long long s_bar[kRowWarps][2];
+  const int v = blockIdx.y;
+  if (status && status[v] != MDI_STATUS_OK) return;
+  const MdiView* vp = views + v;
+  const int H = vp->H, W = vp->W;
+  const int warp = warp_id(), lane = lane_id();
+  const int r0 = ((int)blockIdx.x * kRowWarps + warp) * kRowsPerWarp;
+  if (r0 >= H) return;   // whole warps leave: the kernel has no CTA-wide barrier
+  const int n_strides = prm.fmax - prm.fmin + 1;
+  // strides dividing each of the warp's rows: lane k < 8 ends up owning the stride mask of row r0 + k
+  // (lane k < n_strides holds r0 mod f_k: one division per warp, the eight rows follow by counting up)
+  const int my_f = prm.fmin + (lane < n_strides ? lane : 0);
+  const int my_cols = (W + my_f - 1) / my_f;    // lattice columns of stride f_lane
+  int rem = r0 % my_f;
+  uint32_t fm = 0;
+#pragma unroll
+  for (int i = 0; i < kRowsPerWarp; ++i) {
+    const uint32_t b = __ballot_sync(0xffffffffu, lane < n_strides && rem == 0 && r0 + i < H);
+    if (lane == i) fm = b;
+    if (++rem == my_f) rem = 0;
+  }
+  uint32_t todo = __ballot_sync(0xffffffffu, fm != 0);   // rows of the warp that hold lattice points
+  if (!todo) return;
+
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const float* __restrict__ depth = vp->depth;
+  const bool use_pm = (prm.flags & MDI_KEEP_PRED_MASK) && vp->mask;
+  const uint8_t* __restrict__ pmask = use_pm ? vp->mask : nullptr;
+  const uint8_t* __restrict__ pb =
+      ((prm.flags & MDI_KEEP_PATCH) && patch_blocked) ? patch_blocked + (int64_t)v * MDI_PATCH_STRIDE : nullptr;
+  const int patch_h = vp->patch_h, patch_w = vp->patch_w, grid_h = vp->grid_h, grid_w = vp->grid_w;
+  const uint32_t mh = 0xFFFFFFFFu / (uint32_t)max(patch_h, 1) + 1u, mw = 0xFFFFFFFFu / (uint32_t)max(patch_w, 1) + 1u;
+  // breakpoints of the view: lane L holds B[L] = row[1 + L], L <= n_strides
+  const float* trow = factor_table ? factor_table + (int64_t)v * MDI_FACTOR_TABLE_STRIDE : nullptr;
+  const bool table = trow && trow[0] != 0.f;
+  const float tab = (table && lane <= n_strides) ? trow[1 + lane] : 0.f;
+  // with MDI_KEEP_NONNEG a lattice point of stride f_k is a candidate iff a >= max(B[k+1], 0) && !(a >= B[k])
+  // (a >= 0 also rules out the sentinel and a NaN): lane k holds that lower bound
+  const float my_lo = fmaxf(__shfl_down_sync(0xffffffffu, tab, 1), 0.f);
+  const bool fast_cfg = table && (prm.flags & MDI_KEEP_NONNEG);
+  const float vlo = lo_hi[2 * v], vhi = lo_hi[2 * v + 1];
+
+  unsigned char* my = s_dyn + (size_t)warp * 2 * slot_bytes;
+  uint8_t* s_patch = s_dyn + (size_t)kRowWarps * 2 * slot_bytes + warp * kRowPatchBytes;
+  const uint32_t bar0 = smem_addr(&s_bar[warp][0]);
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+
+  // the 16-byte aligned part of row r that lies inside the view's own arrays: columns [c0, c1) of the
+  // depth row / [m0, m1) of the mask row are staged, the few others (first / last row of a view whose
+  // arrays are not 16-byte aligned) are read from global memory
+  const uintptr_t d_base = reinterpret_cast<uintptr_t>(depth), d_end = d_base + (size_t)H * W * 4;
+  const uintptr_t d_lo_lim = (d_base + 15) & ~(uintptr_t)15, d_hi_lim = d_end & ~(uintptr_t)15;
+  const uintptr_t m_base = reinterpret_cast<uintptr_t>(pmask), m_end = m_base + (size_t)H * W;
+  const uintptr_t m_lo_lim = (m_base + 15) & ~(uintptr_t)15, m_hi_lim = m_end & ~(uintptr_t)15;
+  auto span = [&](uintptr_t a, size_t bytes, uintptr_t lo_lim, uintptr_t hi_lim, uintptr_t* lo, uintptr_t* hi) {
+    uintptr_t l = a & ~(uintptr_t)15, h = (a + bytes + 15) & ~(uintptr_t)15;
+    if (l < lo_lim) l = lo_lim;
+    if (h > hi_lim) h = hi_lim;
+    if (h < l) h = l;
+    *lo = l; *hi = h;
+  };
+  auto issue = [&](int r, int slot) {   // lane 0: both rows of image row r into `slot`, one barrier
+    uintptr_t dl, dh, ml = 0, mh_ = 0;
+    span(d_base + (size_t)r * W * 4, (size_t)W * 4, d_lo_lim, d_hi_lim, &dl, &dh);
+    if (pmask) span(m_base + (size_t)r * W, (size_t)W, m_lo_lim, m_hi_lim, &ml, &mh_);
+    const uint32_t db = (uint32_t)(dh - dl), mb = (uint32_t)(mh_ - ml);
+    const uint32_t bar = bar0 + 8 * slot;
+    const uint32_t dst = smem_addr(my + (size_t)slot * slot_bytes);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(db + mb) : "memory");
+    if (db)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst), "l"(dl), "r"(db), "r"(bar) : "memory");
+    if (mb)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst + (uint32_t)depth_bytes), "l"(ml), "r"(mb), "r"(bar) : "memory");
+  };
+  uint32_t to_issue = todo;
+  if (lane == 0) {
+    for (int slot = 0; slot < 2 && to_issue; ++slot) {
+      const int k = __ffs(to_issue) - 1;
+      issue(r0 + k, slot);
+      to_issue &= to_issue - 1;
+    }
+  }
+  to_issue = __shfl_sync(0xffffffffu, to_issue, 0);
+
+  int cached_pr = -1;   // patch row held in s_patch
+  for (int i = 0; todo; ++i) {
+    const int k = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const int r = r0 + k;
+    const uint32_t fmr = __shfl_sync(0xffffffffu, fm, k);
+    const int slot = i & 1;
+    // SfM-density patch row of this image row (changes every patch_h rows): fetched before the wait
+    const int pr = pb ? (patch_h <= 1 ? r : (int)__umulhi((uint32_t)r, mh)) : -1;
+    const bool pr_in = pb && pr < grid_h;
+    if (pr_in && pr != cached_pr && grid_w <= kRowPatchBytes) {
+      __syncwarp();
+      for (int c = lane; c < grid_w; c += 32) s_patch[c] = __ldg(&pb[pr * grid_w + c]);
+      cached_pr = pr;
+      __syncwarp();
+    }
+    {   // wait for the row (phase of this slot's (i / 2)-th use)
+      const uint32_t bar = bar0 + 8 * slot, parity = (uint32_t)(i >> 1) & 1u;
+      uint32_t ok = 0;
+      while (!ok) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+      }
+    }
+    const int64_t rowpx = (int64_t)r * W;
+    uintptr_t dl, dh, ml = 0, mh_ = 0;
+    span(d_base + (size_t)rowpx * 4, (size_t)W * 4, d_lo_lim, d_hi_lim, &dl, &dh);
+    if (pmask) span(m_base + (size_t)rowpx, (size_t)W, m_lo_lim, m_hi_lim, &ml, &mh_);
+    // column c of the row sits at srow[c] for c0 <= c < c1 (srow may point in front of the slot)
+    const intptr_t d_off = (intptr_t)dl - (intptr_t)(d_base + (size_t)rowpx * 4);   // bytes, multiple of 4
+    const float* srow = reinterpret_cast<const float*>(my + (size_t)slot * slot_bytes) - d_off / 4;
+    const int c0 = d_off > 0 ? (int)(d_off / 4) : 0;
+    const int c1 = (int)min((intptr_t)W, ((intptr_t)dh - (intptr_t)(d_base + (size_t)rowpx * 4)) / 4);
+    const intptr_t m_off = (intptr_t)ml - (intptr_t)(m_base + (size_t)rowpx);
+    const uint8_t* smask = my + (size_t)slot * slot_bytes + depth_bytes - m_off;
+    const int m0 = m_off > 0 ? (int)m_off : 0;
+    const int m1 = (int)min((intptr_t)W, (intptr_t)mh_ - (intptr_t)(m_base + (size_t)rowpx));
+    const float* grow = depth + rowpx;
+
+    // survivors of the stride test: predicted mask, SfM-density patch, then the outputs
+    auto finish_point = [&](const int c) {
+      if (pmask) {
+        const uint8_t mbyte = (c >= m0 && c < m1) ? smask[c] : __ldg(pmask + rowpx + c);
+        if (mbyte == 0) return;
+      }
+      if (pr_in) {
+        const int pc = patch_w <= 1 ? c : (int)__umulhi((uint32_t)c, mw);
+        if (pc < grid_w) {
+          const uint8_t blocked = grid_w <= kRowPatchBytes ? s_patch[pc] : __ldg(&pb[pr * grid_w + pc]);
+          if (blocked) return;
+        }
+      }
+      mark_kept(vp, rowpx + c, keep, bits, tile_counts);
+    };
+    const bool staged = c0 == 0 && c1 >= W;   // the whole depth row is in shared memory (all rows but a view's first / last)
+    for (uint32_t left = fmr; left; left &= left - 1) {
+      const int ks = __ffs(left) - 1;
+      const int f = prm.fmin + ks;
+      const float b_lo = __shfl_sync(0xffffffffu, tab, ks + 1), b_hi = __shfl_sync(0xffffffffu, tab, ks);
+      const float lo_eff = __shfl_sync(0xffffffffu, my_lo, ks);
+      const int n_cols = __shfl_sync(0xffffffffu, my_cols, ks);
+      if (fast_cfg && staged) {
+        // two independent lattice points per lane and step
+        const int step = 32 * f;
+        int c = lane * f;
+        const int c_end = n_cols * f;   // first column past the lattice
+        for (; c + step < c_end; c += 2 * step) {
+          const float a0 = align_depth(srow[c], s, t), a1 = align_depth(srow[c + step], s, t);
+          const bool h0 = (a0 >= lo_eff) && !(a0 >= b_hi), h1 = (a1 >= lo_eff) && !(a1 >= b_hi);
+          if (h0) finish_point(c);
+          if (h1) finish_point(c + step);
+        }
+        if (c < c_end) {
+          const float a0 = align_depth(srow[c], s, t);
+          if ((a0 >= lo_eff) && !(a0 >= b_hi)) finish_point(c);
+        }
+        continue;
+      }
+      for (int j = lane; j < n_cols; j += 32) {
+        const int c = j * f;
+        const float dv = (c >= c0 && c < c1) ? srow[c] : __ldg(grow + c);
+        const float a = align_depth(dv, s, t);
+        bool hit;
+        if (table && a == a) {
+          hit = (a >= b_lo) && !(a >= b_hi);
+        } else {
+          // exact arithmetic; a NaN stride (INT32_MIN) keeps index 0 only: visit it once, at fmin
+          const int fa = adaptive_factor(a, vlo, vhi, prm.fmin, prm.fmax);
+          hit = (fa == INT32_MIN) ? (r == 0 && c == 0 && f == prm.fmin) : (fa == f);
+        }
+        if (prm.flags & MDI_KEEP_SENTINEL) hit = hit && (a != -42.0f);
+        if (prm.flags & MDI_KEEP_NONNEG) hit = hit && (a >= 0.f);
+        if (hit) finish_point(c);
+      }
+    }
+    __syncwarp();   // every lane is done with the slot
+    if (lane == 0 && to_issue) {
+      const int kn = __ffs(to_issue) - 1;
+      issue(r0 + kn, slot);
+    }
+    to_issue &= to_issue - 1;   // (uniform bookkeeping; no-op when empty)
+  }
+}
+
 // Per-pixel predicate for configurations the lattice walk does not cover (no stride test,
 // strides outside 1..max).  One CTA per 4096-pixel tile, one lane per pixel.
 __global__ void __launch_bounds__(kMaskThreads)
@@ -359,10 +587,31 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
       prm.n_flat = n_strides;
       grid = dim3((unsigned)total, 1, n_views);
     }
+    // adaptive strides without the gradient test: rows staged by bulk copies (MDI_KEEP_KERNEL=lattice keeps the gathers)
+    static const bool rows_ok = [] {
+      const char* e = getenv("MDI_KEEP_KERNEL");
+      return !(e && strcmp(e, "lattice") == 0);
+    }();
+    const bool rows = rows_ok && prm.mode == MDI_SUBSAMPLE_ADAPTIVE && n_strides > 1 && n_strides <= 31 &&
+                      !(prm.flags & MDI_KEEP_GRAD) && max_width <= kRowMaxFloats && min_stride >= 1;
+    if (rows) {
+      const int depth_bytes = ((max_width * 4 + 32) + 15) & ~15;        // row + the aligned-superset slack
+      const int mask_bytes = ((max_width + 32) + 15) & ~15;
+      const int slot_bytes = depth_bytes + mask_bytes;
+      const size_t smem = (size_t)kRowWarps * 2 * slot_bytes + kRowWarps * kRowPatchBytes;
+      MDI_CUDA(cudaFuncSetAttribute(keep_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+               "mdi_keep_mask attr");
+      dim3 rgrid((unsigned)((max_height + kRowWarps * kRowsPerWarp - 1) / (kRowWarps * kRowsPerWarp)), (unsigned)n_views);
+      mdi::prof_mark("keep_rows_kernel", st);
+      keep_rows_kernel<<<rgrid, kRowWarps * 32, smem, st>>>(views, scale_shift, status, lo_hi, patch_blocked,
+                                                           factor_table, prm, slot_bytes, depth_bytes, keep, bits,
+                                                           tile_counts);
+    } else {
     mdi::prof_mark("keep_lattice_kernel", st);
     keep_lattice_kernel<<<grid, kLatticeWarps * 32, 0, st>>>(
         views, scale_shift, status, lo_hi, grad_range, patch_blocked, factor_table, prm, keep, bits,
         tile_counts);
+    }
   } else {
     mdi::prof_mark("keep_pixel_kernel", st);
     keep_pixel_kernel<<<(unsigned)total_tiles, kMaskThreads, 0, st>>>(
