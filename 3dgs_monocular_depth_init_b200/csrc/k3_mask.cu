@@ -269,6 +269,7 @@ constexpr int kRowWarps = 4;
 constexpr int kRowsPerWarp = 8;
 constexpr int kRowPatchBytes = 128;   // SfM-density patch row cached per warp (grid_w beyond: global loads)
 constexpr int kRowMaxFloats = 2048;   // widest row staged in one piece; wider views keep the gather kernel
+constexpr int kRowQueue = 256;        // survivors of the stride test queued per warp (columns), drained by full warps
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -324,6 +325,9 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
 
   unsigned char* my = s_dyn + (size_t)warp * 2 * slot_bytes;
   uint8_t* s_patch = s_dyn + (size_t)kRowWarps * 2 * slot_bytes + warp * kRowPatchBytes;
+  uint16_t* s_queue = reinterpret_cast<uint16_t*>(s_dyn + (size_t)kRowWarps * 2 * slot_bytes + kRowWarps * kRowPatchBytes) +
+                      warp * kRowQueue;
+  const uint32_t lt = (1u << lane) - 1u;
   const uint32_t bar0 = smem_addr(&s_bar[warp][0]);
   if (lane == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
@@ -428,6 +432,21 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
       }
       mark_kept(vp, rowpx + c, keep, bits, tile_counts);
     };
+    // About a quarter of the lattice points pass the stride test, a few per warp step: finishing them
+    // where they are found would run the survivor code at a quarter of the lanes nearly every step.
+    // They are queued (column only: the row is fixed) by ballot rank and finished 32 at a time.
+    int n_q = 0;   // warp-uniform
+    auto drain = [&]() {
+      __syncwarp();
+      for (int i = lane; i < n_q; i += 32) finish_point((int)s_queue[i]);
+      __syncwarp();
+      n_q = 0;
+    };
+    auto enqueue = [&](const bool hit, const int c) {   // all lanes together
+      const uint32_t m = __ballot_sync(0xffffffffu, hit);
+      if (hit) s_queue[n_q + __popc(m & lt)] = (uint16_t)c;
+      n_q += __popc(m);
+    };
     const bool staged = c0 == 0 && c1 >= W;   // the whole depth row is in shared memory (all rows but a view's first / last)
     for (uint32_t left = fmr; left; left &= left - 1) {
       const int ks = __ffs(left) - 1;
@@ -435,40 +454,44 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
       const float b_lo = __shfl_sync(0xffffffffu, tab, ks + 1), b_hi = __shfl_sync(0xffffffffu, tab, ks);
       const float lo_eff = __shfl_sync(0xffffffffu, my_lo, ks);
       const int n_cols = __shfl_sync(0xffffffffu, my_cols, ks);
-      if (fast_cfg && staged) {
-        // two independent lattice points per lane and step
-        const int step = 32 * f;
-        int c = lane * f;
-        const int c_end = n_cols * f;   // first column past the lattice
-        for (; c + step < c_end; c += 2 * step) {
-          const float a0 = align_depth(srow[c], s, t), a1 = align_depth(srow[c + step], s, t);
-          const bool h0 = (a0 >= lo_eff) && !(a0 >= b_hi), h1 = (a1 >= lo_eff) && !(a1 >= b_hi);
-          if (h0) finish_point(c);
-          if (h1) finish_point(c + step);
-        }
-        if (c < c_end) {
-          const float a0 = align_depth(srow[c], s, t);
-          if ((a0 >= lo_eff) && !(a0 >= b_hi)) finish_point(c);
-        }
-        continue;
-      }
-      for (int j = lane; j < n_cols; j += 32) {
-        const int c = j * f;
-        const float dv = (c >= c0 && c < c1) ? srow[c] : __ldg(grow + c);
-        const float a = align_depth(dv, s, t);
-        bool hit;
-        if (table && a == a) {
-          hit = (a >= b_lo) && !(a >= b_hi);
+      const int step = 32 * f;
+      const int c_end = n_cols * f;   // first column past the lattice
+      // uniform trip count: every lane takes part in the ballots, lanes past the lattice with hit = false
+      for (int cb = 0; cb < c_end; cb += 2 * step) {
+        if (n_q > kRowQueue - 64) drain();
+        const int ca = cb + lane * f, cc = ca + step;
+        const bool in0 = ca < c_end, in1 = cc < c_end;
+        bool h0, h1;
+        if (fast_cfg && staged) {
+          // (a >= 0 rules out the sentinel and a NaN; the lower bound carries it)
+          const float a0 = align_depth(srow[in0 ? ca : 0], s, t), a1 = align_depth(srow[in1 ? cc : 0], s, t);
+          h0 = in0 && (a0 >= lo_eff) && !(a0 >= b_hi);
+          h1 = in1 && (a1 >= lo_eff) && !(a1 >= b_hi);
         } else {
-          // exact arithmetic; a NaN stride (INT32_MIN) keeps index 0 only: visit it once, at fmin
-          const int fa = adaptive_factor(a, vlo, vhi, prm.fmin, prm.fmax);
-          hit = (fa == INT32_MIN) ? (r == 0 && c == 0 && f == prm.fmin) : (fa == f);
+          auto test = [&](const bool in, const int c) {
+            if (!in) return false;
+            const float dv = (c >= c0 && c < c1) ? srow[c] : __ldg(grow + c);
+            const float a = align_depth(dv, s, t);
+            bool hit;
+            if (table && a == a) {
+              hit = (a >= b_lo) && !(a >= b_hi);
+            } else {
+              // exact arithmetic; a NaN stride (INT32_MIN) keeps index 0 only: visit it once, at fmin
+              const int fa = adaptive_factor(a, vlo, vhi, prm.fmin, prm.fmax);
+              hit = (fa == INT32_MIN) ? (r == 0 && c == 0 && f == prm.fmin) : (fa == f);
+            }
+            if (prm.flags & MDI_KEEP_SENTINEL) hit = hit && (a != -42.0f);
+            if (prm.flags & MDI_KEEP_NONNEG) hit = hit && (a >= 0.f);
+            return hit;
+          };
+          h0 = test(in0, ca);
+          h1 = test(in1, cc);
         }
-        if (prm.flags & MDI_KEEP_SENTINEL) hit = hit && (a != -42.0f);
-        if (prm.flags & MDI_KEEP_NONNEG) hit = hit && (a >= 0.f);
-        if (hit) finish_point(c);
+        enqueue(h0, ca);
+        enqueue(h1, cc);
       }
     }
+    drain();
     __syncwarp();   // every lane is done with the slot
     if (lane == 0 && to_issue) {
       const int kn = __ffs(to_issue) - 1;
@@ -598,7 +621,7 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
       const int depth_bytes = ((max_width * 4 + 32) + 15) & ~15;        // row + the aligned-superset slack
       const int mask_bytes = ((max_width + 32) + 15) & ~15;
       const int slot_bytes = depth_bytes + mask_bytes;
-      const size_t smem = (size_t)kRowWarps * 2 * slot_bytes + kRowWarps * kRowPatchBytes;
+      const size_t smem = (size_t)kRowWarps * 2 * slot_bytes + kRowWarps * kRowPatchBytes + kRowWarps * kRowQueue * 2;
       MDI_CUDA(cudaFuncSetAttribute(keep_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                "mdi_keep_mask attr");
       dim3 rgrid((unsigned)((max_height + kRowWarps * kRowsPerWarp - 1) / (kRowWarps * kRowsPerWarp)), (unsigned)n_views);
