@@ -258,7 +258,7 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
 // by one get about 0.42 of the copy bandwidth out of the 64-byte DRAM bursts (the same ceiling the
 // other gather kernels sit at).  But the lattices of the strides fmin..fmax touch EVERY sector of the
 // rows they visit (a stride is at most 15 floats), and those rows are known up front: row r is
-// visited by every stride that divides it (63 % of the rows for 5..15).  So a warp takes eight
+// visited by every stride that divides it (63 % of the rows for 5..15).  So a warp takes sixteen
 // consecutive rows, and for each of them that some stride divides it streams the whole depth row and
 // the whole predicted-mask row into shared memory with two 1-D bulk copies (TMA) on an mbarrier,
 // two rows in flight per warp; the lattice points of all strides dividing the row are then read from
@@ -266,7 +266,7 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
 // the SfM-density patch row (one per ~40 image rows, fetched a row ahead), and the warps need no
 // CTA-wide barrier.  The per-point decisions are those of keep_lattice_kernel, operation for operation.
 constexpr int kRowWarps = 4;
-constexpr int kRowsPerWarp = 8;
+constexpr int kRowsPerWarp = 16;
 constexpr int kRowPatchBytes = 128;   // SfM-density patch row cached per warp (grid_w beyond: global loads)
 constexpr int kRowMaxFloats = 2048;   // widest row staged in one piece; wider views keep the gather kernel
 constexpr int kRowQueue = 256;        // survivors of the stride test queued per warp (columns), drained by full warps
@@ -289,8 +289,8 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
   const int r0 = ((int)blockIdx.x * kRowWarps + warp) * kRowsPerWarp;
   if (r0 >= H) return;   // whole warps leave: the kernel has no CTA-wide barrier
   const int n_strides = prm.fmax - prm.fmin + 1;
-  // strides dividing each of the warp's rows: lane k < 8 ends up owning the stride mask of row r0 + k
-  // (lane k < n_strides holds r0 mod f_k: one division per warp, the eight rows follow by counting up)
+  // strides dividing each of the warp's rows: lane k < 16 ends up owning the stride mask of row r0 + k
+  // (lane k < n_strides holds r0 mod f_k: one division per warp, the sixteen rows follow by counting up)
   const int my_f = prm.fmin + (lane < n_strides ? lane : 0);
   const int my_cols = (W + my_f - 1) / my_f;    // lattice columns of stride f_lane
   int rem = r0 % my_f;
@@ -304,25 +304,9 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
   uint32_t todo = __ballot_sync(0xffffffffu, fm != 0);   // rows of the warp that hold lattice points
   if (!todo) return;
 
-  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
-  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
   const float* __restrict__ depth = vp->depth;
   const bool use_pm = (prm.flags & MDI_KEEP_PRED_MASK) && vp->mask;
   const uint8_t* __restrict__ pmask = use_pm ? vp->mask : nullptr;
-  const uint8_t* __restrict__ pb =
-      ((prm.flags & MDI_KEEP_PATCH) && patch_blocked) ? patch_blocked + (int64_t)v * MDI_PATCH_STRIDE : nullptr;
-  const int patch_h = vp->patch_h, patch_w = vp->patch_w, grid_h = vp->grid_h, grid_w = vp->grid_w;
-  const uint32_t mh = 0xFFFFFFFFu / (uint32_t)max(patch_h, 1) + 1u, mw = 0xFFFFFFFFu / (uint32_t)max(patch_w, 1) + 1u;
-  // breakpoints of the view: lane L holds B[L] = row[1 + L], L <= n_strides
-  const float* trow = factor_table ? factor_table + (int64_t)v * MDI_FACTOR_TABLE_STRIDE : nullptr;
-  const bool table = trow && trow[0] != 0.f;
-  const float tab = (table && lane <= n_strides) ? trow[1 + lane] : 0.f;
-  // with MDI_KEEP_NONNEG a lattice point of stride f_k is a candidate iff a >= max(B[k+1], 0) && !(a >= B[k])
-  // (a >= 0 also rules out the sentinel and a NaN): lane k holds that lower bound
-  const float my_lo = fmaxf(__shfl_down_sync(0xffffffffu, tab, 1), 0.f);
-  const bool fast_cfg = table && (prm.flags & MDI_KEEP_NONNEG);
-  const float vlo = lo_hi[2 * v], vhi = lo_hi[2 * v + 1];
-
   unsigned char* my = s_dyn + (size_t)warp * 2 * slot_bytes;
   uint8_t* s_patch = s_dyn + (size_t)kRowWarps * 2 * slot_bytes + warp * kRowPatchBytes;
   uint16_t* s_queue = reinterpret_cast<uint16_t*>(s_dyn + (size_t)kRowWarps * 2 * slot_bytes + kRowWarps * kRowPatchBytes) +
@@ -374,6 +358,24 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
     }
   }
   to_issue = __shfl_sync(0xffffffffu, to_issue, 0);
+
+  // per-view constants: loaded while the first rows are on their way
+  const float s = scale_shift ? scale_shift[2 * v] : 1.f;
+  const float t = scale_shift ? scale_shift[2 * v + 1] : 0.f;
+  const uint8_t* __restrict__ pb =
+      ((prm.flags & MDI_KEEP_PATCH) && patch_blocked) ? patch_blocked + (int64_t)v * MDI_PATCH_STRIDE : nullptr;
+  const int patch_h = vp->patch_h, patch_w = vp->patch_w, grid_h = vp->grid_h, grid_w = vp->grid_w;
+  const uint32_t mh = 0xFFFFFFFFu / (uint32_t)max(patch_h, 1) + 1u, mw = 0xFFFFFFFFu / (uint32_t)max(patch_w, 1) + 1u;
+  // breakpoints of the view: lane L holds B[L] = row[1 + L], L <= n_strides
+  const float* trow = factor_table ? factor_table + (int64_t)v * MDI_FACTOR_TABLE_STRIDE : nullptr;
+  const bool table = trow && trow[0] != 0.f;
+  const float tab = (table && lane <= n_strides) ? trow[1 + lane] : 0.f;
+  // with MDI_KEEP_NONNEG a lattice point of stride f_k is a candidate iff a >= max(B[k+1], 0) && !(a >= B[k])
+  // (a >= 0 also rules out the sentinel and a NaN): lane k holds that lower bound
+  const float my_lo = fmaxf(__shfl_down_sync(0xffffffffu, tab, 1), 0.f);
+  const bool fast_cfg = table && (prm.flags & MDI_KEEP_NONNEG);
+  const float vlo = lo_hi[2 * v], vhi = lo_hi[2 * v + 1];
+
 
   int cached_pr = -1;   // patch row held in s_patch
   for (int i = 0; todo; ++i) {
