@@ -139,13 +139,16 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
-def algorithmic_bytes(kernel: str, HW: int, V: int, n_kept: int, n_sfm_slots: int, adaptive: bool) -> float:
+def algorithmic_bytes(kernel: str, HW: int, V: int, n_kept: int, n_sfm_slots: int, adaptive: bool,
+                      lattice_row_fraction: float = 0.6004) -> float:
     """Algorithmic bytes of one launch of a kernel, per SURVEY.md 8(d): per view
-    B = P*HW*5 + HW + 36*Nk + 16*M, split over the kernels that move them."""
+    B = P*HW*5 + HW + 36*Nk + 16*M, split over the kernels that move them.  lattice_row_fraction: share of
+    the image rows that some stride of the default range 5..15 divides (counted: 0.6004)."""
     return {
         "stats_main_kernel": V * HW * 5.0,            # the one statistics read of depth + mask
         "keep_lattice_kernel": V * HW * 5.0,          # the mask pass's read of depth + mask (rows without
                                                       # a lattice point are skipped: real traffic is lower)
+        "keep_rows_kernel": V * HW * 5.0 * lattice_row_fraction,   # depth + mask of the rows some stride divides
         "keep_zero_fill": V * HW * 1.0,               # keep mask written
         "emit_points_kernel": 36.0 * n_kept,          # rgb read, xyz + rgb written
         "project_filter_kernel": 16.0 * n_sfm_slots,  # sfm xyz + index
