@@ -261,14 +261,14 @@ keep_lattice_kernel(const MdiView* __restrict__ views, const float* __restrict__
 // visited by every stride that divides it (63 % of the rows for 5..15).  So a warp takes sixteen
 // consecutive rows, and for each of them that some stride divides it streams the whole depth row and
 // the whole predicted-mask row into shared memory with two 1-D bulk copies (TMA) on an mbarrier,
-// two rows in flight per warp; the lattice points of all strides dividing the row are then read from
-// shared memory.  DRAM sees long sequential reads, the per-point work has no global load left except
+// two rows in flight per warp (rows wider than 2048 pixels go through the slots in column segments);
+// the lattice points of all strides dividing the row are then read from shared memory.  DRAM sees long sequential reads, the per-point work has no global load left except
 // the SfM-density patch row (one per ~40 image rows, fetched a row ahead), and the warps need no
 // CTA-wide barrier.  The per-point decisions are those of keep_lattice_kernel, operation for operation.
 constexpr int kRowWarps = 4;
 constexpr int kRowsPerWarp = 16;
 constexpr int kRowPatchBytes = 128;   // SfM-density patch row cached per warp (grid_w beyond: global loads)
-constexpr int kRowMaxFloats = 2048;   // widest row staged in one piece; wider views keep the gather kernel
+constexpr int kRowSeg = 2048;         // columns staged per piece: a wider row goes through its slot in segments
 constexpr int kRowQueue = 256;        // survivors of the stride test queued per warp (columns), drained by full warps
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -292,7 +292,6 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
   // strides dividing each of the warp's rows: lane k < 16 ends up owning the stride mask of row r0 + k
   // (lane k < n_strides holds r0 mod f_k: one division per warp, the sixteen rows follow by counting up)
   const int my_f = prm.fmin + (lane < n_strides ? lane : 0);
-  const int my_cols = (W + my_f - 1) / my_f;    // lattice columns of stride f_lane
   int rem = r0 % my_f;
   uint32_t fm = 0;
 #pragma unroll
@@ -334,10 +333,12 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
     if (h < l) h = l;
     *lo = l; *hi = h;
   };
-  auto issue = [&](int r, int slot) {   // lane 0: both rows of image row r into `slot`, one barrier
+  const int n_seg = (W + kRowSeg - 1) / kRowSeg;
+  auto issue = [&](int r, int seg, int slot) {   // lane 0: columns of segment `seg` of image row r, depth and mask, one barrier
+    const int seg_lo = seg * kRowSeg, seg_len = min(W - seg_lo, kRowSeg);
     uintptr_t dl, dh, ml = 0, mh_ = 0;
-    span(d_base + (size_t)r * W * 4, (size_t)W * 4, d_lo_lim, d_hi_lim, &dl, &dh);
-    if (pmask) span(m_base + (size_t)r * W, (size_t)W, m_lo_lim, m_hi_lim, &ml, &mh_);
+    span(d_base + ((size_t)r * W + seg_lo) * 4, (size_t)seg_len * 4, d_lo_lim, d_hi_lim, &dl, &dh);
+    if (pmask) span(m_base + (size_t)r * W + seg_lo, (size_t)seg_len, m_lo_lim, m_hi_lim, &ml, &mh_);
     const uint32_t db = (uint32_t)(dh - dl), mb = (uint32_t)(mh_ - ml);
     const uint32_t bar = bar0 + 8 * slot;
     const uint32_t dst = smem_addr(my + (size_t)slot * slot_bytes);
@@ -349,15 +350,16 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                    ::"r"(dst + (uint32_t)depth_bytes), "l"(ml), "r"(mb), "r"(bar) : "memory");
   };
-  uint32_t to_issue = todo;
-  if (lane == 0) {
-    for (int slot = 0; slot < 2 && to_issue; ++slot) {
-      const int k = __ffs(to_issue) - 1;
-      issue(r0 + k, slot);
-      to_issue &= to_issue - 1;
-    }
-  }
-  to_issue = __shfl_sync(0xffffffffu, to_issue, 0);
+  // issue cursor (the same in every lane; lane 0 issues): next (row, segment) piece to put in flight
+  uint32_t iss_rows = todo;
+  int iss_seg = 0;
+  auto issue_next = [&](int slot) {
+    if (!iss_rows) return;
+    if (lane == 0) issue(r0 + __ffs(iss_rows) - 1, iss_seg, slot);
+    if (++iss_seg == n_seg) { iss_seg = 0; iss_rows &= iss_rows - 1; }
+  };
+  issue_next(0);
+  issue_next(1);
 
   // per-view constants: loaded while the first rows are on their way
   const float s = scale_shift ? scale_shift[2 * v] : 1.f;
@@ -378,12 +380,12 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
 
 
   int cached_pr = -1;   // patch row held in s_patch
-  for (int i = 0; todo; ++i) {
+  int i = 0;            // pieces consumed so far: piece i sits in slot i & 1, (i / 2)-th use of it
+  while (todo) {
     const int k = __ffs(todo) - 1;
     todo &= todo - 1;
     const int r = r0 + k;
     const uint32_t fmr = __shfl_sync(0xffffffffu, fm, k);
-    const int slot = i & 1;
     // SfM-density patch row of this image row (changes every patch_h rows): fetched before the wait
     const int pr = pb ? (patch_h <= 1 ? r : (int)__umulhi((uint32_t)r, mh)) : -1;
     const bool pr_in = pb && pr < grid_h;
@@ -393,7 +395,10 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
       cached_pr = pr;
       __syncwarp();
     }
-    {   // wait for the row (phase of this slot's (i / 2)-th use)
+    for (int seg = 0; seg < n_seg; ++seg, ++i) {
+    const int slot = i & 1;
+    const int seg_lo = seg * kRowSeg, seg_hi = min(W, seg_lo + kRowSeg);
+    {   // wait for the piece (phase of this slot's (i / 2)-th use)
       const uint32_t bar = bar0 + 8 * slot, parity = (uint32_t)(i >> 1) & 1u;
       uint32_t ok = 0;
       while (!ok) {
@@ -406,17 +411,17 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
     }
     const int64_t rowpx = (int64_t)r * W;
     uintptr_t dl, dh, ml = 0, mh_ = 0;
-    span(d_base + (size_t)rowpx * 4, (size_t)W * 4, d_lo_lim, d_hi_lim, &dl, &dh);
-    if (pmask) span(m_base + (size_t)rowpx, (size_t)W, m_lo_lim, m_hi_lim, &ml, &mh_);
-    // column c of the row sits at srow[c] for c0 <= c < c1 (srow may point in front of the slot)
-    const intptr_t d_off = (intptr_t)dl - (intptr_t)(d_base + (size_t)rowpx * 4);   // bytes, multiple of 4
+    span(d_base + ((size_t)rowpx + seg_lo) * 4, (size_t)(seg_hi - seg_lo) * 4, d_lo_lim, d_hi_lim, &dl, &dh);
+    if (pmask) span(m_base + (size_t)rowpx + seg_lo, (size_t)(seg_hi - seg_lo), m_lo_lim, m_hi_lim, &ml, &mh_);
+    // column c of the row sits at srow[c] for c0 <= c < c1 (srow points in front of the slot)
+    const intptr_t d_off = (intptr_t)dl - (intptr_t)(d_base + (size_t)rowpx * 4);   // bytes from the row start, multiple of 4
     const float* srow = reinterpret_cast<const float*>(my + (size_t)slot * slot_bytes) - d_off / 4;
-    const int c0 = d_off > 0 ? (int)(d_off / 4) : 0;
-    const int c1 = (int)min((intptr_t)W, ((intptr_t)dh - (intptr_t)(d_base + (size_t)rowpx * 4)) / 4);
+    const int c0 = max(seg_lo, (int)(d_off / 4));
+    const int c1 = (int)min((intptr_t)seg_hi, ((intptr_t)dh - (intptr_t)(d_base + (size_t)rowpx * 4)) / 4);
     const intptr_t m_off = (intptr_t)ml - (intptr_t)(m_base + (size_t)rowpx);
     const uint8_t* smask = my + (size_t)slot * slot_bytes + depth_bytes - m_off;
-    const int m0 = m_off > 0 ? (int)m_off : 0;
-    const int m1 = (int)min((intptr_t)W, (intptr_t)mh_ - (intptr_t)(m_base + (size_t)rowpx));
+    const int m0 = max(seg_lo, (int)m_off);
+    const int m1 = (int)min((intptr_t)seg_hi, (intptr_t)mh_ - (intptr_t)(m_base + (size_t)rowpx));
     const float* grow = depth + rowpx;
 
     // survivors of the stride test: predicted mask, SfM-density patch, then the outputs
@@ -440,7 +445,7 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
     int n_q = 0;   // warp-uniform
     auto drain = [&]() {
       __syncwarp();
-      for (int i = lane; i < n_q; i += 32) finish_point((int)s_queue[i]);
+      for (int qi = lane; qi < n_q; qi += 32) finish_point((int)s_queue[qi]);
       __syncwarp();
       n_q = 0;
     };
@@ -449,24 +454,24 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
       if (hit) s_queue[n_q + __popc(m & lt)] = (uint16_t)c;
       n_q += __popc(m);
     };
-    const bool staged = c0 == 0 && c1 >= W;   // the whole depth row is in shared memory (all rows but a view's first / last)
+    const bool staged = c0 == seg_lo && c1 >= seg_hi;   // the piece's depths are all in shared memory (all but a view's first / last row)
     for (uint32_t left = fmr; left; left &= left - 1) {
       const int ks = __ffs(left) - 1;
       const int f = prm.fmin + ks;
       const float b_lo = __shfl_sync(0xffffffffu, tab, ks + 1), b_hi = __shfl_sync(0xffffffffu, tab, ks);
       const float lo_eff = __shfl_sync(0xffffffffu, my_lo, ks);
-      const int n_cols = __shfl_sync(0xffffffffu, my_cols, ks);
       const int step = 32 * f;
-      const int c_end = n_cols * f;   // first column past the lattice
+      const int c_begin = seg_lo ? ((seg_lo + f - 1) / f) * f : 0;   // first lattice column of the piece
+      const int c_end = seg_hi;   // (a lattice column is < W, so "in the piece" is all there is to test)
       // uniform trip count: every lane takes part in the ballots, lanes past the lattice with hit = false
-      for (int cb = 0; cb < c_end; cb += 2 * step) {
+      for (int cb = c_begin; cb < c_end; cb += 2 * step) {
         if (n_q > kRowQueue - 64) drain();
         const int ca = cb + lane * f, cc = ca + step;
         const bool in0 = ca < c_end, in1 = cc < c_end;
         bool h0, h1;
         if (fast_cfg && staged) {
           // (a >= 0 rules out the sentinel and a NaN; the lower bound carries it)
-          const float a0 = align_depth(srow[in0 ? ca : 0], s, t), a1 = align_depth(srow[in1 ? cc : 0], s, t);
+          const float a0 = align_depth(srow[in0 ? ca : seg_lo], s, t), a1 = align_depth(srow[in1 ? cc : seg_lo], s, t);
           h0 = in0 && (a0 >= lo_eff) && !(a0 >= b_hi);
           h1 = in1 && (a1 >= lo_eff) && !(a1 >= b_hi);
         } else {
@@ -495,11 +500,8 @@ keep_rows_kernel(const MdiView* __restrict__ views, const float* __restrict__ sc
     }
     drain();
     __syncwarp();   // every lane is done with the slot
-    if (lane == 0 && to_issue) {
-      const int kn = __ffs(to_issue) - 1;
-      issue(r0 + kn, slot);
+    issue_next(slot);
     }
-    to_issue &= to_issue - 1;   // (uniform bookkeeping; no-op when empty)
   }
 }
 
@@ -618,10 +620,11 @@ extern "C" int mdi_keep_mask(const MdiView* views, int n_views, int64_t total_ti
       return !(e && strcmp(e, "lattice") == 0);
     }();
     const bool rows = rows_ok && prm.mode == MDI_SUBSAMPLE_ADAPTIVE && n_strides > 1 && n_strides <= 31 &&
-                      !(prm.flags & MDI_KEEP_GRAD) && max_width <= kRowMaxFloats && min_stride >= 1;
+                      !(prm.flags & MDI_KEEP_GRAD) && min_stride >= 1;
     if (rows) {
-      const int depth_bytes = ((max_width * 4 + 32) + 15) & ~15;        // row + the aligned-superset slack
-      const int mask_bytes = ((max_width + 32) + 15) & ~15;
+      const int piece = max_width < kRowSeg ? max_width : kRowSeg;       // columns staged at a time
+      const int depth_bytes = ((piece * 4 + 32) + 15) & ~15;            // piece + the aligned-superset slack
+      const int mask_bytes = ((piece + 32) + 15) & ~15;
       const int slot_bytes = depth_bytes + mask_bytes;
       const size_t smem = (size_t)kRowWarps * 2 * slot_bytes + kRowWarps * kRowPatchBytes + kRowWarps * kRowQueue * 2;
       MDI_CUDA(cudaFuncSetAttribute(keep_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
